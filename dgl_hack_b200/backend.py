@@ -1,0 +1,145 @@
+"""PyTorch-side kernel dispatch: autograd wrappers around dgl_hack_b200.kernel.
+
+Same public surface as the reference's torch backend for this path
+(python/dgl/backend/pytorch/tensor.py:286-381 BinaryReduce / binary_reduce, :519-569 CopyReduce /
+copy_reduce, :572-601 _reduce_grad; interface python/dgl/backend/backend.py:1189-1300):
+
+    binary_reduce(reducer, binary_op, graph, lhs, rhs, lhs_data, rhs_data, out_size,
+                  lhs_map=(None, None), rhs_map=(None, None), out_map=(None, None))
+    copy_reduce(reducer, graph, target, in_data, out_size, in_map=(None, None),
+                out_map=(None, None))
+
+`graph` is a dgl_hack_b200.GraphIndex; maps are (forward_map, backward_map) pairs of int32 CUDA
+tensors. "mean" is handled here like in the reference (the C kernels reject it): sum, then divide
+by the clamped in-degree; gradients are first divided by the same degrees. When there are no id
+mappings the degree comes straight from the in-CSR and copy+mean runs as ONE fused kernel.
+All tensors must live on the graph's CUDA device: there is no CPU fallback.
+"""
+import torch as th
+
+from . import kernel as K
+
+SRC, DST, EDGE = 0, 1, 2  # python/dgl/function/base.py TargetCode
+
+
+def _degrees_for_mean(graph, target, n_in, in_map, out_map, out_rows, like):
+    """In-degree per output row as a float tensor (clamped to >= 1), shaped for broadcasting
+    against an output of `like.dim()` dims. With mappings this is the reference's second
+    copy_reduce over a ones-vector (tensor.py:313-327, 529-540)."""
+    if in_map is None and out_map is None and out_rows == graph.num_dst:
+        degs = graph.in_degrees().to(like.dtype)
+    else:
+        ones = like.new_ones((n_in,))
+        degs = like.new_empty((out_rows,))
+        K.copy_reduce("sum", graph, target, ones, degs, in_map, out_map)
+    return degs.reshape((out_rows,) + (1,) * (like.dim() - 1)).clamp(min=1)
+
+
+def _reduce_grad(grad, shape):
+    """Sum an unreduced gradient (output feature shape) back onto the operand's own feature shape
+    (tensor.py:572-601)."""
+    shape = tuple(shape)
+    g_feat, in_feat = tuple(grad.shape[1:]), shape[1:]
+    if g_feat == in_feat:
+        return grad
+    padded = (1,) * (len(g_feat) - len(in_feat)) + in_feat
+    dims = tuple(i + 1 for i, (a, b) in enumerate(zip(g_feat, padded)) if a != b)
+    return grad.sum(dim=dims, keepdim=True).view(shape)
+
+
+class BinaryReduce(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, reducer, binary_op, graph, lhs, rhs, lhs_data, rhs_data, out_data,
+                out_size, lhs_map, rhs_map, out_map):
+        feat_shape = K.infer_binary_feature_shape(binary_op, lhs_data, rhs_data)
+        kreducer = "sum" if reducer == "mean" else reducer
+        K.binary_op_reduce(kreducer, binary_op, graph, lhs, rhs, lhs_data, rhs_data, out_data,
+                           lhs_map[0], rhs_map[0], out_map[0])
+        degs = None
+        if reducer == "mean":
+            # degree over the operand that is NOT the destination (tensor.py:313-321)
+            if lhs != DST:
+                tgt, n, imap = lhs, lhs_data.shape[0], lhs_map[0]
+            else:
+                tgt, n, imap = rhs, rhs_data.shape[0], rhs_map[0]
+            degs = _degrees_for_mean(graph, tgt, n, imap, out_map[0], out_data.shape[0], out_data)
+            out_data = out_data / degs
+        ctx.backward_cache = (reducer, binary_op, graph, lhs, rhs, lhs_map, rhs_map, out_map,
+                              feat_shape, degs)
+        ctx.save_for_backward(lhs_data, rhs_data, out_data)
+        return out_data
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (reducer, binary_op, graph, lhs, rhs, lhs_map, rhs_map, out_map, feat_shape,
+         degs) = ctx.backward_cache
+        lhs_data, rhs_data, out_data = ctx.saved_tensors
+        kreducer = "sum" if reducer == "mean" else reducer
+        if reducer == "mean":
+            grad_out = grad_out / degs
+        grad_out = grad_out.contiguous()
+        grad_lhs = grad_rhs = None
+        if ctx.needs_input_grad[5]:
+            grad_lhs = grad_out.new_empty((lhs_data.shape[0],) + feat_shape)
+            K.backward_lhs_binary_op_reduce(kreducer, binary_op, graph, lhs, rhs, lhs_data,
+                                            rhs_data, out_data, grad_out, grad_lhs, lhs_map[1],
+                                            rhs_map[1], out_map[1])
+            grad_lhs = _reduce_grad(grad_lhs, lhs_data.shape)
+        if ctx.needs_input_grad[6]:
+            grad_rhs = grad_out.new_empty((rhs_data.shape[0],) + feat_shape)
+            K.backward_rhs_binary_op_reduce(kreducer, binary_op, graph, lhs, rhs, lhs_data,
+                                            rhs_data, out_data, grad_out, grad_rhs, lhs_map[1],
+                                            rhs_map[1], out_map[1])
+            grad_rhs = _reduce_grad(grad_rhs, rhs_data.shape)
+        return (None, None, None, None, None, grad_lhs, grad_rhs, None, None, None, None, None)
+
+
+def binary_reduce(reducer, binary_op, graph, lhs, rhs, lhs_data, rhs_data, out_size,
+                  lhs_map=(None, None), rhs_map=(None, None), out_map=(None, None)):
+    lhs_data, rhs_data = lhs_data.contiguous(), rhs_data.contiguous()
+    feat_shape = K.infer_binary_feature_shape(binary_op, lhs_data, rhs_data)
+    out_shape = feat_shape[:-1] if binary_op == "dot" else feat_shape
+    out_data = lhs_data.new_empty((out_size,) + out_shape)
+    return BinaryReduce.apply(reducer, binary_op, graph, lhs, rhs, lhs_data, rhs_data, out_data,
+                              out_size, lhs_map, rhs_map, out_map)
+
+
+class CopyReduce(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, reducer, graph, target, in_data, out_data, out_size, in_map, out_map):
+        degs = None
+        if reducer == "mean":
+            degs = _degrees_for_mean(graph, target, in_data.shape[0], in_map[0], out_map[0],
+                                     out_data.shape[0], out_data)
+            if in_map[0] is None and out_map[0] is None and out_size == graph.num_dst:
+                # one fused pass: sum in in-CSR order, then one IEEE division by the degree
+                K.copy_reduce_mean(graph, target, in_data, out_data)
+            else:
+                K.copy_reduce("sum", graph, target, in_data, out_data, in_map[0], out_map[0])
+                out_data = out_data / degs
+        else:
+            K.copy_reduce(reducer, graph, target, in_data, out_data, in_map[0], out_map[0])
+        ctx.backward_cache = (reducer, graph, target, in_map, out_map, degs)
+        ctx.save_for_backward(in_data, out_data)
+        return out_data
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        reducer, graph, target, in_map, out_map, degs = ctx.backward_cache
+        in_data, out_data = ctx.saved_tensors
+        grad_in = None
+        if reducer == "mean":
+            grad_out = grad_out / degs
+        grad_out = grad_out.contiguous()
+        if ctx.needs_input_grad[3]:
+            grad_in = grad_out.new_empty(in_data.shape)
+            K.backward_copy_reduce("sum" if reducer == "mean" else reducer, graph, target,
+                                   in_data, out_data, grad_out, grad_in, in_map[1], out_map[1])
+        return None, None, None, grad_in, None, None, None, None
+
+
+def copy_reduce(reducer, graph, target, in_data, out_size, in_map=(None, None),
+                out_map=(None, None)):
+    in_data = in_data.contiguous()
+    out_data = in_data.new_empty((out_size,) + in_data.shape[1:])
+    return CopyReduce.apply(reducer, graph, target, in_data, out_data, out_size, in_map, out_map)

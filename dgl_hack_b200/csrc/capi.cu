@@ -1,0 +1,615 @@
+// C-ABI entry points for the kernels: argument checks, broadcast inference, commutative operand
+// swap and dispatch. Host logic restates src/kernel/binary_reduce.cc:74-155 (HasBcast /
+// CalcBcastInfo), :176-219 (CheckCtx / CheckIdArray / NeedSwitchOrder) and the entry functions
+// :295-336, :452-500, :551-598, :628-647, :667-695. Declarations: include/dgl_b200.h.
+#include <algorithm>
+#include <cstring>
+#include <sstream>
+#include <vector>
+
+#include "../../include/dgl_b200.h"
+#include "common.cuh"
+
+namespace b200 {
+
+static thread_local std::string g_last_error;
+static thread_local const char* g_last_kernel = "";
+static thread_local int64_t g_launches = 0;
+
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+void note_kernel(const char* family, int launches) {
+  if (family) g_last_kernel = family;
+  g_launches += launches;
+}
+
+// ---------------------------------------------------------------- tensor helpers
+static bool is_null(const DGLB200Tensor* t) {
+  // aten::IsNullArray (include/dgl/array.h:102-104): shape[0] == 0; NULL pointer also accepted
+  return t == nullptr || (t->ndim >= 1 && t->shape && t->shape[0] == 0) || t->ndim == 0;
+}
+
+static std::string shape_string(const DGLB200Tensor* t) {
+  std::ostringstream oss;
+  oss << "(";
+  for (int i = 1; i < t->ndim; ++i) {
+    if (i != 1) oss << ",";
+    oss << t->shape[i];
+  }
+  oss << ")";
+  return oss.str();
+}
+
+static int64_t num_elements(const DGLB200Tensor* t) {
+  int64_t n = 1;
+  for (int i = 0; i < t->ndim; ++i) n *= t->shape[i];
+  return n;
+}
+
+static int64_t feat_len(const DGLB200Tensor* t) {
+  int64_t n = 1;
+  for (int i = 1; i < t->ndim; ++i) n *= t->shape[i];
+  return n;
+}
+
+static void check_compact(const DGLB200Tensor* t, const char* name) {
+  if (!t->strides) return;
+  int64_t expect = 1;
+  for (int i = t->ndim - 1; i >= 0; --i) {
+    if (t->shape[i] != 1 && t->strides[i] != expect)
+      throw ApiError{std::string(name) + " must be a compact row-major tensor"};
+    expect *= t->shape[i];
+  }
+}
+
+template <typename T>
+static T* data_ptr(const DGLB200Tensor* t) {
+  return reinterpret_cast<T*>(static_cast<char*>(t->data) + t->byte_offset);
+}
+
+// CheckCtx (binary_reduce.cc:176-190): every non-null array on the graph's device.
+static void check_ctx(const DGLB200Graph* g, const std::vector<const DGLB200Tensor*>& arrays,
+                      const std::vector<const char*>& names) {
+  for (size_t i = 0; i < arrays.size(); ++i) {
+    if (is_null(arrays[i])) continue;
+    const DGLB200Tensor* t = arrays[i];
+    if (t->ctx.device_type != 2 || t->ctx.device_id != g->device) {
+      std::ostringstream oss;
+      oss << "Expected device context gpu(" << g->device << "). But got "
+          << (t->ctx.device_type == 1 ? "cpu" : t->ctx.device_type == 2 ? "gpu" : "dev") << "("
+          << t->ctx.device_id << ") for " << names[i]
+          << ". (this library has no CPU path)";
+      throw ApiError{oss.str()};
+    }
+    check_compact(t, names[i]);
+  }
+}
+
+// CheckIdArray (binary_reduce.cc:193-206): int, 1-D, same width as the graph ids (32 here).
+static void check_id_arrays(const std::vector<const DGLB200Tensor*>& arrays,
+                            const std::vector<const char*>& names) {
+  for (size_t i = 0; i < arrays.size(); ++i) {
+    if (is_null(arrays[i])) continue;
+    const DGLB200Tensor* t = arrays[i];
+    B200_CHECK(t->dtype.code == 0, std::string("Check failed: dtype.code == kDLInt for ") + names[i]);
+    B200_CHECK(t->ndim == 1, std::string("Check failed: ndim == 1 for ") + names[i]);
+    if (t->dtype.bits != 32) {
+      std::ostringstream oss;
+      oss << "Expected 32 integer array. But got " << (int)t->dtype.bits << " for " << names[i]
+          << ".";
+      throw ApiError{oss.str()};
+    }
+  }
+}
+
+static void check_float(const DGLB200Tensor* t, const char* name) {
+  // DGL_DTYPE_SWITCH (src/kernel/common.h:49-55): float32 only
+  if (!(t->dtype.code == 2 && t->dtype.bits == 32 && t->dtype.lanes == 1))
+    throw ApiError{std::string("Unsupported dtype for ") + name + ": only float32 is supported"};
+}
+
+static const int32_t* map_ptr(const DGLB200Tensor* t) {
+  return is_null(t) ? nullptr : data_ptr<const int32_t>(t);
+}
+
+static int parse_op(const std::string& op) {
+  if (op == "add") return kAdd;
+  if (op == "sub") return kSub;
+  if (op == "mul") return kMul;
+  if (op == "div") return kDiv;
+  if (op == "dot") return kDot;
+  if (op == "use_lhs") return kUseLhs;
+  throw ApiError{"Unsupported binary op: " + op};
+}
+
+static int parse_reducer(const std::string& r) {
+  if (r == "sum") return kSum;
+  if (r == "max") return kMax;
+  if (r == "min") return kMin;
+  if (r == "prod") return kProd;
+  if (r == "none") return kRNone;
+  if (r == "mean") throw ApiError{"reduce mean is not supported."};  // binary_reduce_impl.h:95-98
+  throw ApiError{"Unsupported reducer: " + r};
+}
+
+static void check_target(int t, const char* name) {
+  if (t < 0 || t > 2) throw ApiError{std::string("Invalid target code for ") + name};
+}
+
+// ---------------------------------------------------------------- broadcast inference
+static bool has_bcast(const DGLB200Tensor* l, const DGLB200Tensor* r) {
+  if (l->ndim != r->ndim) return true;
+  for (int i = 1; i < l->ndim; ++i)
+    if (l->shape[i] != r->shape[i]) return true;
+  return false;
+}
+
+struct BcastHost {
+  std::vector<int64_t> real_out_shape, lhs_shape, rhs_shape, out_shape;
+  int64_t data_len = 1;
+};
+
+static BcastHost calc_bcast(const std::string& op, const DGLB200Tensor* lhs,
+                            const DGLB200Tensor* rhs) {
+  BcastHost ret;
+  const int max_ndim = std::max(lhs->ndim, rhs->ndim) - 1;
+  int64_t accum = 0;
+  int j = 0;
+  if (op == "dot") {
+    ret.data_len = lhs->shape[lhs->ndim - 1];
+    ++j;
+    ret.real_out_shape.push_back(ret.data_len);
+  }
+  for (; j < max_ndim; ++j) {
+    const int64_t dl = (lhs->ndim - 1 - j < 1) ? 1 : lhs->shape[lhs->ndim - 1 - j];
+    const int64_t dr = (rhs->ndim - 1 - j < 1) ? 1 : rhs->shape[rhs->ndim - 1 - j];
+    if (dl != dr) {
+      if (dl != 1 && dr != 1)
+        throw ApiError{"Invalid broadcasting between feature shapes " + shape_string(lhs) +
+                       " and " + shape_string(rhs)};
+      if (accum != 0) {
+        ret.lhs_shape.push_back(accum);
+        ret.rhs_shape.push_back(accum);
+        ret.out_shape.push_back(accum);
+        accum = 0;
+      }
+      ret.lhs_shape.push_back(dl);
+      ret.rhs_shape.push_back(dr);
+      ret.out_shape.push_back(std::max(dl, dr));
+    } else {
+      accum = (accum == 0) ? dl : accum * dl;
+    }
+    ret.real_out_shape.push_back(std::max(dl, dr));
+  }
+  if (accum != 0) {
+    ret.lhs_shape.push_back(accum);
+    ret.rhs_shape.push_back(accum);
+    ret.out_shape.push_back(accum);
+  }
+  std::reverse(ret.real_out_shape.begin(), ret.real_out_shape.end());
+  std::reverse(ret.lhs_shape.begin(), ret.lhs_shape.end());
+  std::reverse(ret.rhs_shape.begin(), ret.rhs_shape.end());
+  std::reverse(ret.out_shape.begin(), ret.out_shape.end());
+  return ret;
+}
+
+static void fill_dims(const std::vector<int64_t>& shape, int* sh, int* st, int64_t* len) {
+  const int n = (int)shape.size();
+  int64_t run = 1;
+  for (int i = n - 1; i >= 0; --i) {
+    sh[i] = (int)shape[i];
+    st[i] = (int)run;
+    run *= shape[i];
+  }
+  for (int i = n; i < kMaxBcastDim; ++i) {
+    sh[i] = 1;
+    st[i] = 0;
+  }
+  *len = run;
+}
+
+// Bcast for a (lhs, rhs) pair: broadcast path (BinaryReduceBcastImpl) or the plain path
+// (BinaryReduceImpl: x_len = prod(out feat), data_len = last dim for dot).
+static Bcast make_bcast(const std::string& op, const DGLB200Tensor* lhs,
+                        const DGLB200Tensor* rhs) {
+  Bcast bc;
+  std::memset(&bc, 0, sizeof(bc));
+  if (rhs != nullptr && has_bcast(lhs, rhs)) {
+    BcastHost h = calc_bcast(op, lhs, rhs);
+    if (h.out_shape.size() > (size_t)kMaxBcastDim)
+      throw ApiError{"Too many broadcasting dimensions."};
+    bc.ndim = (int)h.out_shape.size();
+    fill_dims(h.lhs_shape, bc.lhs_shape, bc.lhs_stride, &bc.lhs_len);
+    fill_dims(h.rhs_shape, bc.rhs_shape, bc.rhs_stride, &bc.rhs_len);
+    fill_dims(h.out_shape, bc.out_shape, bc.out_stride, &bc.out_len);
+    bc.data_len = h.data_len;
+    if (bc.ndim == 0) {  // all feature dims were consumed by dot: a single output element
+      bc.ndim = 1;
+      bc.lhs_shape[0] = bc.rhs_shape[0] = bc.out_shape[0] = 1;
+      bc.lhs_stride[0] = bc.rhs_stride[0] = bc.out_stride[0] = 1;
+      bc.lhs_len = bc.rhs_len = bc.out_len = 1;
+    }
+  } else {
+    int64_t feat = feat_len(lhs);
+    int64_t dl = 1;
+    if (op == "dot") {
+      B200_CHECK(lhs->ndim >= 2, "dot needs at least one feature dimension");
+      dl = lhs->shape[lhs->ndim - 1];
+    }
+    const int64_t x = dl > 0 ? feat / dl : 0;
+    bc.ndim = 1;
+    std::vector<int64_t> shp{x};
+    fill_dims(shp, bc.lhs_shape, bc.lhs_stride, &bc.lhs_len);
+    fill_dims(shp, bc.rhs_shape, bc.rhs_stride, &bc.rhs_len);
+    fill_dims(shp, bc.out_shape, bc.out_stride, &bc.out_len);
+    bc.data_len = dl;
+  }
+  return bc;
+}
+
+static bool need_switch_order(int op, int lhs, int rhs) {
+  if (lhs == rhs) throw ApiError{"Check failed: lhs != rhs"};
+  return (op == kAdd || op == kMul) && lhs > rhs;
+}
+
+static int64_t expected_rows(const DGLB200Graph* g, int tgt) {
+  return tgt == kSrc ? g->num_src : (tgt == kDst ? g->num_dst : g->num_edges);
+}
+
+// A data tensor addressed WITHOUT a mapping must have one row per node / edge of its target;
+// with a mapping the ids come from the caller (not validated, as in the reference).
+static void check_rows(const DGLB200Graph* g, const DGLB200Tensor* t, int tgt, bool mapped,
+                       const char* name) {
+  if (mapped) return;
+  const int64_t need = expected_rows(g, tgt);
+  if (t->ndim < 1 || t->shape[0] < need) {
+    std::ostringstream oss;
+    oss << name << " has " << (t->ndim < 1 ? 0 : t->shape[0]) << " rows but its target has "
+        << need;
+    throw ApiError{oss.str()};
+  }
+}
+
+static void dispatch(const KernelCall& c) {
+  B200_CUDA(cudaSetDevice(c.g->device));
+  if (try_spmm(c)) return;
+  if (try_sddmm(c)) return;
+  run_generic(c);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+#define API_BEGIN() try {
+#define API_END()                                     \
+  }                                                   \
+  catch (const ::b200::ApiError& e) {                 \
+    ::b200::set_last_error(e.msg);                    \
+    return -1;                                        \
+  }                                                   \
+  catch (const std::exception& e) {                   \
+    ::b200::set_last_error(e.what());                 \
+    return -1;                                        \
+  }                                                   \
+  return 0;
+
+namespace {
+
+// BinaryOpReduce body after the commutative swap (binary_reduce.cc:295-336)
+void binary_op_reduce_impl(const std::string& reducer, const std::string& op, DGLB200Graph* g,
+                           int lhs_tgt, int rhs_tgt, const DGLB200Tensor* lhs,
+                           const DGLB200Tensor* rhs, DGLB200Tensor* out,
+                           const DGLB200Tensor* lhs_map, const DGLB200Tensor* rhs_map,
+                           const DGLB200Tensor* out_map, cudaStream_t s) {
+  const int opc = parse_op(op);
+  const int red = parse_reducer(reducer);
+  if (need_switch_order(opc, lhs_tgt, rhs_tgt)) {
+    binary_op_reduce_impl(reducer, op, g, rhs_tgt, lhs_tgt, rhs, lhs, out, rhs_map, lhs_map,
+                          out_map, s);
+    return;
+  }
+  if (!has_bcast(lhs, rhs)) {
+    // IsValidBinaryOpShape: identical feature shapes
+    B200_CHECK(lhs->ndim == rhs->ndim,
+               "Cannot compute binary operation between feature shapes " + shape_string(lhs) +
+                   " and " + shape_string(rhs));
+  }
+  KernelCall c;
+  c.g = g;
+  c.mode = kFwd;
+  c.red = red;
+  c.op = opc;
+  c.lhs_tgt = lhs_tgt;
+  c.rhs_tgt = rhs_tgt;
+  c.bc = make_bcast(op, lhs, rhs);
+  c.lhs = data_ptr<const float>(lhs);
+  c.rhs = data_ptr<const float>(rhs);
+  c.out = nullptr;
+  c.gout = nullptr;
+  c.dst = data_ptr<float>(out);
+  c.lhs_rows = lhs->shape[0];
+  c.rhs_rows = rhs->shape[0];
+  c.dst_rows = out->shape[0];
+  c.out_rows = out->shape[0];
+  c.lhs_map = map_ptr(lhs_map);
+  c.rhs_map = map_ptr(rhs_map);
+  c.out_map = map_ptr(out_map);
+  c.mean = false;
+  c.stream = s;
+  const int out_tgt = red == kRNone ? kEdge : kDst;
+  check_rows(g, lhs, lhs_tgt, c.lhs_map != nullptr, "lhs_data");
+  check_rows(g, rhs, rhs_tgt, c.rhs_map != nullptr, "rhs_data");
+  check_rows(g, out, out_tgt, c.out_map != nullptr, "out_data");
+  B200_CHECK(feat_len(out) == c.bc.out_len,
+             "out_data feature size does not match the inferred output shape");
+  dispatch(c);
+}
+
+// Backward{Lhs,Rhs}BinaryOpReduce (binary_reduce.cc:452-500, 551-598): mode after swap
+void backward_binary_impl(int mode, const std::string& reducer, const std::string& op,
+                          DGLB200Graph* g, int lhs_tgt, int rhs_tgt,
+                          const DGLB200Tensor* lhs_map, const DGLB200Tensor* rhs_map,
+                          const DGLB200Tensor* out_map, const DGLB200Tensor* lhs,
+                          const DGLB200Tensor* rhs, const DGLB200Tensor* out,
+                          const DGLB200Tensor* gout, DGLB200Tensor* grad, cudaStream_t s) {
+  const int opc = parse_op(op);
+  const int red = parse_reducer(reducer);
+  if (need_switch_order(opc, lhs_tgt, rhs_tgt)) {
+    backward_binary_impl(mode == kGradLhs ? kGradRhs : kGradLhs, reducer, op, g, rhs_tgt, lhs_tgt,
+                         rhs_map, lhs_map, out_map, rhs, lhs, out, gout, grad, s);
+    return;
+  }
+  KernelCall c;
+  c.g = g;
+  c.mode = mode;
+  c.red = red;
+  c.op = opc;
+  c.lhs_tgt = lhs_tgt;
+  c.rhs_tgt = rhs_tgt;
+  c.bc = make_bcast(op, lhs, rhs);
+  c.lhs = data_ptr<const float>(lhs);
+  c.rhs = data_ptr<const float>(rhs);
+  c.out = data_ptr<const float>(out);
+  c.gout = data_ptr<const float>(gout);
+  c.dst = data_ptr<float>(grad);
+  c.lhs_rows = lhs->shape[0];
+  c.rhs_rows = rhs->shape[0];
+  c.dst_rows = grad->shape[0];
+  c.out_rows = out->shape[0];
+  c.lhs_map = map_ptr(lhs_map);
+  c.rhs_map = map_ptr(rhs_map);
+  c.out_map = map_ptr(out_map);
+  c.mean = false;
+  c.stream = s;
+  const int out_tgt = red == kRNone ? kEdge : kDst;
+  check_rows(g, lhs, lhs_tgt, c.lhs_map != nullptr, "lhs_data");
+  check_rows(g, rhs, rhs_tgt, c.rhs_map != nullptr, "rhs_data");
+  check_rows(g, out, out_tgt, c.out_map != nullptr, "out_data");
+  check_rows(g, gout, out_tgt, c.out_map != nullptr, "grad_out_data");
+  check_rows(g, grad, mode == kGradLhs ? lhs_tgt : rhs_tgt,
+             (mode == kGradLhs ? c.lhs_map : c.rhs_map) != nullptr, "grad data");
+  B200_CHECK(feat_len(gout) == c.bc.out_len && feat_len(out) == c.bc.out_len,
+             "out_data / grad_out_data feature size does not match the inferred output shape");
+  B200_CHECK(feat_len(grad) == c.bc.out_len * c.bc.data_len,
+             "gradient tensor must have the (unreduced) output feature shape");
+  dispatch(c);
+}
+
+void copy_reduce_impl(const std::string& reducer, DGLB200Graph* g, int target,
+                      const DGLB200Tensor* in, DGLB200Tensor* out, const DGLB200Tensor* in_map,
+                      const DGLB200Tensor* out_map, bool mean, cudaStream_t s) {
+  KernelCall c;
+  c.g = g;
+  c.mode = kFwd;
+  c.red = mean ? kSum : parse_reducer(reducer);
+  c.op = kUseLhs;
+  c.lhs_tgt = target;
+  c.rhs_tgt = kNone;
+  c.bc = make_bcast("use_lhs", in, nullptr);
+  c.lhs = data_ptr<const float>(in);
+  c.rhs = nullptr;
+  c.out = nullptr;
+  c.gout = nullptr;
+  c.dst = data_ptr<float>(out);
+  c.lhs_rows = in->shape[0];
+  c.rhs_rows = 0;
+  c.dst_rows = out->shape[0];
+  c.out_rows = out->shape[0];
+  c.lhs_map = map_ptr(in_map);
+  c.rhs_map = nullptr;
+  c.out_map = map_ptr(out_map);
+  c.mean = mean;
+  c.stream = s;
+  const int out_tgt = c.red == kRNone ? kEdge : kDst;
+  check_rows(g, in, target, c.lhs_map != nullptr, "in_data");
+  check_rows(g, out, out_tgt, c.out_map != nullptr, "out_data");
+  B200_CHECK(feat_len(out) == c.bc.out_len, "in_data and out_data feature sizes differ");
+  dispatch(c);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* DGLB200GetLastError(void) { return g_last_error.c_str(); }
+int DGLB200Version(void) { return 1; }
+const char* DGLB200LastKernel(void) { return g_last_kernel; }
+int64_t DGLB200LaunchCount(void) { return g_launches; }
+
+int DGLB200KernelInferBinaryFeatureShape(const char* op, const DGLB200Tensor* lhs,
+                                         const DGLB200Tensor* rhs, int32_t* out_ndim,
+                                         int64_t* out_shape) {
+  API_BEGIN();
+  B200_CHECK(op && lhs && rhs && out_ndim && out_shape, "NULL argument");
+  B200_CHECK(lhs->ndim >= 1 && rhs->ndim >= 1, "operands need a leading row dimension");
+  parse_op(op);
+  BcastHost h = calc_bcast(op, lhs, rhs);
+  B200_CHECK(h.real_out_shape.size() <= 16, "too many feature dimensions");
+  *out_ndim = (int32_t)h.real_out_shape.size();
+  for (size_t i = 0; i < h.real_out_shape.size(); ++i) out_shape[i] = h.real_out_shape[i];
+  API_END();
+}
+
+int DGLB200KernelBinaryOpReduce(const char* reducer, const char* op, DGLB200GraphHandle graph,
+                                int lhs_target, int rhs_target, const DGLB200Tensor* lhs_data,
+                                const DGLB200Tensor* rhs_data, DGLB200Tensor* out_data,
+                                const DGLB200Tensor* lhs_mapping,
+                                const DGLB200Tensor* rhs_mapping,
+                                const DGLB200Tensor* out_mapping, void* stream) {
+  API_BEGIN();
+  B200_CHECK(reducer && op && graph && lhs_data && rhs_data && out_data, "NULL argument");
+  check_target(lhs_target, "lhs");
+  check_target(rhs_target, "rhs");
+  check_ctx(graph, {lhs_data, rhs_data, out_data, lhs_mapping, rhs_mapping, out_mapping},
+            {"lhs_data", "rhs_data", "out_data", "lhs_mapping", "rhs_mapping", "out_mapping"});
+  check_id_arrays({lhs_mapping, rhs_mapping, out_mapping},
+                  {"lhs_mapping", "rhs_mapping", "out_mapping"});
+  check_float(lhs_data, "lhs_data");
+  check_float(rhs_data, "rhs_data");
+  check_float(out_data, "out_data");
+  binary_op_reduce_impl(reducer, op, graph, lhs_target, rhs_target, lhs_data, rhs_data, out_data,
+                        lhs_mapping, rhs_mapping, out_mapping,
+                        static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+static int backward_entry(int mode, const char* reducer, const char* op,
+                          DGLB200GraphHandle graph, int lhs_target, int rhs_target,
+                          const DGLB200Tensor* lhs_mapping, const DGLB200Tensor* rhs_mapping,
+                          const DGLB200Tensor* out_mapping, const DGLB200Tensor* lhs_data,
+                          const DGLB200Tensor* rhs_data, const DGLB200Tensor* out_data,
+                          const DGLB200Tensor* grad_out_data, DGLB200Tensor* grad_data,
+                          void* stream) {
+  API_BEGIN();
+  B200_CHECK(reducer && op && graph && lhs_data && rhs_data && out_data && grad_out_data &&
+                 grad_data,
+             "NULL argument");
+  check_target(lhs_target, "lhs");
+  check_target(rhs_target, "rhs");
+  check_ctx(graph,
+            {lhs_data, rhs_data, out_data, grad_out_data, grad_data, lhs_mapping, rhs_mapping,
+             out_mapping},
+            {"lhs_data", "rhs_data", "out_data", "grad_out_data",
+             mode == kGradLhs ? "grad_lhs_data" : "grad_rhs_data", "lhs_mapping", "rhs_mapping",
+             "out_mapping"});
+  check_id_arrays({lhs_mapping, rhs_mapping, out_mapping},
+                  {"lhs_mapping", "rhs_mapping", "out_mapping"});
+  check_float(lhs_data, "lhs_data");
+  check_float(rhs_data, "rhs_data");
+  check_float(out_data, "out_data");
+  check_float(grad_out_data, "grad_out_data");
+  check_float(grad_data, "grad data");
+  backward_binary_impl(mode, reducer, op, graph, lhs_target, rhs_target, lhs_mapping,
+                       rhs_mapping, out_mapping, lhs_data, rhs_data, out_data, grad_out_data,
+                       grad_data, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200KernelBackwardLhsBinaryOpReduce(
+    const char* reducer, const char* op, DGLB200GraphHandle graph, int lhs_target, int rhs_target,
+    const DGLB200Tensor* lhs_mapping, const DGLB200Tensor* rhs_mapping,
+    const DGLB200Tensor* out_mapping, const DGLB200Tensor* lhs_data,
+    const DGLB200Tensor* rhs_data, const DGLB200Tensor* out_data,
+    const DGLB200Tensor* grad_out_data, DGLB200Tensor* grad_lhs_data, void* stream) {
+  return backward_entry(kGradLhs, reducer, op, graph, lhs_target, rhs_target, lhs_mapping,
+                        rhs_mapping, out_mapping, lhs_data, rhs_data, out_data, grad_out_data,
+                        grad_lhs_data, stream);
+}
+
+int DGLB200KernelBackwardRhsBinaryOpReduce(
+    const char* reducer, const char* op, DGLB200GraphHandle graph, int lhs_target, int rhs_target,
+    const DGLB200Tensor* lhs_mapping, const DGLB200Tensor* rhs_mapping,
+    const DGLB200Tensor* out_mapping, const DGLB200Tensor* lhs_data,
+    const DGLB200Tensor* rhs_data, const DGLB200Tensor* out_data,
+    const DGLB200Tensor* grad_out_data, DGLB200Tensor* grad_rhs_data, void* stream) {
+  return backward_entry(kGradRhs, reducer, op, graph, lhs_target, rhs_target, lhs_mapping,
+                        rhs_mapping, out_mapping, lhs_data, rhs_data, out_data, grad_out_data,
+                        grad_rhs_data, stream);
+}
+
+int DGLB200KernelCopyReduce(const char* reducer, DGLB200GraphHandle graph, int target,
+                            const DGLB200Tensor* in_data, DGLB200Tensor* out_data,
+                            const DGLB200Tensor* in_mapping, const DGLB200Tensor* out_mapping,
+                            void* stream) {
+  API_BEGIN();
+  B200_CHECK(reducer && graph && in_data && out_data, "NULL argument");
+  check_target(target, "target");
+  check_ctx(graph, {in_data, out_data, in_mapping, out_mapping},
+            {"in_data", "out_data", "in_mapping", "out_mapping"});
+  check_id_arrays({in_mapping, out_mapping}, {"in_mapping", "out_mapping"});
+  check_float(in_data, "in_data");
+  check_float(out_data, "out_data");
+  copy_reduce_impl(reducer, graph, target, in_data, out_data, in_mapping, out_mapping, false,
+                   static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200KernelCopyReduceMean(DGLB200GraphHandle graph, int target,
+                                const DGLB200Tensor* in_data, DGLB200Tensor* out_data,
+                                void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && in_data && out_data, "NULL argument");
+  check_target(target, "target");
+  check_ctx(graph, {in_data, out_data}, {"in_data", "out_data"});
+  check_float(in_data, "in_data");
+  check_float(out_data, "out_data");
+  B200_CHECK(out_data->shape[0] == graph->num_dst,
+             "CopyReduceMean: out_data must have one row per destination node");
+  copy_reduce_impl("sum", graph, target, in_data, out_data, nullptr, nullptr, true,
+                   static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200KernelBackwardCopyReduce(const char* reducer, DGLB200GraphHandle graph, int target,
+                                    const DGLB200Tensor* in_data, const DGLB200Tensor* out_data,
+                                    const DGLB200Tensor* grad_out_data,
+                                    DGLB200Tensor* grad_in_data,
+                                    const DGLB200Tensor* in_mapping,
+                                    const DGLB200Tensor* out_mapping, void* stream) {
+  API_BEGIN();
+  B200_CHECK(reducer && graph && in_data && out_data && grad_out_data && grad_in_data,
+             "NULL argument");
+  check_target(target, "target");
+  check_ctx(graph, {in_data, out_data, grad_out_data, grad_in_data, in_mapping, out_mapping},
+            {"in_data", "out_data", "grad_out_data", "grad_in_data", "in_mapping",
+             "out_mapping"});
+  check_id_arrays({in_mapping, out_mapping}, {"in_mapping", "out_mapping"});
+  check_float(in_data, "in_data");
+  check_float(out_data, "out_data");
+  check_float(grad_out_data, "grad_out_data");
+  check_float(grad_in_data, "grad_in_data");
+  KernelCall c;
+  c.g = graph;
+  c.mode = kGradLhs;
+  c.red = parse_reducer(reducer);
+  c.op = kUseLhs;
+  c.lhs_tgt = target;
+  c.rhs_tgt = kNone;
+  c.bc = make_bcast("use_lhs", in_data, nullptr);
+  c.lhs = data_ptr<const float>(in_data);
+  c.rhs = nullptr;
+  c.out = data_ptr<const float>(out_data);
+  c.gout = data_ptr<const float>(grad_out_data);
+  c.dst = data_ptr<float>(grad_in_data);
+  c.lhs_rows = in_data->shape[0];
+  c.rhs_rows = 0;
+  c.dst_rows = grad_in_data->shape[0];
+  c.out_rows = out_data->shape[0];
+  c.lhs_map = map_ptr(in_mapping);
+  c.rhs_map = nullptr;
+  c.out_map = map_ptr(out_mapping);
+  c.mean = false;
+  c.stream = static_cast<cudaStream_t>(stream);
+  const int out_tgt = c.red == kRNone ? kEdge : kDst;
+  check_rows(graph, in_data, target, c.lhs_map != nullptr, "in_data");
+  check_rows(graph, grad_in_data, target, c.lhs_map != nullptr, "grad_in_data");
+  check_rows(graph, out_data, out_tgt, c.out_map != nullptr, "out_data");
+  check_rows(graph, grad_out_data, out_tgt, c.out_map != nullptr, "grad_out_data");
+  B200_CHECK(feat_len(grad_out_data) == c.bc.out_len && feat_len(grad_in_data) == c.bc.out_len &&
+                 feat_len(out_data) == c.bc.out_len,
+             "in/out/grad feature sizes differ");
+  dispatch(c);
+  API_END();
+}
+
+}  // extern "C"

@@ -1,0 +1,209 @@
+// Shared definitions for the sm_100a message-passing kernels.
+//
+// Arithmetic contract (what makes results reproducible against the reference's single-threaded
+// CPU path): every float op is an explicitly rounded intrinsic (__fadd_rn / __fmul_rn / __fdiv_rn)
+// so nvcc never contracts mul+add into an FMA, and every reduction visits a row's edges
+// sequentially in CSR order -- the same order in which minigun's CPU advance
+// (third_party/minigun/minigun/cpu/advance.h:71-117) reaches a given output element when run with
+// one thread. Functor semantics follow src/kernel/binary_reduce_common.h:131-213, 406-498 and
+// src/kernel/cpu/functor.h:18-72.
+#pragma once
+#include <cuda_runtime.h>
+#include "../../include/dgl_b200.h"
+#include <float.h>
+#include <stdint.h>
+
+#include <string>
+
+namespace b200 {
+
+enum Target { kSrc = 0, kDst = 1, kEdge = 2, kNone = 3 };
+enum OpCode { kAdd = 0, kSub = 1, kMul = 2, kDiv = 3, kDot = 4, kUseLhs = 5 };
+enum RedCode { kSum = 0, kMax = 1, kMin = 2, kProd = 3, kRNone = 4 };
+enum Mode { kFwd = 0, kGradLhs = 1, kGradRhs = 2 };
+
+constexpr int kMaxBcastDim = 8;  // BCAST_NDIM_SWITCH tops out at 8 (binary_reduce_impl.h:238-255)
+
+// BcastInfo (src/kernel/binary_reduce.h:21-35) with the row dimension removed. The
+// non-broadcast path is ndim == 1 with all three shapes equal to {x_len}.
+struct Bcast {
+  int ndim;
+  int lhs_shape[kMaxBcastDim], lhs_stride[kMaxBcastDim];
+  int rhs_shape[kMaxBcastDim], rhs_stride[kMaxBcastDim];
+  int out_shape[kMaxBcastDim], out_stride[kMaxBcastDim];
+  int64_t lhs_len, rhs_len, out_len, data_len;
+};
+
+// ---------------------------------------------------------------- functors
+__device__ __forceinline__ float red_identity(int red) {
+  switch (red) {
+    case kMax: return -FLT_MAX;  // std::numeric_limits<float>::lowest()
+    case kMin: return FLT_MAX;
+    case kProd: return 1.f;
+    default: return 0.f;
+  }
+}
+inline float red_identity_host(int red) {
+  switch (red) {
+    case kMax: return -FLT_MAX;
+    case kMin: return FLT_MAX;
+    case kProd: return 1.f;
+    default: return 0.f;
+  }
+}
+
+__device__ __forceinline__ float red_call(int red, float acc, float v) {
+  switch (red) {
+    case kSum: return __fadd_rn(acc, v);
+    case kMax: return (acc < v) ? v : acc;  // std::max(acc, v)
+    case kMin: return (v < acc) ? v : acc;  // std::min(acc, v)
+    case kProd: return __fmul_rn(acc, v);
+    default: return v;
+  }
+}
+
+__device__ __forceinline__ float red_bwd(int red, float val, float accum) {
+  switch (red) {
+    case kMax:
+    case kMin: return (val == accum) ? 1.f : 0.f;
+    case kProd: return __fdiv_rn(accum, val);
+    default: return 1.f;
+  }
+}
+
+// scalar binary op on single elements (everything except dot)
+__device__ __forceinline__ float op_scalar(int op, float l, float r) {
+  switch (op) {
+    case kAdd: return __fadd_rn(l, r);
+    case kSub: return __fsub_rn(l, r);
+    case kMul: return __fmul_rn(l, r);
+    case kDiv: return __fdiv_rn(l, r);
+    default: return l;  // use_lhs
+  }
+}
+
+__device__ __forceinline__ float op_call(int op, const float* __restrict__ l,
+                                         const float* __restrict__ r, int len) {
+  if (op == kDot) {
+    float o = 0.f;
+    for (int i = 0; i < len; ++i) o = __fadd_rn(o, __fmul_rn(__ldg(l + i), __ldg(r + i)));
+    return o;
+  }
+  if (op == kUseLhs) return __ldg(l);
+  return op_scalar(op, __ldg(l), __ldg(r));
+}
+
+__device__ __forceinline__ float op_bwd_lhs(int op, float l, float r) {
+  switch (op) {
+    case kMul:
+    case kDot: return r;
+    case kDiv: return __fdiv_rn(1.f, r);
+    default: return 1.f;  // add, sub, use_lhs
+  }
+}
+
+__device__ __forceinline__ float op_bwd_rhs(int op, float l, float r) {
+  switch (op) {
+    case kAdd: return 1.f;
+    case kSub: return -1.f;
+    case kMul:
+    case kDot: return l;
+    case kUseLhs: return 0.f;
+    default: return __fdiv_rn(-l, __fmul_rn(r, r));  // div
+  }
+}
+
+// ---------------------------------------------------------------- host helpers
+void set_last_error(const std::string& msg);
+void note_kernel(const char* family, int launches);
+
+struct ApiError {
+  std::string msg;
+};
+
+#define B200_CHECK(cond, message)                       \
+  do {                                                  \
+    if (!(cond)) throw ::b200::ApiError{std::string(message)}; \
+  } while (0)
+
+#define B200_CUDA(expr)                                                                   \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess)                                                                \
+      throw ::b200::ApiError{std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " + \
+                             __FILE__ + ":" + std::to_string(__LINE__)};                   \
+  } while (0)
+
+inline int ceil_div(int64_t a, int64_t b) { return static_cast<int>((a + b - 1) / b); }
+
+// Stream-ordered scratch allocation (the reference's WorkspacePool role,
+// src/runtime/workspace_pool.cc): freed on the same stream, never synchronises.
+struct Scratch {
+  void* ptr = nullptr;
+  cudaStream_t stream = nullptr;
+  Scratch() {}
+  Scratch(size_t bytes, cudaStream_t s) { alloc(bytes, s); }
+  void alloc(size_t bytes, cudaStream_t s) {
+    stream = s;
+    if (bytes == 0) bytes = 4;
+    B200_CUDA(cudaMallocAsync(&ptr, bytes, s));
+  }
+  ~Scratch() {
+    if (ptr) cudaFreeAsync(ptr, stream);
+  }
+  Scratch(const Scratch&) = delete;
+  Scratch& operator=(const Scratch&) = delete;
+  template <typename T>
+  T* as() { return static_cast<T*>(ptr); }
+};
+
+// ---------------------------------------------------------------- device graph index
+struct Csr {
+  int32_t* indptr = nullptr;   // [n_rows + 1]
+  int32_t* indices = nullptr;  // [nnz] column (= the other endpoint)
+  int32_t* eids = nullptr;     // [nnz] edge id (csr.data)
+  int32_t* row = nullptr;      // [nnz] row of each position (lazily built COO expansion)
+  int32_t* to_other = nullptr; // [nnz] position of the same edge in the other CSR (lazy)
+  int32_t* heavy_first = nullptr;  // [n_rows] row schedule: heavy rows first (lazy)
+  int64_t n_rows = 0, n_cols = 0;
+  int32_t max_deg = -1;
+};
+
+}  // namespace b200
+
+struct DGLB200Graph {
+  int64_t num_src = 0, num_dst = 0, num_edges = 0;
+  int device = 0;
+  b200::Csr in;   // rows = dst, cols = src
+  b200::Csr out;  // rows = src, cols = dst
+};
+
+namespace b200 {
+
+// graph.cu
+const int32_t* csr_rows(DGLB200Graph* g, bool out_csr, cudaStream_t s);      // row-of-position
+const int32_t* csr_to_other(DGLB200Graph* g, bool out_csr, cudaStream_t s);  // pos -> other pos
+const int32_t* csr_schedule(DGLB200Graph* g, bool out_csr, cudaStream_t s);  // may be NULL
+void exclusive_scan_i32(int32_t* data, int64_t n, cudaStream_t s);
+void fill_f32(float* p, int64_t n, float v, cudaStream_t s);
+
+// generic.cu / spmm.cu / sddmm.cu
+struct KernelCall {
+  DGLB200Graph* g;
+  int mode;  // Mode
+  int red, op;
+  int lhs_tgt, rhs_tgt;
+  const float *lhs, *rhs, *out, *gout;  // out/gout only in backward
+  float* dst;                           // forward: out tensor; backward: grad tensor
+  int64_t lhs_rows, rhs_rows, dst_rows, out_rows;
+  const int32_t *lhs_map, *rhs_map, *out_map;  // user mappings (NULL = none)
+  Bcast bc;
+  bool mean;  // extension: divide the row sum by max(deg, 1)
+  cudaStream_t stream;
+};
+
+void run_generic(const KernelCall& c);
+bool try_spmm(const KernelCall& c);  // returns false if the call is not an SpMM-shaped case
+bool try_sddmm(const KernelCall& c);
+
+}  // namespace b200

@@ -1,0 +1,709 @@
+// Device-side index preparation and the graph handle.
+//
+// Replaces the reference's single-threaded CPU path for the arrays the kernels consume:
+//   aten::COOToCSR      src/array/cpu/spmat_op_impl_coo.cc:230-283  (stable counting sort by row)
+//   aten::CSRTranspose  src/array/cpu/spmat_op_impl.cc:323-369      (stable)
+//   aten::CSRToCOO      src/array/cpu/spmat_op_impl.cc:371-385
+//   AsNumBits / CopyTo  src/graph/immutable_graph.cc:548-590
+// Both conversions are "stable sort of positions by a small integer key", done here with a
+// hand-written LSD radix sort (8 bits per pass, only as many passes as the key range needs).
+// Integer work: results are bit-identical to the reference.
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------- small utilities
+__global__ void fill_f32_kernel(float* __restrict__ p, int64_t n, float v) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  // 128-bit stores on the aligned body
+  if ((reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+    const int64_t n4 = n >> 2;
+    float4 v4 = make_float4(v, v, v, v);
+    for (int64_t k = i; k < n4; k += stride) reinterpret_cast<float4*>(p)[k] = v4;
+    for (int64_t k = (n4 << 2) + i; k < n; k += stride) p[k] = v;
+  } else {
+    for (int64_t k = i; k < n; k += stride) p[k] = v;
+  }
+}
+
+void fill_f32(float* p, int64_t n, float v, cudaStream_t s) {
+  if (n <= 0) return;
+  int blocks = (int)std::min<int64_t>((n / 4 + 255) / 256 + 1, 148 * 16);
+  fill_f32_kernel<<<blocks, 256, 0, s>>>(p, n, v);
+  note_kernel(nullptr, 1);
+}
+
+__global__ void fill_i32_kernel(int32_t* __restrict__ p, int64_t n, int32_t v) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride) p[k] = v;
+}
+static void fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t s) {
+  if (n <= 0) return;
+  int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  fill_i32_kernel<<<blocks, 256, 0, s>>>(p, n, v);
+  note_kernel(nullptr, 1);
+}
+
+__global__ void narrow_kernel(const int64_t* __restrict__ in, int32_t* __restrict__ out,
+                              int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride)
+    out[k] = (int32_t)in[k];
+}
+static void narrow(const int64_t* in, int32_t* out, int64_t n, cudaStream_t s) {
+  if (n <= 0) return;
+  int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  narrow_kernel<<<blocks, 256, 0, s>>>(in, out, n);
+  note_kernel(nullptr, 1);
+}
+
+__global__ void widen_diff_kernel(const int32_t* __restrict__ indptr, int64_t* __restrict__ out,
+                                  int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride)
+    out[k] = (int64_t)(indptr[k + 1] - indptr[k]);
+}
+
+__global__ void gather_i32_kernel(const int32_t* __restrict__ table,
+                                  const int32_t* __restrict__ idx, int32_t* __restrict__ out,
+                                  int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride)
+    out[k] = table[idx[k]];
+}
+static void gather_i32(const int32_t* table, const int32_t* idx, int32_t* out, int64_t n,
+                       cudaStream_t s) {
+  if (n <= 0) return;
+  int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  gather_i32_kernel<<<blocks, 256, 0, s>>>(table, idx, out, n);
+  note_kernel(nullptr, 1);
+}
+
+// out[idx[k]] = k  (inverse permutation)
+__global__ void invert_perm_kernel(const int32_t* __restrict__ idx, int32_t* __restrict__ out,
+                                   int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride)
+    out[idx[k]] = (int32_t)k;
+}
+
+__global__ void count_keys_kernel(const int32_t* __restrict__ keys, int64_t n,
+                                  int32_t* __restrict__ counts) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride)
+    atomicAdd(&counts[keys[k]], 1);
+}
+
+// row[p] = r for p in [indptr[r], indptr[r+1]); one warp per row, lanes stride the row.
+__global__ void expand_rows_kernel(const int32_t* __restrict__ indptr, int64_t n_rows,
+                                   int32_t* __restrict__ row) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < n_rows; r += n_warps) {
+    const int beg = indptr[r], end = indptr[r + 1];
+    for (int p = beg + lane; p < end; p += 32) row[p] = (int32_t)r;
+  }
+}
+static void expand_rows(const int32_t* indptr, int64_t n_rows, int32_t* row, cudaStream_t s) {
+  if (n_rows <= 0) return;
+  int blocks = (int)std::min<int64_t>((n_rows * 32 + 255) / 256, 148 * 32);
+  expand_rows_kernel<<<blocks, 256, 0, s>>>(indptr, n_rows, row);
+  note_kernel(nullptr, 1);
+}
+
+// ---------------------------------------------------------------- exclusive scan (int32)
+// Three-phase: per-block reduce -> scan of block sums (recursive) -> per-block scan + offset.
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ int block_exclusive_scan_256(int v, int* total) {
+  // exclusive scan of one int per thread over 256 threads
+  __shared__ int warp_sums[8];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_sums[wid] = inc;
+  __syncthreads();
+  if (wid == 0) {
+    int w = lane < 8 ? warp_sums[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += t;
+    }
+    if (lane < 8) warp_sums[lane] = w;  // inclusive over warps
+  }
+  __syncthreads();
+  const int warp_off = wid == 0 ? 0 : warp_sums[wid - 1];
+  if (total) *total = warp_sums[7];
+  const int res = warp_off + inc - v;
+  __syncthreads();  // warp_sums reusable by the caller's next invocation
+  return res;
+}
+
+__global__ void scan_reduce_kernel(const int32_t* __restrict__ data, int64_t n,
+                                   int32_t* __restrict__ block_sums) {
+  const int64_t base = (int64_t)blockIdx.x * kScanTile;
+  int sum = 0;
+#pragma unroll
+  for (int i = 0; i < kScanItems; ++i) {
+    const int64_t k = base + i * kScanThreads + threadIdx.x;
+    if (k < n) sum += data[k];
+  }
+  int total;
+  block_exclusive_scan_256(sum, &total);
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+__global__ void scan_apply_kernel(int32_t* __restrict__ data, int64_t n,
+                                  const int32_t* __restrict__ block_offsets) {
+  // thread t owns kScanItems CONSECUTIVE elements so the scan order is the array order
+  const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
+  int v[kScanItems];
+  int sum = 0;
+#pragma unroll
+  for (int i = 0; i < kScanItems; ++i) {
+    v[i] = (base + i < n) ? data[base + i] : 0;
+    sum += v[i];
+  }
+  int run = block_exclusive_scan_256(sum, nullptr) + (block_offsets ? block_offsets[blockIdx.x] : 0);
+#pragma unroll
+  for (int i = 0; i < kScanItems; ++i) {
+    if (base + i < n) data[base + i] = run;
+    run += v[i];
+  }
+}
+
+void exclusive_scan_i32(int32_t* data, int64_t n, cudaStream_t s) {
+  if (n <= 0) return;
+  const int blocks = ceil_div(n, kScanTile);
+  if (blocks == 1) {
+    scan_apply_kernel<<<1, kScanThreads, 0, s>>>(data, n, nullptr);
+    note_kernel(nullptr, 1);
+    return;
+  }
+  Scratch sums((size_t)blocks * sizeof(int32_t), s);
+  scan_reduce_kernel<<<blocks, kScanThreads, 0, s>>>(data, n, sums.as<int32_t>());
+  note_kernel(nullptr, 1);
+  exclusive_scan_i32(sums.as<int32_t>(), blocks, s);
+  scan_apply_kernel<<<blocks, kScanThreads, 0, s>>>(data, n, sums.as<int32_t>());
+  note_kernel(nullptr, 1);
+}
+
+// ---------------------------------------------------------------- stable LSD radix sort
+// Sorts (key, value) pairs by 32-bit non-negative keys, 8 bits per pass; values default to the
+// element index on the first pass. Stability is what makes the result equal to the reference's
+// counting sort: ties keep their input order.
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 16;  // per thread
+constexpr int kSortTile = kSortThreads * kSortItems;  // 4096
+constexpr int kRadix = 256;
+
+__global__ void __launch_bounds__(kSortThreads)
+radix_hist_kernel(const int32_t* __restrict__ keys, int64_t n, int shift, int n_blocks,
+                  int32_t* __restrict__ block_hist /* [kRadix][n_blocks] */) {
+  __shared__ int hist[kRadix];
+  hist[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * kSortTile;
+#pragma unroll
+  for (int i = 0; i < kSortItems; ++i) {
+    const int64_t k = base + i * kSortThreads + threadIdx.x;
+    if (k < n) atomicAdd(&hist[(keys[k] >> shift) & (kRadix - 1)], 1);
+  }
+  __syncthreads();
+  block_hist[(int64_t)threadIdx.x * n_blocks + blockIdx.x] = hist[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+radix_scatter_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict__ vals_in,
+                     int64_t n, int shift, int n_blocks,
+                     const int32_t* __restrict__ block_offs /* scanned [kRadix][n_blocks] */,
+                     int32_t* __restrict__ keys_out, int32_t* __restrict__ vals_out) {
+  __shared__ int warp_cnt[kSortThreads / 32][kRadix];
+  __shared__ int digit_base[kRadix];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < (kSortThreads / 32) * kRadix; i += kSortThreads)
+    (&warp_cnt[0][0])[i] = 0;
+  digit_base[threadIdx.x] = block_offs[(int64_t)threadIdx.x * n_blocks + blockIdx.x];
+  __syncthreads();
+
+  // warp `wid` owns the contiguous slice [wbase, wbase + 32*kSortItems) of this block's tile
+  const int64_t wbase = (int64_t)blockIdx.x * kSortTile + (int64_t)wid * (32 * kSortItems);
+  int key[kSortItems], rank[kSortItems];
+  const unsigned lt_mask = (1u << lane) - 1u;
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r) {
+    const int64_t k = wbase + r * 32 + lane;
+    const bool valid = k < n;
+    key[r] = valid ? keys_in[k] : -1;
+    const unsigned digit = valid ? (unsigned)((key[r] >> shift) & (kRadix - 1)) : 0xffffffffu;
+    const unsigned peers = __match_any_sync(0xffffffffu, digit);
+    const int before = __popc(peers & lt_mask);
+    int old = 0;
+    if (valid) old = warp_cnt[wid][digit];
+    __syncwarp();
+    if (valid && before == 0) warp_cnt[wid][digit] = old + __popc(peers);
+    __syncwarp();
+    rank[r] = old + before;
+  }
+  __syncthreads();
+  {
+    // exclusive scan of each digit's count over the warps (warp order = element order)
+    const int d = threadIdx.x;
+    int run = 0;
+#pragma unroll
+    for (int w = 0; w < kSortThreads / 32; ++w) {
+      const int t = warp_cnt[w][d];
+      warp_cnt[w][d] = run;
+      run += t;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r) {
+    const int64_t k = wbase + r * 32 + lane;
+    if (k < n) {
+      const int digit = (key[r] >> shift) & (kRadix - 1);
+      const int64_t pos = (int64_t)digit_base[digit] + warp_cnt[wid][digit] + rank[r];
+      keys_out[pos] = key[r];
+      vals_out[pos] = vals_in ? vals_in[k] : (int32_t)k;
+    }
+  }
+}
+
+// Sorts n pairs stably by keys in [0, key_range). On return *sorted_keys / *sorted_vals point at
+// whichever of the ping-pong buffers holds the result. vals_in == nullptr means iota.
+// keys_a is the input (may be overwritten if more than one pass is needed).
+static void radix_sort_pairs(int32_t* keys_a, int32_t* keys_b, const int32_t* vals_in,
+                             int32_t* vals_a, int32_t* vals_b, int64_t n, int64_t key_range,
+                             int32_t** sorted_keys, int32_t** sorted_vals, cudaStream_t s) {
+  int bits = 1;
+  while (bits < 31 && ((int64_t)1 << bits) < key_range) ++bits;
+  const int passes = std::max(1, (bits + 7) / 8);
+  const int n_blocks = std::max(1, ceil_div(n, kSortTile));
+  Scratch hist((size_t)kRadix * n_blocks * sizeof(int32_t), s);
+  int32_t* kin = keys_a;
+  int32_t* kout = keys_b;
+  const int32_t* vin = vals_in;
+  int32_t* vout = vals_a;
+  for (int p = 0; p < passes; ++p) {
+    const int shift = p * 8;
+    radix_hist_kernel<<<n_blocks, kSortThreads, 0, s>>>(kin, n, shift, n_blocks,
+                                                        hist.as<int32_t>());
+    note_kernel(nullptr, 1);
+    exclusive_scan_i32(hist.as<int32_t>(), (int64_t)kRadix * n_blocks, s);
+    radix_scatter_kernel<<<n_blocks, kSortThreads, 0, s>>>(kin, vin, n, shift, n_blocks,
+                                                           hist.as<int32_t>(), kout, vout);
+    note_kernel(nullptr, 1);
+    std::swap(kin, kout);
+    vin = vout;
+    vout = (vout == vals_a) ? vals_b : vals_a;
+  }
+  *sorted_keys = kin;
+  *sorted_vals = const_cast<int32_t*>(vin);
+}
+
+// ---------------------------------------------------------------- CSR construction
+// rows/cols: device int32 [nnz]. Produces indptr [n_rows+1], indices [nnz], data [nnz] with
+// data[p] = original position, stable in input order (== aten::COOToCSR unsorted branch).
+// If row_of_pos != nullptr it also receives the sorted row keys (the COO row expansion).
+static void coo_to_csr_device(int64_t n_rows, int64_t nnz, const int32_t* rows,
+                              const int32_t* cols, const int32_t* data_in, int32_t* indptr,
+                              int32_t* indices, int32_t* data, int32_t* row_of_pos,
+                              int32_t* src_pos /* optional: sorted position permutation */,
+                              cudaStream_t s) {
+  fill_i32(indptr, n_rows + 1, 0, s);
+  if (nnz > 0) {
+    int blocks = (int)std::min<int64_t>((nnz + 255) / 256, 148 * 16);
+    count_keys_kernel<<<blocks, 256, 0, s>>>(rows, nnz, indptr);
+    note_kernel(nullptr, 1);
+  }
+  exclusive_scan_i32(indptr, n_rows + 1, s);
+  if (nnz == 0) return;
+  Scratch ka((size_t)nnz * 4, s), kb((size_t)nnz * 4, s), va((size_t)nnz * 4, s),
+      vb((size_t)nnz * 4, s);
+  B200_CUDA(cudaMemcpyAsync(ka.ptr, rows, (size_t)nnz * 4, cudaMemcpyDeviceToDevice, s));
+  int32_t *sk, *sv;
+  radix_sort_pairs(ka.as<int32_t>(), kb.as<int32_t>(), nullptr, va.as<int32_t>(),
+                   vb.as<int32_t>(), nnz, n_rows, &sk, &sv, s);
+  // sv[p] = input position of the p-th sorted element
+  gather_i32(cols, sv, indices, nnz, s);
+  if (data_in) {
+    gather_i32(data_in, sv, data, nnz, s);
+  } else {
+    B200_CUDA(cudaMemcpyAsync(data, sv, (size_t)nnz * 4, cudaMemcpyDeviceToDevice, s));
+  }
+  if (row_of_pos)
+    B200_CUDA(cudaMemcpyAsync(row_of_pos, sk, (size_t)nnz * 4, cudaMemcpyDeviceToDevice, s));
+  if (src_pos)
+    B200_CUDA(cudaMemcpyAsync(src_pos, sv, (size_t)nnz * 4, cudaMemcpyDeviceToDevice, s));
+}
+
+// ---------------------------------------------------------------- lazily built per-CSR arrays
+static void ensure_device(int device) { B200_CUDA(cudaSetDevice(device)); }
+
+const int32_t* csr_rows(DGLB200Graph* g, bool out_csr, cudaStream_t s) {
+  Csr& c = out_csr ? g->out : g->in;
+  if (!c.row) {
+    B200_CUDA(cudaMalloc(&c.row, std::max<int64_t>(g->num_edges, 1) * 4));
+    expand_rows(c.indptr, c.n_rows, c.row, s);
+  }
+  return c.row;
+}
+
+const int32_t* csr_to_other(DGLB200Graph* g, bool out_csr, cudaStream_t s) {
+  Csr& c = out_csr ? g->out : g->in;
+  Csr& o = out_csr ? g->in : g->out;
+  if (!c.to_other) {
+    const int64_t e = g->num_edges;
+    B200_CUDA(cudaMalloc(&c.to_other, std::max<int64_t>(e, 1) * 4));
+    if (e > 0) {
+      // pos_of_eid_in_other[o.eids[q]] = q ; to_other[p] = pos_of_eid_in_other[c.eids[p]]
+      Scratch inv((size_t)e * 4, s);
+      int blocks = (int)std::min<int64_t>((e + 255) / 256, 148 * 16);
+      invert_perm_kernel<<<blocks, 256, 0, s>>>(o.eids, inv.as<int32_t>(), e);
+      note_kernel(nullptr, 1);
+      gather_i32(inv.as<int32_t>(), c.eids, c.to_other, e, s);
+    }
+  }
+  return c.to_other;
+}
+
+// Row schedule for the row-parallel kernels: rows whose degree is far above the mean are moved
+// to the front (largest first) so the longest sequential reductions start first; all other rows
+// keep their natural order (which preserves whatever locality the node numbering has).
+__global__ void max_deg_kernel(const int32_t* __restrict__ indptr, int64_t n_rows,
+                               int32_t* __restrict__ out) {
+  int m = 0;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n_rows; k += stride)
+    m = max(m, indptr[k + 1] - indptr[k]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out, m);
+}
+
+__global__ void schedule_key_kernel(const int32_t* __restrict__ indptr, int64_t n_rows,
+                                    int heavy_threshold, int max_deg,
+                                    int32_t* __restrict__ keys) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n_rows; k += stride) {
+    const int deg = indptr[k + 1] - indptr[k];
+    int key = 255;
+    if (deg >= heavy_threshold) key = 254 - (int)(((int64_t)deg * 254) / max_deg);
+    keys[k] = key;
+  }
+}
+
+const int32_t* csr_schedule(DGLB200Graph* g, bool out_csr, cudaStream_t s) {
+  Csr& c = out_csr ? g->out : g->in;
+  if (c.max_deg < 0) {
+    // one-time, synchronising: decide whether this CSR is skewed enough to need a schedule
+    Scratch m(4, s);
+    B200_CUDA(cudaMemsetAsync(m.ptr, 0, 4, s));
+    if (c.n_rows > 0) {
+      int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 8);
+      max_deg_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, m.as<int32_t>());
+      note_kernel(nullptr, 1);
+    }
+    int32_t h = 0;
+    B200_CUDA(cudaMemcpyAsync(&h, m.ptr, 4, cudaMemcpyDeviceToHost, s));
+    B200_CUDA(cudaStreamSynchronize(s));
+    c.max_deg = h;
+    const int64_t mean = c.n_rows > 0 ? (g->num_edges + c.n_rows - 1) / c.n_rows : 0;
+    const int64_t thr = std::max<int64_t>(8 * std::max<int64_t>(mean, 1), 1024);
+    if (c.max_deg >= thr && c.n_rows > 1) {
+      Scratch ka((size_t)c.n_rows * 4, s), kb((size_t)c.n_rows * 4, s), va((size_t)c.n_rows * 4, s),
+          vb((size_t)c.n_rows * 4, s);
+      int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 8);
+      schedule_key_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, (int)thr, c.max_deg,
+                                                 ka.as<int32_t>());
+      note_kernel(nullptr, 1);
+      int32_t *sk, *sv;
+      radix_sort_pairs(ka.as<int32_t>(), kb.as<int32_t>(), nullptr, va.as<int32_t>(),
+                       vb.as<int32_t>(), c.n_rows, 256, &sk, &sv, s);
+      B200_CUDA(cudaMalloc(&c.heavy_first, (size_t)c.n_rows * 4));
+      B200_CUDA(cudaMemcpyAsync(c.heavy_first, sv, (size_t)c.n_rows * 4,
+                                cudaMemcpyDeviceToDevice, s));
+    }
+  }
+  return c.heavy_first;
+}
+
+static void free_csr(Csr& c) {
+  cudaFree(c.indptr);
+  cudaFree(c.indices);
+  cudaFree(c.eids);
+  cudaFree(c.row);
+  cudaFree(c.to_other);
+  cudaFree(c.heavy_first);
+  c = Csr();
+}
+
+static void alloc_csr(Csr& c, int64_t n_rows, int64_t n_cols, int64_t nnz) {
+  c.n_rows = n_rows;
+  c.n_cols = n_cols;
+  B200_CUDA(cudaMalloc(&c.indptr, (size_t)(n_rows + 1) * 4));
+  B200_CUDA(cudaMalloc(&c.indices, (size_t)std::max<int64_t>(nnz, 1) * 4));
+  B200_CUDA(cudaMalloc(&c.eids, (size_t)std::max<int64_t>(nnz, 1) * 4));
+}
+
+static bool is_device_ptr(const void* p) {
+  cudaPointerAttributes a;
+  cudaError_t e = cudaPointerGetAttributes(&a, p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// copies `n` index values (int32 or int64, host or device) into a device int32 array
+static void upload_idx(const void* src, int bits, int64_t n, int32_t* dst, cudaStream_t s) {
+  if (n <= 0) return;
+  const bool dev = is_device_ptr(src);
+  if (bits == 32) {
+    B200_CUDA(cudaMemcpyAsync(dst, src, (size_t)n * 4,
+                              dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
+  } else {
+    if (dev) {
+      narrow(static_cast<const int64_t*>(src), dst, n, s);
+    } else {
+      Scratch tmp((size_t)n * 8, s);
+      B200_CUDA(cudaMemcpyAsync(tmp.ptr, src, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+      narrow(tmp.as<int64_t>(), dst, n, s);
+      // the host buffer must stay valid until the copy has been consumed
+      B200_CUDA(cudaStreamSynchronize(s));
+    }
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+#define API_BEGIN() try {
+#define API_END()                                     \
+  }                                                   \
+  catch (const ::b200::ApiError& e) {                 \
+    ::b200::set_last_error(e.msg);                    \
+    return -1;                                        \
+  }                                                   \
+  catch (const std::exception& e) {                   \
+    ::b200::set_last_error(e.what());                 \
+    return -1;                                        \
+  }                                                   \
+  return 0;
+
+extern "C" {
+
+int DGLB200GraphCreateFromCOO(int64_t num_src, int64_t num_dst, int64_t num_edges,
+                              const int64_t* src, const int64_t* dst, int device, void* stream,
+                              DGLB200GraphHandle* out) {
+  API_BEGIN();
+  B200_CHECK(out != nullptr, "DGLB200GraphCreateFromCOO: out handle is NULL");
+  B200_CHECK(num_src >= 0 && num_dst >= 0 && num_edges >= 0, "negative graph size");
+  // graph_index.py:941-952 picks 64-bit ids only if N or E >= 2^31; the GPU kernels of the
+  // reference are int32-only (src/kernel/common.h:62-81) and so are these.
+  B200_CHECK(num_src < (1ll << 31) - 1 && num_dst < (1ll << 31) - 1 && num_edges < (1ll << 31) - 1,
+             "graph needs 64-bit ids; the GPU kernels are int32-only (as in the reference)");
+  B200_CHECK(num_edges == 0 || (src && dst), "src/dst arrays are NULL");
+  ensure_device(device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  DGLB200Graph* g = new DGLB200Graph();
+  g->num_src = num_src;
+  g->num_dst = num_dst;
+  g->num_edges = num_edges;
+  g->device = device;
+  try {
+    alloc_csr(g->in, num_dst, num_src, num_edges);
+    alloc_csr(g->out, num_src, num_dst, num_edges);
+    const int64_t e = num_edges;
+    Scratch s32((size_t)std::max<int64_t>(e, 1) * 4, s), d32((size_t)std::max<int64_t>(e, 1) * 4, s);
+    upload_idx(src, 64, e, s32.as<int32_t>(), s);
+    upload_idx(dst, 64, e, d32.as<int32_t>(), s);
+    // in-CSR = COOToCSR keyed by dst (immutable_graph.cc:407-421); keep the row expansion,
+    // the transpose needs it.
+    B200_CUDA(cudaMalloc(&g->in.row, (size_t)std::max<int64_t>(e, 1) * 4));
+    coo_to_csr_device(num_dst, e, d32.as<int32_t>(), s32.as<int32_t>(), nullptr, g->in.indptr,
+                      g->in.indices, g->in.eids, g->in.row, nullptr, s);
+    // out-CSR = in_csr.Transpose() (immutable_graph.cc:424-437): stable sort of in-CSR positions
+    // by src; column = dst row of the position, data = its edge id. The sorted position
+    // permutation is out->in ("to_other" of the out-CSR), kept because it is free here.
+    B200_CUDA(cudaMalloc(&g->out.to_other, (size_t)std::max<int64_t>(e, 1) * 4));
+    coo_to_csr_device(num_src, e, g->in.indices, g->in.row, g->in.eids, g->out.indptr,
+                      g->out.indices, g->out.eids, nullptr, g->out.to_other, s);
+  } catch (...) {
+    free_csr(g->in);
+    free_csr(g->out);
+    delete g;
+    throw;
+  }
+  *out = g;
+  API_END();
+}
+
+int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edges, int idx_bits,
+                              const void* in_indptr, const void* in_indices, const void* in_eids,
+                              const void* out_indptr, const void* out_indices,
+                              const void* out_eids, int device, void* stream,
+                              DGLB200GraphHandle* out) {
+  API_BEGIN();
+  B200_CHECK(out != nullptr, "DGLB200GraphCreateFromCSR: out handle is NULL");
+  B200_CHECK(idx_bits == 32 || idx_bits == 64, "idx_bits must be 32 or 64");
+  B200_CHECK(num_src < (1ll << 31) - 1 && num_dst < (1ll << 31) - 1 && num_edges < (1ll << 31) - 1,
+             "graph needs 64-bit ids; the GPU kernels are int32-only (as in the reference)");
+  ensure_device(device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  DGLB200Graph* g = new DGLB200Graph();
+  g->num_src = num_src;
+  g->num_dst = num_dst;
+  g->num_edges = num_edges;
+  g->device = device;
+  try {
+    alloc_csr(g->in, num_dst, num_src, num_edges);
+    alloc_csr(g->out, num_src, num_dst, num_edges);
+    upload_idx(in_indptr, idx_bits, num_dst + 1, g->in.indptr, s);
+    upload_idx(in_indices, idx_bits, num_edges, g->in.indices, s);
+    upload_idx(in_eids, idx_bits, num_edges, g->in.eids, s);
+    upload_idx(out_indptr, idx_bits, num_src + 1, g->out.indptr, s);
+    upload_idx(out_indices, idx_bits, num_edges, g->out.indices, s);
+    upload_idx(out_eids, idx_bits, num_edges, g->out.eids, s);
+    B200_CUDA(cudaStreamSynchronize(s));  // host buffers may be released by the caller now
+  } catch (...) {
+    free_csr(g->in);
+    free_csr(g->out);
+    delete g;
+    throw;
+  }
+  *out = g;
+  API_END();
+}
+
+int DGLB200GraphFree(DGLB200GraphHandle g) {
+  API_BEGIN();
+  if (g) {
+    cudaSetDevice(g->device);
+    cudaDeviceSynchronize();
+    free_csr(g->in);
+    free_csr(g->out);
+    delete g;
+  }
+  API_END();
+}
+
+int DGLB200GraphInfo(DGLB200GraphHandle g, int64_t* info) {
+  API_BEGIN();
+  B200_CHECK(g && info, "NULL argument");
+  info[0] = g->num_src;
+  info[1] = g->num_dst;
+  info[2] = g->num_edges;
+  info[3] = g->device;
+  API_END();
+}
+
+int DGLB200GraphGetCSR(DGLB200GraphHandle g, int transpose, const int32_t** indptr,
+                       const int32_t** indices, const int32_t** eids) {
+  API_BEGIN();
+  B200_CHECK(g, "NULL graph");
+  const Csr& c = transpose ? g->out : g->in;
+  if (indptr) *indptr = c.indptr;
+  if (indices) *indices = c.indices;
+  if (eids) *eids = c.eids;
+  API_END();
+}
+
+int DGLB200GraphCopyCSR(DGLB200GraphHandle g, int transpose, int32_t* indptr, int32_t* indices,
+                        int32_t* eids, void* stream) {
+  API_BEGIN();
+  B200_CHECK(g, "NULL graph");
+  ensure_device(g->device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const Csr& c = transpose ? g->out : g->in;
+  bool host = false;
+  auto copy = [&](int32_t* dst, const int32_t* src, int64_t n) {
+    if (!dst || n <= 0) return;
+    const bool dev = is_device_ptr(dst);
+    host = host || !dev;
+    B200_CUDA(cudaMemcpyAsync(dst, src, (size_t)n * 4,
+                              dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+  };
+  copy(indptr, c.indptr, c.n_rows + 1);
+  copy(indices, c.indices, g->num_edges);
+  copy(eids, c.eids, g->num_edges);
+  if (host) B200_CUDA(cudaStreamSynchronize(s));
+  API_END();
+}
+
+int DGLB200GraphDegrees(DGLB200GraphHandle g, int which, int64_t* out, void* stream) {
+  API_BEGIN();
+  B200_CHECK(g && out, "NULL argument");
+  ensure_device(g->device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const Csr& c = which ? g->out : g->in;
+  if (c.n_rows > 0) {
+    const bool dev = is_device_ptr(out);
+    Scratch tmp;
+    int64_t* d = out;
+    if (!dev) {
+      tmp.alloc((size_t)c.n_rows * 8, s);
+      d = tmp.as<int64_t>();
+    }
+    int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 16);
+    widen_diff_kernel<<<blocks, 256, 0, s>>>(c.indptr, d, c.n_rows);
+    note_kernel(nullptr, 1);
+    if (!dev)
+      B200_CUDA(cudaMemcpyAsync(out, d, (size_t)c.n_rows * 8, cudaMemcpyDeviceToHost, s));
+    B200_CUDA(cudaStreamSynchronize(s));
+  }
+  API_END();
+}
+
+int DGLB200COOToCSR(int64_t num_rows, int64_t nnz, const int32_t* row, const int32_t* col,
+                    int32_t* indptr, int32_t* indices, int32_t* data, void* stream) {
+  API_BEGIN();
+  B200_CHECK(num_rows >= 0 && nnz >= 0, "negative size");
+  coo_to_csr_device(num_rows, nnz, row, col, nullptr, indptr, indices, data, nullptr, nullptr,
+                    static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200CSRTranspose(int64_t num_rows, int64_t num_cols, int64_t nnz, const int32_t* indptr,
+                        const int32_t* indices, const int32_t* data, int32_t* t_indptr,
+                        int32_t* t_indices, int32_t* t_data, void* stream) {
+  API_BEGIN();
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  Scratch row((size_t)std::max<int64_t>(nnz, 1) * 4, s);
+  expand_rows(indptr, num_rows, row.as<int32_t>(), s);
+  // transpose: key = column, new column = old row, data follows (or position if absent)
+  coo_to_csr_device(num_cols, nnz, indices, row.as<int32_t>(), data, t_indptr, t_indices, t_data,
+                    nullptr, nullptr, s);
+  API_END();
+}
+
+int DGLB200CSRToCOORows(int64_t num_rows, int64_t nnz, const int32_t* indptr, int32_t* row,
+                        void* stream) {
+  API_BEGIN();
+  (void)nnz;
+  expand_rows(indptr, num_rows, row, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200AsInt32(int64_t n, const int64_t* in, int32_t* out, void* stream) {
+  API_BEGIN();
+  narrow(in, out, n, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+}  // extern "C"

@@ -1,0 +1,499 @@
+// SpMM-style gather-reduce over CSR rows (the hot kernel).
+//
+// Replaces, for node-output reductions, minigun's edge-parallel advance + atomics
+// (third_party/minigun/minigun/cuda/advance_all.cuh:38-91 with the UDF
+// src/kernel/cuda/binary_reduce_impl.cuh:22-53) and the cuSPARSE csrmm2 + cuBLAS geam transpose
+// special case for copy_src+sum (src/kernel/cuda/binary_reduce_sum.cu:83-143, 228-276):
+//
+//   out[r, :] = REDUCE_{p in row r}  A[ida(p), :]  (op)  B[idb(p), :]
+//
+// over the in-CSR (forward; rows = destination nodes) or the out-CSR (gradients w.r.t. a
+// source-target operand; rows = source nodes, A = grad_out gathered by destination).
+//
+// Mapping: the feature row is cut into VEC-wide vector columns; a lane owns CH vector columns and
+// keeps their accumulators in registers for the whole row, so each output element is reduced
+// sequentially in CSR order (bit-reproducible, no atomics, no identity pre-fill, each output row
+// written exactly once with 64/128-bit stores). A row is served by LPR lanes (a sub-warp for narrow
+// features, a full warp, or several warps = "slabs" for wide features). The row's neighbour ids
+// are fetched by the lanes cooperatively (one coalesced load per LPR edges) and broadcast with
+// shuffles; feature loads of U consecutive neighbours are issued back to back before they are
+// consumed so U*CH independent 8/16-byte loads are in flight per lane.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace b200 {
+
+enum IdSrc { kFromCol = 0, kFromEid = 1, kFromRow = 2 };
+enum BMode { kBNone = 0, kBFull = 1, kBHead = 2 };
+constexpr int kOpNegA = 100;  // internal: value = -A (gradient of the rhs of "sub")
+
+struct SpmmArgs {
+  const int32_t* indptr;
+  const int32_t* indices;
+  const int32_t* sched;  // optional row schedule
+  int n_rows;
+  int lpr;    // lanes per row (power of two <= 32)
+  int slabs;  // warps per row when lpr == 32
+  int D;      // floats per feature row
+  int nvec;   // D / VEC
+  const float* A;
+  int a_src;
+  const int32_t* a_pos_ids;   // a_src == kFromEid: position-indexed ids
+  const int32_t* a_node_map;  // a_src == kFromCol: optional node map
+  const float* B;
+  int b_src;
+  const int32_t* b_pos_ids;
+  const int32_t* b_node_map;
+  int b_width;     // floats per B row
+  int b_head_div;  // kBHead: B column = A column / b_head_div
+  int b_is_lhs;
+  int op, red, mean;
+  float* out;
+  const int32_t* out_map;
+  int need_col;
+};
+
+template <int VEC>
+struct Vec {
+  float v[VEC];
+};
+
+template <int VEC>
+__device__ __forceinline__ Vec<VEC> ld_vec(const float* __restrict__ p);
+template <>
+__device__ __forceinline__ Vec<1> ld_vec<1>(const float* __restrict__ p) {
+  Vec<1> r;
+  r.v[0] = __ldg(p);
+  return r;
+}
+template <>
+__device__ __forceinline__ Vec<2> ld_vec<2>(const float* __restrict__ p) {
+  const float2 t = __ldg(reinterpret_cast<const float2*>(p));
+  Vec<2> r;
+  r.v[0] = t.x;
+  r.v[1] = t.y;
+  return r;
+}
+template <>
+__device__ __forceinline__ Vec<4> ld_vec<4>(const float* __restrict__ p) {
+  const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+  Vec<4> r;
+  r.v[0] = t.x;
+  r.v[1] = t.y;
+  r.v[2] = t.z;
+  r.v[3] = t.w;
+  return r;
+}
+
+template <int VEC>
+__device__ __forceinline__ void st_vec(float* __restrict__ p, const Vec<VEC>& x);
+template <>
+__device__ __forceinline__ void st_vec<1>(float* __restrict__ p, const Vec<1>& x) {
+  p[0] = x.v[0];
+}
+template <>
+__device__ __forceinline__ void st_vec<2>(float* __restrict__ p, const Vec<2>& x) {
+  *reinterpret_cast<float2*>(p) = make_float2(x.v[0], x.v[1]);
+}
+template <>
+__device__ __forceinline__ void st_vec<4>(float* __restrict__ p, const Vec<4>& x) {
+  *reinterpret_cast<float4*>(p) = make_float4(x.v[0], x.v[1], x.v[2], x.v[3]);
+}
+
+__device__ __forceinline__ float spmm_value(int op, int b_is_lhs, float av, float bv) {
+  if (op == kOpNegA) return __fmul_rn(av, -1.f);
+  return b_is_lhs ? op_scalar(op, bv, av) : op_scalar(op, av, bv);
+}
+
+template <int VEC, int CH, int U, bool SUM, int BMODE>
+__global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lpr = a.lpr;
+  const int sub = lane & (lpr - 1);
+
+  // ---- work item -> (row, slab)
+  int64_t row_idx;
+  int slab = 0;
+  if (lpr == 32) {
+    row_idx = warp / a.slabs;
+    slab = (int)(warp - row_idx * a.slabs);
+  } else {
+    row_idx = warp * (32 / lpr) + lane / lpr;
+  }
+  const bool row_ok = row_idx < a.n_rows;
+  const int r = row_ok ? (a.sched ? __ldg(a.sched + row_idx) : (int)row_idx) : 0;
+  const int beg = row_ok ? __ldg(a.indptr + r) : 0;
+  const int deg = row_ok ? __ldg(a.indptr + r + 1) - beg : 0;
+
+  // ---- the vector columns this lane owns
+  int col[CH];   // float offset inside a feature row
+  bool cok[CH];
+  int bcol[CH];  // kBHead: B column
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    const int vc = slab * (32 * CH) + c * lpr + sub;
+    cok[c] = vc < a.nvec;
+    col[c] = vc * VEC;
+    bcol[c] = (BMODE == kBHead) ? col[c] / a.b_head_div : 0;
+  }
+
+  const float ident = SUM ? 0.f : red_identity(a.red);
+  Vec<VEC> acc[CH];
+#pragma unroll
+  for (int c = 0; c < CH; ++c)
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[c].v[e] = ident;
+
+  int64_t b_row_const = 0;
+  if (BMODE != kBNone && a.b_src == kFromRow)
+    b_row_const = (int64_t)(a.b_node_map ? __ldg(a.b_node_map + r) : r) * a.b_width;
+
+  const int maxdeg = __reduce_max_sync(0xffffffffu, deg);
+  for (int base = 0; base < maxdeg; base += lpr) {
+    // ---- cooperative fetch of up to lpr neighbour ids per row
+    const int my = base + sub;
+    const bool okp = my < deg;
+    int pa = 0, pb = 0;
+    if (okp) {
+      const int p = beg + my;
+      int cidx = 0;
+      if (a.need_col) cidx = __ldg(a.indices + p);
+      if (a.a_src == kFromCol) {
+        pa = a.a_node_map ? __ldg(a.a_node_map + cidx) : cidx;
+      } else {
+        pa = __ldg(a.a_pos_ids + p);
+      }
+      if (BMODE != kBNone) {
+        if (a.b_src == kFromCol) {
+          pb = a.b_node_map ? __ldg(a.b_node_map + cidx) : cidx;
+        } else if (a.b_src == kFromEid) {
+          pb = __ldg(a.b_pos_ids + p);
+        }
+      }
+    }
+    const int cnt = min(lpr, maxdeg - base);  // warp-uniform
+    for (int i = 0; i < cnt; i += U) {
+      Vec<VEC> va[U][CH];
+      Vec<VEC> vb[U][CH];
+      float sb[U][CH];
+      bool on[U];
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        const int srcl = (i + k) & (lpr - 1);
+        const int ia = __shfl_sync(0xffffffffu, pa, srcl, lpr);
+        int ib = 0;
+        if (BMODE != kBNone) ib = __shfl_sync(0xffffffffu, pb, srcl, lpr);
+        on[k] = (i + k < lpr) && (base + i + k < deg);
+        const float* ap = a.A + (int64_t)ia * a.D;
+        const float* bp = nullptr;
+        if (BMODE != kBNone)
+          bp = a.B + ((a.b_src == kFromRow) ? b_row_const : (int64_t)ib * a.b_width);
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+          if (on[k] && cok[c]) {
+            va[k][c] = ld_vec<VEC>(ap + col[c]);
+            if (BMODE == kBFull) vb[k][c] = ld_vec<VEC>(bp + col[c]);
+            if (BMODE == kBHead) sb[k][c] = __ldg(bp + bcol[c]);
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        if (on[k]) {
+#pragma unroll
+          for (int c = 0; c < CH; ++c) {
+            if (cok[c]) {
+#pragma unroll
+              for (int e = 0; e < VEC; ++e) {
+                float val = va[k][c].v[e];
+                if (BMODE == kBFull) val = spmm_value(a.op, a.b_is_lhs, val, vb[k][c].v[e]);
+                if (BMODE == kBHead) val = spmm_value(a.op, a.b_is_lhs, val, sb[k][c]);
+                if (BMODE == kBNone && a.op == kOpNegA) val = __fmul_rn(val, -1.f);
+                acc[c].v[e] = SUM ? __fadd_rn(acc[c].v[e], val) : red_call(a.red, acc[c].v[e], val);
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  if (row_ok) {
+    const int64_t orow = a.out_map ? __ldg(a.out_map + r) : r;
+    float* op = a.out + orow * a.D;
+    const float dn = (float)(deg > 1 ? deg : 1);
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      if (cok[c]) {
+        if (a.mean) {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fdiv_rn(acc[c].v[e], dn);
+        }
+        st_vec<VEC>(op + col[c], acc[c]);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------- host side
+template <int VEC, int CH, int U>
+static void launch_shape(const SpmmArgs& a, int bmode, bool sum, int blocks, cudaStream_t s) {
+#define B200_SPMM_LAUNCH(SUMV, BM) \
+  spmm_kernel<VEC, CH, U, SUMV, BM><<<blocks, 256, 0, s>>>(a)
+  if (sum) {
+    if (bmode == kBNone) B200_SPMM_LAUNCH(true, kBNone);
+    else if (bmode == kBFull) B200_SPMM_LAUNCH(true, kBFull);
+    else B200_SPMM_LAUNCH(true, kBHead);
+  } else {
+    if (bmode == kBNone) B200_SPMM_LAUNCH(false, kBNone);
+    else if (bmode == kBFull) B200_SPMM_LAUNCH(false, kBFull);
+    else B200_SPMM_LAUNCH(false, kBHead);
+  }
+#undef B200_SPMM_LAUNCH
+}
+
+template <int VEC>
+static void launch_vec(const SpmmArgs& a, int ch, int bmode, bool sum, int blocks,
+                       cudaStream_t s) {
+  switch (ch) {
+    case 1: launch_shape<VEC, 1, 8>(a, bmode, sum, blocks, s); break;
+    case 2: launch_shape<VEC, 2, 8>(a, bmode, sum, blocks, s); break;
+    case 3: launch_shape<VEC, 3, 4>(a, bmode, sum, blocks, s); break;
+    case 4: launch_shape<VEC, 4, 4>(a, bmode, sum, blocks, s); break;
+    case 6: launch_shape<VEC, 6, 2>(a, bmode, sum, blocks, s); break;
+    default: launch_shape<VEC, 8, 2>(a, bmode, sum, blocks, s); break;
+  }
+}
+
+static int round_ch(int ch) {
+  if (ch <= 4) return ch;
+  if (ch <= 6) return 6;
+  return 8;
+}
+
+__global__ void compose_ids_kernel(const int32_t* __restrict__ map,
+                                   const int32_t* __restrict__ to_other,
+                                   int32_t* __restrict__ out, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride)
+    out[k] = map[to_other[k]];
+}
+
+// Describes how the narrow operand lines up against the D-wide one. Returns kBNone on "cannot".
+static int classify_b(const Bcast& bc, bool b_is_lhs, int* b_width, int* head_div) {
+  const int* bs = b_is_lhs ? bc.lhs_shape : bc.rhs_shape;
+  const int* as = b_is_lhs ? bc.rhs_shape : bc.lhs_shape;
+  const int64_t blen = b_is_lhs ? bc.lhs_len : bc.rhs_len;
+  const int64_t alen = b_is_lhs ? bc.rhs_len : bc.lhs_len;
+  if (alen != bc.out_len) return -1;
+  if (blen == bc.out_len) {
+    // same length: element-wise only if no dimension is broadcast
+    for (int d = 0; d < bc.ndim; ++d)
+      if (bs[d] != bc.out_shape[d] || as[d] != bc.out_shape[d]) return -1;
+    *b_width = (int)blen;
+    *head_div = 1;
+    return kBFull;
+  }
+  if (bc.ndim == 1 && bs[0] == 1) {  // [.,D] x [.,1]
+    *b_width = 1;
+    *head_div = (int)bc.out_len;
+    return kBHead;
+  }
+  if (bc.ndim == 2 && bs[1] == 1 && bs[0] == bc.out_shape[0] && as[0] == bc.out_shape[0] &&
+      as[1] == bc.out_shape[1]) {  // [.,H,F] x [.,H,1]
+    *b_width = bs[0];
+    *head_div = bc.out_shape[1];
+    return kBHead;
+  }
+  return -1;
+}
+
+bool try_spmm(const KernelCall& c) {
+  DGLB200Graph* g = c.g;
+  cudaStream_t s = c.stream;
+  if (c.op == kDot || c.bc.data_len != 1) return false;
+  const int64_t D = c.bc.out_len;
+  if (D <= 0 || D > (1 << 20)) return false;
+  const int64_t E = g->num_edges;
+
+  SpmmArgs a;
+  a.B = nullptr;
+  a.b_src = kFromCol;
+  a.b_pos_ids = nullptr;
+  a.b_node_map = nullptr;
+  a.b_width = 0;
+  a.b_head_div = 1;
+  a.b_is_lhs = 0;
+  a.a_pos_ids = nullptr;
+  a.a_node_map = nullptr;
+  a.mean = c.mean ? 1 : 0;
+  a.red = c.red;
+  a.op = c.op;
+  int bmode = kBNone;
+  bool use_out_csr;
+  // (tensor, target, user map) of the two gathered operands in "row/col of the walked CSR" terms
+  const float *A = nullptr, *B = nullptr;
+  int a_tgt = kNone, b_tgt = kNone;
+  const int32_t *a_map = nullptr, *b_map = nullptr, *o_map = nullptr;
+  float fill_v = 0.f;
+
+  if (c.mode == kFwd) {
+    if (c.red == kRNone) return false;
+    use_out_csr = false;
+    fill_v = red_identity_host(c.red);
+    o_map = c.out_map;
+    if (c.op == kUseLhs) {
+      A = c.lhs; a_tgt = c.lhs_tgt; a_map = c.lhs_map;
+    } else {
+      // pick the D-wide, gatherable operand as A
+      int bw, hd;
+      const bool lhs_can_be_a = c.bc.lhs_len == D && c.lhs_tgt != kDst;
+      const bool rhs_can_be_a = c.bc.rhs_len == D && c.rhs_tgt != kDst;
+      int m = -1;
+      if (lhs_can_be_a && (m = classify_b(c.bc, /*b_is_lhs=*/false, &bw, &hd)) > 0) {
+        A = c.lhs; a_tgt = c.lhs_tgt; a_map = c.lhs_map;
+        B = c.rhs; b_tgt = c.rhs_tgt; b_map = c.rhs_map;
+        a.b_is_lhs = 0;
+      } else if (rhs_can_be_a && (m = classify_b(c.bc, /*b_is_lhs=*/true, &bw, &hd)) > 0) {
+        A = c.rhs; a_tgt = c.rhs_tgt; a_map = c.rhs_map;
+        B = c.lhs; b_tgt = c.lhs_tgt; b_map = c.lhs_map;
+        a.b_is_lhs = 1;
+      } else {
+        return false;
+      }
+      bmode = m;
+      a.b_width = bw;
+      a.b_head_div = hd;
+    }
+  } else {
+    // gradient of a SOURCE-target operand under a sum reduction: a transposed SpMM of grad_out
+    if (c.red != kSum) return false;
+    const int t_tgt = c.mode == kGradLhs ? c.lhs_tgt : c.rhs_tgt;
+    if (t_tgt != kSrc) return false;
+    use_out_csr = true;
+    o_map = c.mode == kGradLhs ? c.lhs_map : c.rhs_map;
+    A = c.gout; a_tgt = kDst; a_map = c.out_map;  // gathered by the destination of each out-edge
+    if (c.op == kUseLhs || c.op == kAdd || (c.op == kSub && c.mode == kGradLhs)) {
+      a.op = kUseLhs;
+    } else if (c.op == kSub) {
+      a.op = kOpNegA;
+    } else if (c.op == kMul) {
+      int bw, hd;
+      // the OTHER operand multiplies grad_out; it must line up against the out feature row
+      const bool other_is_lhs = (c.mode == kGradRhs);
+      Bcast sw = c.bc;
+      // classify with "A" = a full-width pseudo operand: pretend the differentiated operand has
+      // the out shape (grad is unreduced), keep the other operand's real shape.
+      if (other_is_lhs) {
+        for (int d = 0; d < sw.ndim; ++d) sw.rhs_shape[d] = sw.out_shape[d];
+        sw.rhs_len = sw.out_len;
+      } else {
+        for (int d = 0; d < sw.ndim; ++d) sw.lhs_shape[d] = sw.out_shape[d];
+        sw.lhs_len = sw.out_len;
+      }
+      const int m = classify_b(sw, other_is_lhs, &bw, &hd);
+      if (m <= 0) return false;
+      bmode = m;
+      a.b_width = bw;
+      a.b_head_div = hd;
+      B = other_is_lhs ? c.lhs : c.rhs;
+      b_tgt = other_is_lhs ? c.lhs_tgt : c.rhs_tgt;
+      b_map = other_is_lhs ? c.lhs_map : c.rhs_map;
+      a.op = kMul;
+    } else {
+      return false;
+    }
+  }
+
+  const Csr& csr = use_out_csr ? g->out : g->in;
+  const int row_tgt = use_out_csr ? kSrc : kDst;
+  const int col_tgt = use_out_csr ? kDst : kSrc;
+  const bool maps_index_out_csr = (c.mode == kFwd);
+  if (a_tgt == row_tgt) return false;  // A must be gathered per edge
+  if (csr.n_rows >= (1ll << 31) || E >= (1ll << 31)) return false;
+
+  // ---- vector width from divisibility and pointer alignment
+  auto aligned = [](const void* p, int bytes) {
+    return (reinterpret_cast<uintptr_t>(p) % bytes) == 0;
+  };
+  int vec = 4;
+  while (vec > 1) {
+    bool ok = (D % vec == 0) && aligned(A, vec * 4) && aligned(c.dst, vec * 4);
+    if (bmode == kBFull) ok = ok && aligned(B, vec * 4);
+    if (bmode == kBHead) ok = ok && (a.b_head_div % vec == 0);
+    if (ok) break;
+    vec >>= 1;
+  }
+  const int nvec = (int)(D / vec);
+  int lpr = 1;
+  while (lpr < 32 && lpr < nvec) lpr <<= 1;
+  int slabs = 1, ch = 1;
+  if (lpr == 32) {
+    slabs = (nvec + 32 * 8 - 1) / (32 * 8);
+    ch = round_ch((nvec + 32 * slabs - 1) / (32 * slabs));
+    slabs = (nvec + 32 * ch - 1) / (32 * ch);
+  }
+
+  // ---- id sources
+  Scratch tmp_a, tmp_b;
+  auto edge_ids = [&](const int32_t* map, Scratch& tmp) -> const int32_t* {
+    if (!map) return csr.eids;
+    if (maps_index_out_csr == use_out_csr || E == 0) return map;
+    const int32_t* to_other = csr_to_other(g, use_out_csr, s);
+    tmp.alloc((size_t)E * 4, s);
+    int blocks = (int)std::min<int64_t>((E + 255) / 256, 148 * 16);
+    compose_ids_kernel<<<blocks, 256, 0, s>>>(map, to_other, tmp.as<int32_t>(), E);
+    note_kernel(nullptr, 1);
+    return tmp.as<int32_t>();
+  };
+  a.A = A;
+  if (a_tgt == kEdge) {
+    a.a_src = kFromEid;
+    a.a_pos_ids = edge_ids(a_map, tmp_a);
+  } else {  // col_tgt
+    a.a_src = kFromCol;
+    a.a_node_map = a_map;
+  }
+  a.B = B;
+  if (bmode != kBNone) {
+    if (b_tgt == kEdge) {
+      a.b_src = kFromEid;
+      a.b_pos_ids = edge_ids(b_map, tmp_b);
+    } else if (b_tgt == col_tgt) {
+      a.b_src = kFromCol;
+      a.b_node_map = b_map;
+    } else {
+      a.b_src = kFromRow;
+      a.b_node_map = b_map;
+    }
+  }
+  a.need_col = (a.a_src == kFromCol) || (bmode != kBNone && a.b_src == kFromCol);
+
+  a.indptr = csr.indptr;
+  a.indices = csr.indices;
+  a.n_rows = (int)csr.n_rows;
+  a.lpr = lpr;
+  a.slabs = slabs;
+  a.D = (int)D;
+  a.nvec = nvec;
+  a.out = c.dst;
+  a.out_map = o_map;
+  a.sched = csr_schedule(g, use_out_csr, s);
+
+  if (o_map != nullptr || c.dst_rows != csr.n_rows) fill_f32(c.dst, c.dst_rows * D, fill_v, s);
+  if (csr.n_rows == 0) return true;
+
+  const int64_t n_warps =
+      (lpr == 32) ? csr.n_rows * slabs : (csr.n_rows + (32 / lpr) - 1) / (32 / lpr);
+  const int blocks = (int)((n_warps + 7) / 8);
+  const bool sum = (c.red == kSum);
+  if (vec == 4) launch_vec<4>(a, ch, bmode, sum, blocks, s);
+  else if (vec == 2) launch_vec<2>(a, ch, bmode, sum, blocks, s);
+  else launch_vec<1>(a, ch, bmode, sum, blocks, s);
+  note_kernel("spmm", 1);
+  return true;
+}
+
+}  // namespace b200

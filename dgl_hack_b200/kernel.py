@@ -1,0 +1,106 @@
+"""Kernel wrappers with the names, argument order and meaning of python/dgl/kernel.py.
+
+Each function binds one C-ABI entry point of include/dgl_b200.h, which replaces the PackedFunc of
+the same name (`kernel._CAPI_DGLKernel*`, src/kernel/binary_reduce.cc). `G` is a
+dgl_hack_b200.graph_index.GraphIndex; tensors are ndarray.NDArray views (or torch tensors);
+optional `*_rows` mappings are None / NDArray / torch int32 tensors. Outputs are caller-allocated
+and written in place, as in the reference.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import LIB, check_call
+from .ndarray import NDArray, null, zerocopy_to_dgl_ndarray
+
+
+def _nd(x):
+    return x if isinstance(x, NDArray) else zerocopy_to_dgl_ndarray(x)
+
+
+def _map(x):
+    """None -> nd.null() (python/dgl/kernel.py:138-148)."""
+    return null() if x is None else _nd(x)
+
+
+def _stream(G):
+    return ctypes.c_void_p(torch.cuda.current_stream(G.device).cuda_stream)
+
+
+def infer_binary_feature_shape(op, lhs, rhs):
+    """kernel.py:8-26 -> kernel._CAPI_DGLKernelInferBinaryFeatureShape."""
+    lhs, rhs = _nd(lhs), _nd(rhs)
+    ndim = ctypes.c_int32()
+    shape = (ctypes.c_int64 * 16)()
+    check_call(LIB.DGLB200KernelInferBinaryFeatureShape(op.encode(), lhs.ptr, rhs.ptr,
+                                                        ctypes.byref(ndim), shape))
+    return tuple(int(shape[i]) for i in range(ndim.value))
+
+
+def binary_op_reduce(reducer, op, G, A_target, B_target, A, B, out,
+                     A_rows=None, B_rows=None, out_rows=None):
+    """kernel.py:29-148 -> kernel._CAPI_DGLKernelBinaryOpReduce."""
+    A, B, out = _nd(A), _nd(B), _nd(out)
+    ar, br, orr = _map(A_rows), _map(B_rows), _map(out_rows)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelBinaryOpReduce(
+            reducer.encode(), op.encode(), G.handle, int(A_target), int(B_target),
+            A.ptr, B.ptr, out.ptr, ar.ptr, br.ptr, orr.ptr, _stream(G)))
+
+
+def backward_lhs_binary_op_reduce(reducer, op, G, A_target, B_target, A, B, out, grad_out,
+                                  grad_A, A_rows=None, B_rows=None, out_rows=None):
+    """kernel.py:172-235 -> kernel._CAPI_DGLKernelBackwardLhsBinaryOpReduce."""
+    A, B, out, grad_out, grad_A = _nd(A), _nd(B), _nd(out), _nd(grad_out), _nd(grad_A)
+    ar, br, orr = _map(A_rows), _map(B_rows), _map(out_rows)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelBackwardLhsBinaryOpReduce(
+            reducer.encode(), op.encode(), G.handle, int(A_target), int(B_target),
+            ar.ptr, br.ptr, orr.ptr, A.ptr, B.ptr, out.ptr, grad_out.ptr, grad_A.ptr,
+            _stream(G)))
+
+
+def backward_rhs_binary_op_reduce(reducer, op, G, A_target, B_target, A, B, out, grad_out,
+                                  grad_B, A_rows=None, B_rows=None, out_rows=None):
+    """kernel.py:237-300 -> kernel._CAPI_DGLKernelBackwardRhsBinaryOpReduce."""
+    A, B, out, grad_out, grad_B = _nd(A), _nd(B), _nd(out), _nd(grad_out), _nd(grad_B)
+    ar, br, orr = _map(A_rows), _map(B_rows), _map(out_rows)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelBackwardRhsBinaryOpReduce(
+            reducer.encode(), op.encode(), G.handle, int(A_target), int(B_target),
+            ar.ptr, br.ptr, orr.ptr, A.ptr, B.ptr, out.ptr, grad_out.ptr, grad_B.ptr,
+            _stream(G)))
+
+
+def copy_reduce(reducer, G, target, X, out, X_rows=None, out_rows=None):
+    """kernel.py:302-394 -> kernel._CAPI_DGLKernelCopyReduce."""
+    X, out = _nd(X), _nd(out)
+    xr, orr = _map(X_rows), _map(out_rows)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelCopyReduce(reducer.encode(), G.handle, int(target), X.ptr,
+                                               out.ptr, xr.ptr, orr.ptr, _stream(G)))
+
+
+def backward_copy_reduce(reducer, G, target, X, out, grad_out, grad_X, X_rows=None,
+                         out_rows=None):
+    """kernel.py:396-435 -> kernel._CAPI_DGLKernelBackwardCopyReduce."""
+    X, out, grad_out, grad_X = _nd(X), _nd(out), _nd(grad_out), _nd(grad_X)
+    xr, orr = _map(X_rows), _map(out_rows)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelBackwardCopyReduce(
+            reducer.encode(), G.handle, int(target), X.ptr, out.ptr, grad_out.ptr, grad_X.ptr,
+            xr.ptr, orr.ptr, _stream(G)))
+
+
+def copy_reduce_mean(G, target, X, out):
+    """Extension (no reference PackedFunc): copy + mean in one pass, see
+    DGLB200KernelCopyReduceMean in include/dgl_b200.h."""
+    X, out = _nd(X), _nd(out)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelCopyReduceMean(G.handle, int(target), X.ptr, out.ptr,
+                                                   _stream(G)))
+
+
+last_kernel = _lib.last_kernel
+launch_count = _lib.launch_count

@@ -1,0 +1,207 @@
+/*
+ * dgl_b200.h -- C ABI of the B200-native (sm_100a) replacement for DGL 0.4's builtin
+ * message-passing kernels (reference: ydwu4/dgl-hack, src/kernel BinaryOpReduce / CopyReduce and
+ * their backward kernels, plus the CSR/COO index preparation they consume).
+ *
+ * Every entry point is `extern "C"`, takes plain pointers and sizes, returns 0 on success and
+ * -1 on failure with the message available from DGLB200GetLastError() (thread-local), i.e. the
+ * reference's API_BEGIN/API_END + DGLGetLastError convention (src/runtime/runtime_base.h:13-31,
+ * src/runtime/c_runtime_api.cc:138-146). Nothing here calls exit() or throws across the ABI.
+ *
+ * Tensors cross as `DGLB200Tensor`, which is layout-identical to the `DLTensor` the reference's
+ * PackedFuncs receive (third_party/dlpack/include/dlpack/dlpack.h, DLPACK_VERSION 020): a
+ * DLTensor* obtained from the reference's NDArray / torch DLPack capsule can be passed as is.
+ * Optional id-mapping tensors follow the reference's convention: NULL or a 1-D array with
+ * shape[0]==0 means "not given" (aten::IsNullArray, include/dgl/array.h:102-104).
+ *
+ * All kernels are enqueued on `stream` (a cudaStream_t passed as void*; NULL = legacy default
+ * stream, the reference's CUDAThreadEntry default, src/runtime/cuda/cuda_common.h:54). No entry
+ * point synchronises the host unless its comment says so.
+ *
+ * There is no CPU path: every compute entry point fails with an error if its tensors are not on
+ * a CUDA device.
+ */
+#ifndef DGL_B200_H_
+#define DGL_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- DLTensor-compatible tensor view (dlpack.h: DLContext, DLDataType, DLTensor) ---- */
+typedef struct {
+  int32_t device_type; /* 1 = kDLCPU, 2 = kDLGPU, 3 = kDLCPUPinned */
+  int32_t device_id;
+} DGLB200Context;
+
+typedef struct {
+  uint8_t code; /* 0 = kDLInt, 1 = kDLUInt, 2 = kDLFloat */
+  uint8_t bits;
+  uint16_t lanes;
+} DGLB200DataType;
+
+typedef struct {
+  void* data;
+  DGLB200Context ctx;
+  int32_t ndim;
+  DGLB200DataType dtype;
+  int64_t* shape;
+  int64_t* strides; /* NULL = compact row-major (the only layout accepted, as in the reference) */
+  uint64_t byte_offset;
+} DGLB200Tensor;
+
+/* Target codes: src/kernel/binary_reduce_common.h:39-44 == python/dgl/function/base.py:7-21 */
+enum { DGLB200_SRC = 0, DGLB200_DST = 1, DGLB200_EDGE = 2, DGLB200_NONE = 3 };
+
+/* Opaque device-resident graph index: in-CSR + out-CSR (int32 indptr / indices / edge ids) of a
+ * (num_src x num_dst) graph, i.e. what CSRWrapper::GetInCSRMatrix / GetOutCSRMatrix hand to the
+ * reference kernels (src/kernel/csr_interface.h:23-29, include/dgl/array.h:299-318). */
+typedef struct DGLB200Graph* DGLB200GraphHandle;
+
+/* ---- errors / library info ---- */
+/* Replaces DGLGetLastError (include/dgl/runtime/c_runtime_api.h:166). */
+const char* DGLB200GetLastError(void);
+/* Returns the library ABI version (bumped on any signature change). */
+int DGLB200Version(void);
+
+/* ---- index preparation (replaces the single-threaded CPU path
+ *      GraphIndex.get_immutable_gidx(ctx) -> ImmutableGraph::AsNumBits / CopyTo
+ *      (python/dgl/graph_index.py:671-686, src/graph/immutable_graph.cc:548-590), i.e.
+ *      aten::COOToCSR (src/array/cpu/spmat_op_impl_coo.cc:230-283) + aten::CSRTranspose
+ *      (src/array/cpu/spmat_op_impl.cc:323-369) + narrowing to int32 + H2D copy) ---- */
+
+/* Builds both CSRs ON THE DEVICE from a COO edge list (edge id = position in the list).
+ * src/dst: int64 arrays of length num_edges, host or device memory (detected).
+ * Results are bit-identical to the reference: in-CSR = stable counting sort by dst,
+ * out-CSR = stable transpose of the in-CSR. `device` is the CUDA ordinal. */
+int DGLB200GraphCreateFromCOO(int64_t num_src, int64_t num_dst, int64_t num_edges,
+                              const int64_t* src, const int64_t* dst, int device, void* stream,
+                              DGLB200GraphHandle* out);
+
+/* Wraps CSR arrays that already exist (e.g. the outputs of the reference's
+ * graph_index._CAPI_DGLGraphGetAdj(g, transpose, "csr"), src/graph/graph_apis.cc:285-292):
+ * arrays may be int32 or int64 (`idx_bits`), host or device; they are copied to `device` as
+ * int32. Replaces ImmutableGraph::CopyTo / UnitGraph::CopyTo (immutable_graph.cc:548-559,
+ * unit_graph.cc:1146-1161). */
+int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edges, int idx_bits,
+                              const void* in_indptr, const void* in_indices, const void* in_eids,
+                              const void* out_indptr, const void* out_indices,
+                              const void* out_eids, int device, void* stream,
+                              DGLB200GraphHandle* out);
+
+int DGLB200GraphFree(DGLB200GraphHandle g);
+
+/* num_src, num_dst, num_edges, device -> info[4]. */
+int DGLB200GraphInfo(DGLB200GraphHandle g, int64_t* info);
+
+/* Device pointers (int32) to one CSR: transpose=0 -> in-CSR (rows = dst), 1 -> out-CSR
+ * (rows = src); same meaning as _CAPI_DGLGraphGetAdj(g, transpose, "csr"). */
+int DGLB200GraphGetCSR(DGLB200GraphHandle g, int transpose, const int32_t** indptr,
+                       const int32_t** indices, const int32_t** eids);
+
+/* Copies one CSR (same `transpose` meaning) into caller buffers (host or device memory):
+ * indptr [rows+1], indices [E], eids [E], int32. Synchronises `stream` when a buffer is on the
+ * host. Any of the three may be NULL. */
+int DGLB200GraphCopyCSR(DGLB200GraphHandle g, int transpose, int32_t* indptr, int32_t* indices,
+                        int32_t* eids, void* stream);
+
+/* Copies in-degrees (which=0) or out-degrees (which=1) as int64 into `out` (host or device),
+ * = indptr[v+1]-indptr[v] (src/graph/immutable_graph.cc:177). Synchronises `stream`. */
+int DGLB200GraphDegrees(DGLB200GraphHandle g, int which, int64_t* out, void* stream);
+
+/* Standalone index ops on device int32/int64 arrays, bit-exact with the reference's CPU
+ * functions (test surface of tests/cpp/test_spmat.cc). All pointers are DEVICE pointers.
+ * COOToCSR: aten::COOToCSR (spmat_op_impl_coo.cc:230-283); data[] = COO position. */
+int DGLB200COOToCSR(int64_t num_rows, int64_t nnz, const int32_t* row, const int32_t* col,
+                    int32_t* indptr, int32_t* indices, int32_t* data, void* stream);
+/* CSRTranspose: aten::CSRTranspose (spmat_op_impl.cc:323-369); data may be NULL (= position). */
+int DGLB200CSRTranspose(int64_t num_rows, int64_t num_cols, int64_t nnz, const int32_t* indptr,
+                        const int32_t* indices, const int32_t* data, int32_t* t_indptr,
+                        int32_t* t_indices, int32_t* t_data, void* stream);
+/* CSRToCOO row expansion: aten::CSRToCOO (spmat_op_impl.cc:371-385). */
+int DGLB200CSRToCOORows(int64_t num_rows, int64_t nnz, const int32_t* indptr, int32_t* row,
+                        void* stream);
+/* AsNumBits 64 -> 32 (src/array/array.cc AsNumBits; ImmutableGraph::AsNumBits
+ * immutable_graph.cc:574-590). */
+int DGLB200AsInt32(int64_t n, const int64_t* in, int32_t* out, void* stream);
+
+/* ---- kernels: one entry point per reference PackedFunc, same positional meaning ---- */
+
+/* kernel._CAPI_DGLKernelInferBinaryFeatureShape(op, lhs, rhs) (src/kernel/binary_reduce.cc:274-293).
+ * Pure host function (no GPU needed). Writes the broadcast output feature shape (for "dot" it
+ * includes the reduced last dim, exactly as the reference) into out_shape[0..*out_ndim). */
+int DGLB200KernelInferBinaryFeatureShape(const char* op, const DGLB200Tensor* lhs,
+                                         const DGLB200Tensor* rhs, int32_t* out_ndim,
+                                         int64_t* out_shape /* capacity >= 16 */);
+
+/* kernel._CAPI_DGLKernelBinaryOpReduce(reducer, op, graph, lhs_tgt, rhs_tgt, lhs, rhs, out,
+ *   lhs_map, rhs_map, out_map)  (src/kernel/binary_reduce.cc:295-378).
+ * reducer in {"sum","max","min","prod","none"} ("mean" is rejected like the reference,
+ * binary_reduce_impl.h:95-98); op in {"add","sub","mul","div","dot"}. `out` is caller-allocated
+ * and fully overwritten (rows without in-edges receive the reducer identity: 0, -FLT_MAX,
+ * FLT_MAX, 1 -- binary_reduce_common.h:447-470). */
+int DGLB200KernelBinaryOpReduce(const char* reducer, const char* op, DGLB200GraphHandle graph,
+                                int lhs_target, int rhs_target, const DGLB200Tensor* lhs_data,
+                                const DGLB200Tensor* rhs_data, DGLB200Tensor* out_data,
+                                const DGLB200Tensor* lhs_mapping,
+                                const DGLB200Tensor* rhs_mapping,
+                                const DGLB200Tensor* out_mapping, void* stream);
+
+/* kernel._CAPI_DGLKernelBackwardLhsBinaryOpReduce(reducer, op, graph, lhs_tgt, rhs_tgt, lhs_map,
+ *   rhs_map, out_map, lhs, rhs, out, grad_out, grad_lhs)  (binary_reduce.cc:452-527).
+ * grad_lhs has the UNREDUCED out feature shape (rows = lhs rows), as in the reference. */
+int DGLB200KernelBackwardLhsBinaryOpReduce(
+    const char* reducer, const char* op, DGLB200GraphHandle graph, int lhs_target, int rhs_target,
+    const DGLB200Tensor* lhs_mapping, const DGLB200Tensor* rhs_mapping,
+    const DGLB200Tensor* out_mapping, const DGLB200Tensor* lhs_data,
+    const DGLB200Tensor* rhs_data, const DGLB200Tensor* out_data,
+    const DGLB200Tensor* grad_out_data, DGLB200Tensor* grad_lhs_data, void* stream);
+
+/* kernel._CAPI_DGLKernelBackwardRhsBinaryOpReduce(...)  (binary_reduce.cc:551-626). */
+int DGLB200KernelBackwardRhsBinaryOpReduce(
+    const char* reducer, const char* op, DGLB200GraphHandle graph, int lhs_target, int rhs_target,
+    const DGLB200Tensor* lhs_mapping, const DGLB200Tensor* rhs_mapping,
+    const DGLB200Tensor* out_mapping, const DGLB200Tensor* lhs_data,
+    const DGLB200Tensor* rhs_data, const DGLB200Tensor* out_data,
+    const DGLB200Tensor* grad_out_data, DGLB200Tensor* grad_rhs_data, void* stream);
+
+/* kernel._CAPI_DGLKernelCopyReduce(reducer, graph, target, in, out, in_map, out_map)
+ * (binary_reduce.cc:628-665). */
+int DGLB200KernelCopyReduce(const char* reducer, DGLB200GraphHandle graph, int target,
+                            const DGLB200Tensor* in_data, DGLB200Tensor* out_data,
+                            const DGLB200Tensor* in_mapping, const DGLB200Tensor* out_mapping,
+                            void* stream);
+
+/* kernel._CAPI_DGLKernelBackwardCopyReduce(reducer, graph, target, in, out, grad_out, grad_in,
+ *   in_map, out_map)  (binary_reduce.cc:667-716). */
+int DGLB200KernelBackwardCopyReduce(const char* reducer, DGLB200GraphHandle graph, int target,
+                                    const DGLB200Tensor* in_data, const DGLB200Tensor* out_data,
+                                    const DGLB200Tensor* grad_out_data,
+                                    DGLB200Tensor* grad_in_data,
+                                    const DGLB200Tensor* in_mapping,
+                                    const DGLB200Tensor* out_mapping, void* stream);
+
+/* ---- extensions (no reference PackedFunc; they replace multi-call sequences the reference's
+ *      torch backend performs around the kernels) ---- */
+
+/* copy_{src,edge} + mean in ONE pass: out[v] = (sum_e in[sel]) / max(deg(v), 1). Replaces the
+ * sum + second copy_reduce over a ones-vector + clamp + divide of
+ * python/dgl/backend/pytorch/tensor.py:529-540 (same arithmetic: fp32 sum in in-CSR order, then
+ * one IEEE division by the exact degree). No id mappings. */
+int DGLB200KernelCopyReduceMean(DGLB200GraphHandle graph, int target,
+                                const DGLB200Tensor* in_data, DGLB200Tensor* out_data,
+                                void* stream);
+
+/* Dispatch introspection for tests / bench: name of the kernel family the LAST compute call on
+ * this thread used ("spmm", "generic_row", "generic_edge", ...), and how many kernel launches
+ * the library has issued on this thread since load. */
+const char* DGLB200LastKernel(void);
+int64_t DGLB200LaunchCount(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGL_B200_H_ */
