@@ -176,14 +176,25 @@ struct DGLB200Graph {
   int device = 0;
   b200::Csr in;   // rows = dst, cols = src
   b200::Csr out;  // rows = src, cols = dst
+  // The in-CSR with every row re-ordered by (src, edge id) = Transpose(out-CSR). This is the
+  // order in which the reference's forward pass (out-CSR walk, one thread) reaches the
+  // contributions of a destination row, so reducing over it sequentially reproduces the
+  // reference's floating-point sums bit for bit; ascending sources also gather with better
+  // locality. indptr / row / heavy_first alias `in` (same degrees); to_other -> out-CSR position.
+  b200::Csr in_s;
 };
 
 namespace b200 {
 
 // graph.cu
-const int32_t* csr_rows(DGLB200Graph* g, bool out_csr, cudaStream_t s);      // row-of-position
-const int32_t* csr_to_other(DGLB200Graph* g, bool out_csr, cudaStream_t s);  // pos -> other pos
-const int32_t* csr_schedule(DGLB200Graph* g, bool out_csr, cudaStream_t s);  // may be NULL
+enum Walk { kWalkIn = 0, kWalkOut = 1, kWalkInSorted = 2 };
+inline const Csr& walk_csr(const DGLB200Graph* g, int walk) {
+  return walk == kWalkOut ? g->out : (walk == kWalkInSorted ? g->in_s : g->in);
+}
+const int32_t* csr_rows(DGLB200Graph* g, int walk, cudaStream_t s);      // row-of-position
+// position in the "other" CSR: in -> out, out -> in, in_sorted -> out
+const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s);
+const int32_t* csr_schedule(DGLB200Graph* g, int walk, cudaStream_t s);  // may be NULL
 void exclusive_scan_i32(int32_t* data, int64_t n, cudaStream_t s);
 void fill_f32(float* p, int64_t n, float v, cudaStream_t s);
 

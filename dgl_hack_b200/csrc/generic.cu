@@ -189,14 +189,19 @@ void run_generic(const KernelCall& c) {
   // Which CSR is walked. Forward maps given for EDGE targets are indexed by out-CSR position,
   // backward maps by in-CSR position (python/dgl/runtime/spmv.py:146-215; the reference walks
   // the out-CSR forward and the in-CSR backward).
-  bool use_out_csr;
+  int walk;
   if (dst_tgt == kEdge) {
-    use_out_csr = (c.mode == kFwd);  // walk the CSR the maps are indexed by: no re-indexing
+    walk = (c.mode == kFwd) ? kWalkOut : kWalkIn;  // the CSR the maps are indexed by
+  } else if (dst_tgt == kSrc) {
+    walk = kWalkOut;
   } else {
-    use_out_csr = (dst_tgt == kSrc);
+    // forward reduce: reference accumulation order (see DGLB200Graph::in_s); gradients of a
+    // dst-target operand: the reference walks the in-CSR itself
+    walk = (c.mode == kFwd) ? kWalkInSorted : kWalkIn;
   }
+  const bool use_out_csr = (walk == kWalkOut);
   const bool maps_index_out_csr = (c.mode == kFwd);
-  const Csr& csr = use_out_csr ? g->out : g->in;
+  const Csr& csr = walk_csr(g, walk);
 
   GArgs a;
   a.indptr = csr.indptr;
@@ -230,7 +235,7 @@ void run_generic(const KernelCall& c) {
   for (int i = 0; i < 3; ++i) {
     ids[i] = maps[i];
     if (maps[i] && tgts[i] == kEdge && maps_index_out_csr != use_out_csr && E > 0) {
-      const int32_t* to_other = csr_to_other(g, use_out_csr, s);
+      const int32_t* to_other = csr_to_other(g, walk, s);
       tmp[i].alloc((size_t)E * 4, s);
       int blocks = (int)std::min<int64_t>((E + 255) / 256, 148 * 16);
       compose_map_kernel<<<blocks, 256, 0, s>>>(maps[i], to_other, tmp[i].as<int32_t>(), E);
@@ -252,7 +257,7 @@ void run_generic(const KernelCall& c) {
   if (n_elem == 0) return;
   if (dst_tgt == kEdge) {
     if (E == 0) return;
-    a.row = csr_rows(g, use_out_csr, s);
+    a.row = csr_rows(g, walk, s);
     const int lanes = pow2_at_most(n_elem, 32);
     const int pos_per_block = 256 / lanes;
     const int blocks = (int)std::min<int64_t>((E + pos_per_block - 1) / pos_per_block, 148 * 64);

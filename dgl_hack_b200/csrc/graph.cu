@@ -353,8 +353,8 @@ static void coo_to_csr_device(int64_t n_rows, int64_t nnz, const int32_t* rows,
 // ---------------------------------------------------------------- lazily built per-CSR arrays
 static void ensure_device(int device) { B200_CUDA(cudaSetDevice(device)); }
 
-const int32_t* csr_rows(DGLB200Graph* g, bool out_csr, cudaStream_t s) {
-  Csr& c = out_csr ? g->out : g->in;
+const int32_t* csr_rows(DGLB200Graph* g, int walk, cudaStream_t s) {
+  Csr& c = (walk == kWalkOut) ? g->out : g->in;  // in_sorted shares the in-CSR's indptr
   if (!c.row) {
     B200_CUDA(cudaMalloc(&c.row, std::max<int64_t>(g->num_edges, 1) * 4));
     expand_rows(c.indptr, c.n_rows, c.row, s);
@@ -362,7 +362,9 @@ const int32_t* csr_rows(DGLB200Graph* g, bool out_csr, cudaStream_t s) {
   return c.row;
 }
 
-const int32_t* csr_to_other(DGLB200Graph* g, bool out_csr, cudaStream_t s) {
+const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s) {
+  if (walk == kWalkInSorted) return g->in_s.to_other;  // built with the index
+  const bool out_csr = (walk == kWalkOut);
   Csr& c = out_csr ? g->out : g->in;
   Csr& o = out_csr ? g->in : g->out;
   if (!c.to_other) {
@@ -406,8 +408,8 @@ __global__ void schedule_key_kernel(const int32_t* __restrict__ indptr, int64_t 
   }
 }
 
-const int32_t* csr_schedule(DGLB200Graph* g, bool out_csr, cudaStream_t s) {
-  Csr& c = out_csr ? g->out : g->in;
+const int32_t* csr_schedule(DGLB200Graph* g, int walk, cudaStream_t s) {
+  Csr& c = (walk == kWalkOut) ? g->out : g->in;  // depends on degrees only
   if (c.max_deg < 0) {
     // one-time, synchronising: decide whether this CSR is skewed enough to need a schedule
     Scratch m(4, s);
@@ -457,6 +459,23 @@ static void alloc_csr(Csr& c, int64_t n_rows, int64_t n_cols, int64_t nnz) {
   B200_CUDA(cudaMalloc(&c.indptr, (size_t)(n_rows + 1) * 4));
   B200_CUDA(cudaMalloc(&c.indices, (size_t)std::max<int64_t>(nnz, 1) * 4));
   B200_CUDA(cudaMalloc(&c.eids, (size_t)std::max<int64_t>(nnz, 1) * 4));
+}
+
+// in_s = Transpose(out-CSR): stable sort of the out-CSR positions by destination.
+static void build_in_sorted(DGLB200Graph* g, cudaStream_t s) {
+  const int64_t e = g->num_edges;
+  Csr& c = g->in_s;
+  c.n_rows = g->num_dst;
+  c.n_cols = g->num_src;
+  c.indptr = g->in.indptr;  // alias (never freed through in_s)
+  B200_CUDA(cudaMalloc(&c.indices, (size_t)std::max<int64_t>(e, 1) * 4));
+  B200_CUDA(cudaMalloc(&c.eids, (size_t)std::max<int64_t>(e, 1) * 4));
+  B200_CUDA(cudaMalloc(&c.to_other, (size_t)std::max<int64_t>(e, 1) * 4));
+  if (e == 0) return;
+  const int32_t* out_row = csr_rows(g, kWalkOut, s);
+  Scratch ip((size_t)(g->num_dst + 1) * 4, s);
+  coo_to_csr_device(g->num_dst, e, g->out.indices, out_row, g->out.eids, ip.as<int32_t>(),
+                    c.indices, c.eids, nullptr, c.to_other, s);
 }
 
 static bool is_device_ptr(const void* p) {
@@ -544,7 +563,10 @@ int DGLB200GraphCreateFromCOO(int64_t num_src, int64_t num_dst, int64_t num_edge
     B200_CUDA(cudaMalloc(&g->out.to_other, (size_t)std::max<int64_t>(e, 1) * 4));
     coo_to_csr_device(num_src, e, g->in.indices, g->in.row, g->in.eids, g->out.indptr,
                       g->out.indices, g->out.eids, nullptr, g->out.to_other, s);
+    build_in_sorted(g, s);
   } catch (...) {
+    g->in_s.indptr = nullptr;
+    free_csr(g->in_s);
     free_csr(g->in);
     free_csr(g->out);
     delete g;
@@ -580,8 +602,11 @@ int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edge
     upload_idx(out_indptr, idx_bits, num_src + 1, g->out.indptr, s);
     upload_idx(out_indices, idx_bits, num_edges, g->out.indices, s);
     upload_idx(out_eids, idx_bits, num_edges, g->out.eids, s);
+    build_in_sorted(g, s);
     B200_CUDA(cudaStreamSynchronize(s));  // host buffers may be released by the caller now
   } catch (...) {
+    g->in_s.indptr = nullptr;
+    free_csr(g->in_s);
     free_csr(g->in);
     free_csr(g->out);
     delete g;
@@ -596,6 +621,8 @@ int DGLB200GraphFree(DGLB200GraphHandle g) {
   if (g) {
     cudaSetDevice(g->device);
     cudaDeviceSynchronize();
+    g->in_s.indptr = nullptr;
+    free_csr(g->in_s);
     free_csr(g->in);
     free_csr(g->out);
     delete g;

@@ -1,0 +1,251 @@
+// SpMM kernel template + launchers, included by spmm_v{1,2,4}.cu (one translation unit per
+// vector width so the instantiations compile in parallel). See spmm.cu for the design notes.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+enum IdSrc { kFromCol = 0, kFromEid = 1, kFromRow = 2 };
+enum BMode { kBNone = 0, kBFull = 1, kBHead = 2 };
+constexpr int kOpNegA = 100;  // internal: value = -A (gradient of the rhs of "sub")
+
+struct SpmmArgs {
+  const int32_t* indptr;
+  const int32_t* indices;
+  const int32_t* sched;  // optional row schedule
+  int n_rows;
+  int lpr;    // lanes per row (power of two <= 32)
+  int slabs;  // warps per row when lpr == 32
+  int D;      // floats per feature row
+  int nvec;   // D / VEC
+  const float* A;
+  int a_src;
+  const int32_t* a_pos_ids;   // a_src == kFromEid: position-indexed ids
+  const int32_t* a_node_map;  // a_src == kFromCol: optional node map
+  const float* B;
+  int b_src;
+  const int32_t* b_pos_ids;
+  const int32_t* b_node_map;
+  int b_width;     // floats per B row
+  int b_head_div;  // kBHead: B column = A column / b_head_div
+  int b_is_lhs;
+  int op, red, mean;
+  float* out;
+  const int32_t* out_map;
+  int need_col;
+};
+
+template <int VEC>
+struct Vec {
+  float v[VEC];
+};
+
+template <int VEC>
+__device__ __forceinline__ Vec<VEC> ld_vec(const float* __restrict__ p);
+template <>
+__device__ __forceinline__ Vec<1> ld_vec<1>(const float* __restrict__ p) {
+  Vec<1> r;
+  r.v[0] = __ldg(p);
+  return r;
+}
+template <>
+__device__ __forceinline__ Vec<2> ld_vec<2>(const float* __restrict__ p) {
+  const float2 t = __ldg(reinterpret_cast<const float2*>(p));
+  Vec<2> r;
+  r.v[0] = t.x;
+  r.v[1] = t.y;
+  return r;
+}
+template <>
+__device__ __forceinline__ Vec<4> ld_vec<4>(const float* __restrict__ p) {
+  const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+  Vec<4> r;
+  r.v[0] = t.x;
+  r.v[1] = t.y;
+  r.v[2] = t.z;
+  r.v[3] = t.w;
+  return r;
+}
+
+template <int VEC>
+__device__ __forceinline__ void st_vec(float* __restrict__ p, const Vec<VEC>& x);
+template <>
+__device__ __forceinline__ void st_vec<1>(float* __restrict__ p, const Vec<1>& x) {
+  p[0] = x.v[0];
+}
+template <>
+__device__ __forceinline__ void st_vec<2>(float* __restrict__ p, const Vec<2>& x) {
+  *reinterpret_cast<float2*>(p) = make_float2(x.v[0], x.v[1]);
+}
+template <>
+__device__ __forceinline__ void st_vec<4>(float* __restrict__ p, const Vec<4>& x) {
+  *reinterpret_cast<float4*>(p) = make_float4(x.v[0], x.v[1], x.v[2], x.v[3]);
+}
+
+__device__ __forceinline__ float spmm_value(int op, int b_is_lhs, float av, float bv) {
+  if (op == kOpNegA) return __fmul_rn(av, -1.f);
+  return b_is_lhs ? op_scalar(op, bv, av) : op_scalar(op, av, bv);
+}
+
+template <int VEC, int CH, int U, bool SUM, int BMODE>
+__global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lpr = a.lpr;
+  const int sub = lane & (lpr - 1);
+
+  // ---- work item -> (row, slab)
+  int64_t row_idx;
+  int slab = 0;
+  if (lpr == 32) {
+    row_idx = warp / a.slabs;
+    slab = (int)(warp - row_idx * a.slabs);
+  } else {
+    row_idx = warp * (32 / lpr) + lane / lpr;
+  }
+  const bool row_ok = row_idx < a.n_rows;
+  const int r = row_ok ? (a.sched ? __ldg(a.sched + row_idx) : (int)row_idx) : 0;
+  const int beg = row_ok ? __ldg(a.indptr + r) : 0;
+  const int deg = row_ok ? __ldg(a.indptr + r + 1) - beg : 0;
+
+  // ---- the vector columns this lane owns
+  int col[CH];   // float offset inside a feature row
+  bool cok[CH];
+  int bcol[CH];  // kBHead: B column
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    const int vc = slab * (32 * CH) + c * lpr + sub;
+    cok[c] = vc < a.nvec;
+    col[c] = vc * VEC;
+    bcol[c] = (BMODE == kBHead) ? col[c] / a.b_head_div : 0;
+  }
+
+  const float ident = SUM ? 0.f : red_identity(a.red);
+  Vec<VEC> acc[CH];
+#pragma unroll
+  for (int c = 0; c < CH; ++c)
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[c].v[e] = ident;
+
+  int64_t b_row_const = 0;
+  if (BMODE != kBNone && a.b_src == kFromRow)
+    b_row_const = (int64_t)(a.b_node_map ? __ldg(a.b_node_map + r) : r) * a.b_width;
+
+  const int maxdeg = __reduce_max_sync(0xffffffffu, deg);
+  for (int base = 0; base < maxdeg; base += lpr) {
+    // ---- cooperative fetch of up to lpr neighbour ids per row
+    const int my = base + sub;
+    const bool okp = my < deg;
+    int pa = 0, pb = 0;
+    if (okp) {
+      const int p = beg + my;
+      int cidx = 0;
+      if (a.need_col) cidx = __ldg(a.indices + p);
+      if (a.a_src == kFromCol) {
+        pa = a.a_node_map ? __ldg(a.a_node_map + cidx) : cidx;
+      } else {
+        pa = __ldg(a.a_pos_ids + p);
+      }
+      if (BMODE != kBNone) {
+        if (a.b_src == kFromCol) {
+          pb = a.b_node_map ? __ldg(a.b_node_map + cidx) : cidx;
+        } else if (a.b_src == kFromEid) {
+          pb = __ldg(a.b_pos_ids + p);
+        }
+      }
+    }
+    const int cnt = min(lpr, maxdeg - base);  // warp-uniform
+    for (int i = 0; i < cnt; i += U) {
+      Vec<VEC> va[U][CH];
+      Vec<VEC> vb[U][CH];
+      float sb[U][CH];
+      bool on[U];
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        const int srcl = (i + k) & (lpr - 1);
+        const int ia = __shfl_sync(0xffffffffu, pa, srcl, lpr);
+        int ib = 0;
+        if (BMODE != kBNone) ib = __shfl_sync(0xffffffffu, pb, srcl, lpr);
+        on[k] = (i + k < lpr) && (base + i + k < deg);
+        const float* ap = a.A + (int64_t)ia * a.D;
+        const float* bp = nullptr;
+        if (BMODE != kBNone)
+          bp = a.B + ((a.b_src == kFromRow) ? b_row_const : (int64_t)ib * a.b_width);
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+          if (on[k] && cok[c]) {
+            va[k][c] = ld_vec<VEC>(ap + col[c]);
+            if (BMODE == kBFull) vb[k][c] = ld_vec<VEC>(bp + col[c]);
+            if (BMODE == kBHead) sb[k][c] = __ldg(bp + bcol[c]);
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        if (on[k]) {
+#pragma unroll
+          for (int c = 0; c < CH; ++c) {
+            if (cok[c]) {
+#pragma unroll
+              for (int e = 0; e < VEC; ++e) {
+                float val = va[k][c].v[e];
+                if (BMODE == kBFull) val = spmm_value(a.op, a.b_is_lhs, val, vb[k][c].v[e]);
+                if (BMODE == kBHead) val = spmm_value(a.op, a.b_is_lhs, val, sb[k][c]);
+                if (BMODE == kBNone && a.op == kOpNegA) val = __fmul_rn(val, -1.f);
+                acc[c].v[e] = SUM ? __fadd_rn(acc[c].v[e], val) : red_call(a.red, acc[c].v[e], val);
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  if (row_ok) {
+    const int64_t orow = a.out_map ? __ldg(a.out_map + r) : r;
+    float* op = a.out + orow * a.D;
+    const float dn = (float)(deg > 1 ? deg : 1);
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      if (cok[c]) {
+        if (a.mean) {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fdiv_rn(acc[c].v[e], dn);
+        }
+        st_vec<VEC>(op + col[c], acc[c]);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------- host side
+template <int VEC, int CH, int U>
+static void launch_shape(const SpmmArgs& a, int bmode, bool sum, int blocks, cudaStream_t s) {
+#define B200_SPMM_LAUNCH(SUMV, BM) \
+  spmm_kernel<VEC, CH, U, SUMV, BM><<<blocks, 256, 0, s>>>(a)
+  if (sum) {
+    if (bmode == kBNone) B200_SPMM_LAUNCH(true, kBNone);
+    else if (bmode == kBFull) B200_SPMM_LAUNCH(true, kBFull);
+    else B200_SPMM_LAUNCH(true, kBHead);
+  } else {
+    if (bmode == kBNone) B200_SPMM_LAUNCH(false, kBNone);
+    else if (bmode == kBFull) B200_SPMM_LAUNCH(false, kBFull);
+    else B200_SPMM_LAUNCH(false, kBHead);
+  }
+#undef B200_SPMM_LAUNCH
+}
+
+template <int VEC>
+void launch_vec(const SpmmArgs& a, int ch, int bmode, bool sum, int blocks,
+                       cudaStream_t s) {
+  switch (ch) {
+    case 1: launch_shape<VEC, 1, 8>(a, bmode, sum, blocks, s); break;
+    case 2: launch_shape<VEC, 2, 8>(a, bmode, sum, blocks, s); break;
+    case 3: launch_shape<VEC, 3, 4>(a, bmode, sum, blocks, s); break;
+    case 4: launch_shape<VEC, 4, 4>(a, bmode, sum, blocks, s); break;
+    case 6: launch_shape<VEC, 6, 2>(a, bmode, sum, blocks, s); break;
+    default: launch_shape<VEC, 8, 2>(a, bmode, sum, blocks, s); break;
+  }
+}
+
+}  // namespace b200

@@ -1,0 +1,4 @@
+#include "spmm_kernels.cuh"
+namespace b200 {
+template void launch_vec<4>(const SpmmArgs&, int, int, bool, int, cudaStream_t);
+}
