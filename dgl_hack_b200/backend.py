@@ -27,7 +27,7 @@ def _degrees_for_mean(graph, target, n_in, in_map, out_map, out_rows, like):
     against an output of `like.dim()` dims. With mappings this is the reference's second
     copy_reduce over a ones-vector (tensor.py:313-327, 529-540)."""
     if in_map is None and out_map is None and out_rows == graph.num_dst:
-        degs = graph.in_degrees().to(like.dtype)
+        return graph.mean_divisor(like.dtype).reshape((out_rows,) + (1,) * (like.dim() - 1))
     else:
         ones = like.new_ones((n_in,))
         degs = like.new_empty((out_rows,))

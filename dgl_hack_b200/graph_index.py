@@ -116,6 +116,20 @@ class GraphIndex(object):
         return tuple(t.cpu().numpy() for t in self._csr_view(True))
 
     def _degrees(self, which):
+        cache = self.__dict__.setdefault("_deg_cache", {})
+        if which not in cache:
+            cache[which] = self._degrees_uncached(which)
+        return cache[which]
+
+    def mean_divisor(self, dtype):
+        """clamp(in_degree, min=1) as a float vector, cached (used by the 'mean' reducer)."""
+        cache = self.__dict__.setdefault("_deg_cache", {})
+        key = ("mean", dtype)
+        if key not in cache:
+            cache[key] = self.in_degrees().to(dtype).clamp(min=1)
+        return cache[key]
+
+    def _degrees_uncached(self, which):
         n = self.num_src if which else self.num_dst
         out = torch.empty((n,), dtype=torch.int64, device=self.device)
         with torch.cuda.device(self.device):
