@@ -3,6 +3,7 @@
 // CalcBcastInfo), :176-219 (CheckCtx / CheckIdArray / NeedSwitchOrder) and the entry functions
 // :295-336, :452-500, :551-598, :628-647, :667-695. Declarations: include/dgl_b200.h.
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <sstream>
 #include <vector>
@@ -13,13 +14,14 @@
 namespace b200 {
 
 static thread_local std::string g_last_error;
-static thread_local const char* g_last_kernel = "";
-static thread_local int64_t g_launches = 0;
+// process-wide (autograd runs backward on its own thread): last kernel family + launch counter
+static std::atomic<const char*> g_last_kernel{""};
+static std::atomic<int64_t> g_launches{0};
 
 void set_last_error(const std::string& msg) { g_last_error = msg; }
 void note_kernel(const char* family, int launches) {
-  if (family) g_last_kernel = family;
-  g_launches += launches;
+  if (family) g_last_kernel.store(family);
+  g_launches.fetch_add(launches);
 }
 
 // ---------------------------------------------------------------- tensor helpers
@@ -433,8 +435,8 @@ extern "C" {
 
 const char* DGLB200GetLastError(void) { return g_last_error.c_str(); }
 int DGLB200Version(void) { return 1; }
-const char* DGLB200LastKernel(void) { return g_last_kernel; }
-int64_t DGLB200LaunchCount(void) { return g_launches; }
+const char* DGLB200LastKernel(void) { return g_last_kernel.load(); }
+int64_t DGLB200LaunchCount(void) { return g_launches.load(); }
 
 int DGLB200KernelInferBinaryFeatureShape(const char* op, const DGLB200Tensor* lhs,
                                          const DGLB200Tensor* rhs, int32_t* out_ndim,

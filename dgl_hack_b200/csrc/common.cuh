@@ -164,9 +164,22 @@ struct Csr {
   int32_t* eids = nullptr;     // [nnz] edge id (csr.data)
   int32_t* row = nullptr;      // [nnz] row of each position (lazily built COO expansion)
   int32_t* to_other = nullptr; // [nnz] position of the same edge in the other CSR (lazy)
-  int32_t* heavy_first = nullptr;  // [n_rows] row schedule: heavy rows first (lazy)
   int64_t n_rows = 0, n_cols = 0;
-  int32_t max_deg = -1;
+  // Segment plan (lazy): rows with more than seg_len edges are cut into segments of seg_len
+  // consecutive positions so that no single warp walks a hub row alone.
+  int32_t seg_len = 0;          // 0 = plan not built
+  int32_t n_seg = 0;            // total segments of heavy rows
+  int32_t n_heavy = 0;          // heavy rows
+  int32_t* seg_row = nullptr;   // [n_seg] row of the segment
+  int32_t* seg_beg = nullptr;   // [n_seg] first CSR position
+  int32_t* seg_end = nullptr;   // [n_seg] one past the last CSR position
+  int32_t* heavy_row = nullptr; // [n_heavy]
+  int32_t* heavy_ptr = nullptr; // [n_heavy + 1] segment range of each heavy row
+};
+
+struct SegPlan {
+  int seg_len, n_seg, n_heavy;
+  const int32_t *seg_row, *seg_beg, *seg_end, *heavy_row, *heavy_ptr;
 };
 
 }  // namespace b200
@@ -194,7 +207,8 @@ inline const Csr& walk_csr(const DGLB200Graph* g, int walk) {
 const int32_t* csr_rows(DGLB200Graph* g, int walk, cudaStream_t s);      // row-of-position
 // position in the "other" CSR: in -> out, out -> in, in_sorted -> out
 const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s);
-const int32_t* csr_schedule(DGLB200Graph* g, int walk, cudaStream_t s);  // may be NULL
+// Segment plan of a CSR for segments of `seg_len` positions (built once; synchronises then).
+SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s);
 void exclusive_scan_i32(int32_t* data, int64_t n, cudaStream_t s);
 void fill_f32(float* p, int64_t n, float v, cudaStream_t s);
 

@@ -382,65 +382,91 @@ const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s) {
   return c.to_other;
 }
 
-// Row schedule for the row-parallel kernels: rows whose degree is far above the mean are moved
-// to the front (largest first) so the longest sequential reductions start first; all other rows
-// keep their natural order (which preserves whatever locality the node numbering has).
-__global__ void max_deg_kernel(const int32_t* __restrict__ indptr, int64_t n_rows,
-                               int32_t* __restrict__ out) {
-  int m = 0;
+// ---------------------------------------------------------------- segment plan
+__global__ void seg_count_kernel(const int32_t* __restrict__ indptr, int64_t n_rows, int seg_len,
+                                 int32_t* __restrict__ nseg, int32_t* __restrict__ heavy) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n_rows; k += stride)
-    m = max(m, indptr[k + 1] - indptr[k]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-  if ((threadIdx.x & 31) == 0) atomicMax(out, m);
-}
-
-__global__ void schedule_key_kernel(const int32_t* __restrict__ indptr, int64_t n_rows,
-                                    int heavy_threshold, int max_deg,
-                                    int32_t* __restrict__ keys) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n_rows; k += stride) {
-    const int deg = indptr[k + 1] - indptr[k];
-    int key = 255;
-    if (deg >= heavy_threshold) key = 254 - (int)(((int64_t)deg * 254) / max_deg);
-    keys[k] = key;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += stride) {
+    const int deg = indptr[r + 1] - indptr[r];
+    const bool h = deg > seg_len;
+    nseg[r] = h ? (deg + seg_len - 1) / seg_len : 0;
+    heavy[r] = h ? 1 : 0;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    nseg[n_rows] = 0;
+    heavy[n_rows] = 0;
   }
 }
 
-const int32_t* csr_schedule(DGLB200Graph* g, int walk, cudaStream_t s) {
-  Csr& c = (walk == kWalkOut) ? g->out : g->in;  // depends on degrees only
-  if (c.max_deg < 0) {
-    // one-time, synchronising: decide whether this CSR is skewed enough to need a schedule
-    Scratch m(4, s);
-    B200_CUDA(cudaMemsetAsync(m.ptr, 0, 4, s));
+__global__ void seg_fill_kernel(const int32_t* __restrict__ indptr, int64_t n_rows, int seg_len,
+                                const int32_t* __restrict__ seg_off,
+                                const int32_t* __restrict__ heavy_idx,
+                                int32_t* __restrict__ seg_row, int32_t* __restrict__ seg_beg,
+                                int32_t* __restrict__ seg_end, int32_t* __restrict__ heavy_row,
+                                int32_t* __restrict__ heavy_ptr) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += stride) {
+    const int beg = indptr[r], end = indptr[r + 1];
+    if (end - beg <= seg_len) continue;
+    const int h = heavy_idx[r], o = seg_off[r];
+    heavy_row[h] = (int32_t)r;
+    heavy_ptr[h] = o;
+    const int n = (end - beg + seg_len - 1) / seg_len;
+    for (int k = 0; k < n; ++k) {
+      seg_row[o + k] = (int32_t)r;
+      seg_beg[o + k] = beg + k * seg_len;
+      seg_end[o + k] = min(end, beg + (k + 1) * seg_len);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    heavy_ptr[heavy_idx[n_rows]] = seg_off[n_rows];  // sentinel: totals after the scans
+}
+
+SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
+  Csr& c = (walk == kWalkOut) ? g->out : g->in;  // in_sorted has the in-CSR's degrees
+  if (c.seg_len != seg_len) {
+    cudaFree(c.seg_row); cudaFree(c.seg_beg); cudaFree(c.seg_end);
+    cudaFree(c.heavy_row); cudaFree(c.heavy_ptr);
+    c.seg_row = c.seg_beg = c.seg_end = c.heavy_row = c.heavy_ptr = nullptr;
+    c.n_seg = c.n_heavy = 0;
     if (c.n_rows > 0) {
+      Scratch nseg((size_t)(c.n_rows + 1) * 4, s), heavy((size_t)(c.n_rows + 1) * 4, s);
       int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 8);
-      max_deg_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, m.as<int32_t>());
+      seg_count_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, seg_len, nseg.as<int32_t>(),
+                                              heavy.as<int32_t>());
       note_kernel(nullptr, 1);
+      exclusive_scan_i32(nseg.as<int32_t>(), c.n_rows + 1, s);
+      exclusive_scan_i32(heavy.as<int32_t>(), c.n_rows + 1, s);
+      int32_t tot[2] = {0, 0};
+      B200_CUDA(cudaMemcpyAsync(&tot[0], nseg.as<int32_t>() + c.n_rows, 4, cudaMemcpyDeviceToHost, s));
+      B200_CUDA(cudaMemcpyAsync(&tot[1], heavy.as<int32_t>() + c.n_rows, 4, cudaMemcpyDeviceToHost, s));
+      B200_CUDA(cudaStreamSynchronize(s));
+      c.n_seg = tot[0];
+      c.n_heavy = tot[1];
+      if (c.n_seg > 0) {
+        B200_CUDA(cudaMalloc(&c.seg_row, (size_t)c.n_seg * 4));
+        B200_CUDA(cudaMalloc(&c.seg_beg, (size_t)c.n_seg * 4));
+        B200_CUDA(cudaMalloc(&c.seg_end, (size_t)c.n_seg * 4));
+        B200_CUDA(cudaMalloc(&c.heavy_row, (size_t)c.n_heavy * 4));
+        B200_CUDA(cudaMalloc(&c.heavy_ptr, (size_t)(c.n_heavy + 1) * 4));
+        seg_fill_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, seg_len, nseg.as<int32_t>(),
+                                               heavy.as<int32_t>(), c.seg_row, c.seg_beg,
+                                               c.seg_end, c.heavy_row, c.heavy_ptr);
+        note_kernel(nullptr, 1);
+      }
     }
-    int32_t h = 0;
-    B200_CUDA(cudaMemcpyAsync(&h, m.ptr, 4, cudaMemcpyDeviceToHost, s));
-    B200_CUDA(cudaStreamSynchronize(s));
-    c.max_deg = h;
-    const int64_t mean = c.n_rows > 0 ? (g->num_edges + c.n_rows - 1) / c.n_rows : 0;
-    const int64_t thr = std::max<int64_t>(8 * std::max<int64_t>(mean, 1), 1024);
-    if (c.max_deg >= thr && c.n_rows > 1) {
-      Scratch ka((size_t)c.n_rows * 4, s), kb((size_t)c.n_rows * 4, s), va((size_t)c.n_rows * 4, s),
-          vb((size_t)c.n_rows * 4, s);
-      int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 8);
-      schedule_key_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, (int)thr, c.max_deg,
-                                                 ka.as<int32_t>());
-      note_kernel(nullptr, 1);
-      int32_t *sk, *sv;
-      radix_sort_pairs(ka.as<int32_t>(), kb.as<int32_t>(), nullptr, va.as<int32_t>(),
-                       vb.as<int32_t>(), c.n_rows, 256, &sk, &sv, s);
-      B200_CUDA(cudaMalloc(&c.heavy_first, (size_t)c.n_rows * 4));
-      B200_CUDA(cudaMemcpyAsync(c.heavy_first, sv, (size_t)c.n_rows * 4,
-                                cudaMemcpyDeviceToDevice, s));
-    }
+    c.seg_len = seg_len;
   }
-  return c.heavy_first;
+  SegPlan p;
+  p.seg_len = seg_len;
+  p.n_seg = c.n_seg;
+  p.n_heavy = c.n_heavy;
+  p.seg_row = c.seg_row;
+  p.seg_beg = c.seg_beg;
+  p.seg_end = c.seg_end;
+  p.heavy_row = c.heavy_row;
+  p.heavy_ptr = c.heavy_ptr;
+  return p;
 }
 
 static void free_csr(Csr& c) {
@@ -449,7 +475,11 @@ static void free_csr(Csr& c) {
   cudaFree(c.eids);
   cudaFree(c.row);
   cudaFree(c.to_other);
-  cudaFree(c.heavy_first);
+  cudaFree(c.seg_row);
+  cudaFree(c.seg_beg);
+  cudaFree(c.seg_end);
+  cudaFree(c.heavy_row);
+  cudaFree(c.heavy_ptr);
   c = Csr();
 }
 

@@ -20,13 +20,66 @@
 // consumed so U*CH independent 8/16-byte loads are in flight per lane.
 #include <algorithm>
 
+#include <cstdlib>
+#include <cstring>
+
 #include "spmm_kernels.cuh"
+#include "spmm_tma_kernels.cuh"
 
 namespace b200 {
 
 extern template void launch_vec<1>(const SpmmArgs&, int, int, bool, int, cudaStream_t);
 extern template void launch_vec<2>(const SpmmArgs&, int, int, bool, int, cudaStream_t);
 extern template void launch_vec<4>(const SpmmArgs&, int, int, bool, int, cudaStream_t);
+extern template void launch_tma_vec<1>(const TmaArgs&, int, bool, bool, int, size_t, cudaStream_t);
+extern template void launch_tma_vec<2>(const TmaArgs&, int, bool, bool, int, size_t, cudaStream_t);
+extern template void launch_tma_vec<4>(const TmaArgs&, int, bool, bool, int, size_t, cudaStream_t);
+
+// B200_SPMM_PATH=reg|tma forces one SpMM implementation (profiling / A-B runs); default: auto.
+static int forced_path() {
+  const char* e = std::getenv("B200_SPMM_PATH");
+  if (!e) return 0;
+  if (!std::strcmp(e, "reg")) return 1;
+  if (!std::strcmp(e, "tma")) return 2;
+  return 0;
+}
+
+// B200_SPMM_SEG=<edges per segment> (0 = never split rows). Default 4096.
+static int segment_length() {
+  const char* e = std::getenv("B200_SPMM_SEG");
+  if (e) {
+    const long v = std::atol(e);
+    return v <= 0 ? 0x7fffffff : (int)std::min<long>(v, 0x7fffffff);
+  }
+  return 4096;
+}
+
+// out[row] = fold of the row's partial rows in segment order (+ mean division)
+__global__ void __launch_bounds__(128)
+combine_partials_kernel(const int32_t* __restrict__ heavy_row,
+                        const int32_t* __restrict__ heavy_ptr, const float* __restrict__ partial,
+                        const int32_t* __restrict__ indptr, float* __restrict__ out,
+                        const int32_t* __restrict__ out_map, int D, int red, int mean) {
+  const int h = blockIdx.x;
+  const int r = heavy_row[h];
+  const int p0 = heavy_ptr[h], p1 = heavy_ptr[h + 1];
+  const int64_t orow = out_map ? out_map[r] : r;
+  const int deg = indptr[r + 1] - indptr[r];
+  const float dn = (float)(deg > 1 ? deg : 1);
+  for (int col = threadIdx.x; col < D; col += blockDim.x) {
+    float acc = partial[(int64_t)p0 * D + col];
+    for (int k = p0 + 1; k < p1; ++k) acc = red_call(red, acc, partial[(int64_t)k * D + col]);
+    if (mean) acc = __fdiv_rn(acc, dn);
+    out[orow * D + col] = acc;
+  }
+}
+
+static int round_tma_ch(int ch) {
+  const int allowed[] = {1, 2, 3, 4, 5, 6, 8, 10, 12, 16};
+  for (int v : allowed)
+    if (ch <= v) return v;
+  return -1;
+}
 
 static int round_ch(int ch) {
   if (ch <= 4) return ch;
@@ -242,19 +295,89 @@ bool try_spmm(const KernelCall& c) {
   a.nvec = nvec;
   a.out = c.dst;
   a.out_map = o_map;
-  a.sched = csr_schedule(g, walk, s);
 
   if (o_map != nullptr || c.dst_rows != csr.n_rows) fill_f32(c.dst, c.dst_rows * D, fill_v, s);
   if (csr.n_rows == 0) return true;
 
+  // ---- heavy rows (hubs of power-law graphs) are cut into segments of seg_len edges, each
+  // reduced by its own warp into a partial row; combine_partials_kernel folds the partials of a
+  // row in segment order. Rows up to seg_len edges keep the strictly sequential (bit-exact vs the
+  // single-threaded reference) reduction; B200_SPMM_SEG=0 disables segmentation altogether.
+  const SegPlan plan = csr_segments(g, walk, segment_length(), s);
+  Scratch partial;
+  if (plan.n_seg > 0) partial.alloc((size_t)plan.n_seg * D * 4, s);
+  a.n_seg = plan.n_seg;
+  a.seg_len = plan.seg_len;
+  a.seg_row = plan.seg_row;
+  a.seg_beg = plan.seg_beg;
+  a.seg_end = plan.seg_end;
+  a.partial = partial.as<float>();
+  const int64_t n_items = (int64_t)plan.n_seg + csr.n_rows;
+  auto combine = [&]() {
+    if (plan.n_seg == 0) return;
+    combine_partials_kernel<<<plan.n_heavy, 128, 0, s>>>(
+        plan.heavy_row, plan.heavy_ptr, partial.as<float>(), csr.indptr, c.dst, o_map, (int)D,
+        c.red, a.mean);
+    note_kernel(nullptr, 1);
+  };
+
+  // ---- TMA bulk-copy staged path: full-warp rows, plain copy or scalar-per-edge weight
+  {
+    const int force = forced_path();
+    const bool scalar_w = (bmode == kBHead && a.b_width == 1 && a.b_src == kFromEid);
+    const int tch = round_tma_ch((nvec + 31) / 32);
+    const int64_t row_bytes = D * 4;
+    bool ok = (lpr == 32) && (bmode == kBNone || scalar_w) && tch > 0 && row_bytes <= 8192 &&
+              aligned(A, 16);
+    const int64_t mean_deg = E / std::max<int64_t>(csr.n_rows, 1);
+    const bool want = (force == 2) || (force == 0 && row_bytes >= 256 && mean_deg >= 4);
+    if (ok && want) {
+      TmaArgs t;
+      t.indptr = csr.indptr;
+      t.a_pos_ids = (a.a_src == kFromCol) ? csr.indices : a.a_pos_ids;
+      t.a_node_map = (a.a_src == kFromCol) ? a.a_node_map : nullptr;
+      t.n_seg = a.n_seg;
+      t.seg_len = a.seg_len;
+      t.seg_row = a.seg_row;
+      t.seg_beg = a.seg_beg;
+      t.seg_end = a.seg_end;
+      t.partial = a.partial;
+      t.n_rows = a.n_rows;
+      t.D = (int)D;
+      t.nvec = nvec;
+      t.A = A;
+      t.a_rows = (A == c.lhs) ? c.lhs_rows : ((A == c.rhs) ? c.rhs_rows : c.out_rows);
+      t.W = scalar_w ? B : nullptr;
+      t.w_pos_ids = scalar_w ? a.b_pos_ids : nullptr;
+      t.w_is_lhs = a.b_is_lhs;
+      t.op = a.op;
+      t.red = a.red;
+      t.mean = a.mean;
+      t.out = a.out;
+      t.out_map = a.out_map;
+      t.slot_bytes = (int)((row_bytes + 30) & ~(int64_t)15);
+      t.stages = (int)std::min<int64_t>(16, std::max<int64_t>(2, 24576 / t.slot_bytes));
+      const size_t smem = (size_t)kTmaWarps * t.stages * (t.slot_bytes + 8);
+      const int tblocks = (int)((n_items + kTmaWarps - 1) / kTmaWarps);
+      const bool tsum = (c.red == kSum);
+      if (vec == 4) launch_tma_vec<4>(t, tch, tsum, scalar_w, tblocks, smem, s);
+      else if (vec == 2) launch_tma_vec<2>(t, tch, tsum, scalar_w, tblocks, smem, s);
+      else launch_tma_vec<1>(t, tch, tsum, scalar_w, tblocks, smem, s);
+      note_kernel("spmm_tma", 1);
+      combine();
+      return true;
+    }
+  }
+
   const int64_t n_warps =
-      (lpr == 32) ? csr.n_rows * slabs : (csr.n_rows + (32 / lpr) - 1) / (32 / lpr);
+      (lpr == 32) ? n_items * slabs : (n_items + (32 / lpr) - 1) / (32 / lpr);
   const int blocks = (int)((n_warps + 7) / 8);
   const bool sum = (c.red == kSum);
   if (vec == 4) launch_vec<4>(a, ch, bmode, sum, blocks, s);
   else if (vec == 2) launch_vec<2>(a, ch, bmode, sum, blocks, s);
   else launch_vec<1>(a, ch, bmode, sum, blocks, s);
   note_kernel("spmm", 1);
+  combine();
   return true;
 }
 

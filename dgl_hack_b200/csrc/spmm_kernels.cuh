@@ -12,7 +12,12 @@ constexpr int kOpNegA = 100;  // internal: value = -A (gradient of the rhs of "s
 struct SpmmArgs {
   const int32_t* indptr;
   const int32_t* indices;
-  const int32_t* sched;  // optional row schedule
+  // work items: [0, n_seg) = segments of heavy rows (partial results into `partial`), then
+  // one item per row (heavy rows skip themselves)
+  int n_seg;
+  int seg_len;
+  const int32_t *seg_row, *seg_beg, *seg_end;
+  float* partial;  // [n_seg, D]
   int n_rows;
   int lpr;    // lanes per row (power of two <= 32)
   int slabs;  // warps per row when lpr == 32
@@ -94,19 +99,33 @@ __global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
   const int lpr = a.lpr;
   const int sub = lane & (lpr - 1);
 
-  // ---- work item -> (row, slab)
-  int64_t row_idx;
+  // ---- work item -> (row or heavy-row segment, slab)
+  int64_t item;
   int slab = 0;
   if (lpr == 32) {
-    row_idx = warp / a.slabs;
-    slab = (int)(warp - row_idx * a.slabs);
+    item = warp / a.slabs;
+    slab = (int)(warp - item * a.slabs);
   } else {
-    row_idx = warp * (32 / lpr) + lane / lpr;
+    item = warp * (32 / lpr) + lane / lpr;
   }
-  const bool row_ok = row_idx < a.n_rows;
-  const int r = row_ok ? (a.sched ? __ldg(a.sched + row_idx) : (int)row_idx) : 0;
-  const int beg = row_ok ? __ldg(a.indptr + r) : 0;
-  const int deg = row_ok ? __ldg(a.indptr + r + 1) - beg : 0;
+  bool row_ok = item < (int64_t)a.n_seg + a.n_rows;
+  const bool is_seg = item < a.n_seg;
+  int r = 0, beg = 0, deg = 0;
+  if (row_ok) {
+    if (is_seg) {
+      r = __ldg(a.seg_row + item);
+      beg = __ldg(a.seg_beg + item);
+      deg = __ldg(a.seg_end + item) - beg;
+    } else {
+      r = (int)(item - a.n_seg);
+      beg = __ldg(a.indptr + r);
+      deg = __ldg(a.indptr + r + 1) - beg;
+      if (a.n_seg > 0 && deg > a.seg_len) {  // heavy row: served by its segments
+        row_ok = false;
+        deg = 0;
+      }
+    }
+  }
 
   // ---- the vector columns this lane owns
   int col[CH];   // float offset inside a feature row
@@ -202,13 +221,18 @@ __global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
   }
 
   if (row_ok) {
-    const int64_t orow = a.out_map ? __ldg(a.out_map + r) : r;
-    float* op = a.out + orow * a.D;
+    float* op;
+    if (is_seg) {
+      op = a.partial + item * a.D;
+    } else {
+      const int64_t orow = a.out_map ? __ldg(a.out_map + r) : r;
+      op = a.out + orow * a.D;
+    }
     const float dn = (float)(deg > 1 ? deg : 1);
 #pragma unroll
     for (int c = 0; c < CH; ++c) {
       if (cok[c]) {
-        if (a.mean) {
+        if (a.mean && !is_seg) {
 #pragma unroll
           for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fdiv_rn(acc[c].v[e], dn);
         }

@@ -195,9 +195,9 @@ int DGLB200KernelCopyReduceMean(DGLB200GraphHandle graph, int target,
                                 const DGLB200Tensor* in_data, DGLB200Tensor* out_data,
                                 void* stream);
 
-/* Dispatch introspection for tests / bench: name of the kernel family the LAST compute call on
- * this thread used ("spmm", "generic_row", "generic_edge", ...), and how many kernel launches
- * the library has issued on this thread since load. */
+/* Dispatch introspection for tests / bench: name of the kernel family the LAST compute call in
+ * this process used ("spmm", "generic_row", "generic_edge", ...), and how many kernel launches
+ * the library has issued since load (all threads). */
 const char* DGLB200LastKernel(void);
 int64_t DGLB200LaunchCount(void);
 

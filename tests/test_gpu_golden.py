@@ -43,10 +43,13 @@ def test_empty_and_isolated(impl):
     assert np.array_equal(impl.copy_reduce("sum", g, 2, e, 3, None, None), np.zeros((3, 4)))
 
 
-@pytest.mark.parametrize("d", [1, 2, 3, 7, 16, 47, 100, 128, 130, 256, 602, 1000])
-def test_spmm_widths_vs_oracle(impl, d):
-    """Every vector-width / lanes-per-row / slab shape of the SpMM kernel against the oracle."""
+@pytest.mark.parametrize("path", ["reg", "tma"])
+@pytest.mark.parametrize("d", [1, 2, 3, 7, 16, 47, 100, 128, 130, 256, 602, 1000, 2048])
+def test_spmm_widths_vs_oracle(impl, d, path, monkeypatch):
+    """Every vector-width / lanes-per-row / slab shape of both SpMM kernels (register-staged and
+    TMA bulk-copy staged; B200_SPMM_PATH forces one) against the oracle."""
     from oracle import oracle as O
+    monkeypatch.setenv("B200_SPMM_PATH", path)
     ns, nd, ne = 700, 650, 9000
     src, dst = cases.powerlaw_graph(ns, nd, ne, 0.7, 100 + d)
     og, gg = O.Graph(ns, nd, src, dst), impl.make_graph(ns, nd, src, dst)
@@ -57,7 +60,7 @@ def test_spmm_widths_vs_oracle(impl, d):
     for red in ("sum", "max", "min", "prod"):
         want = O.copy_reduce(red, og, 0, x, nd)
         got = impl.copy_reduce(red, gg, 0, x, nd, None, None)
-        assert impl.last == "spmm"
+        assert impl.last.startswith("spmm")
         golden_util.check("copy_u_%s_d%d" % (red, d), got, want, red,
                           scale=None if red != "sum" else _abs_sum(og, x, nd))
     for name, b in (("full", w), ("scalar", w1)):
@@ -66,7 +69,7 @@ def test_spmm_widths_vs_oracle(impl, d):
         for op in ("mul", "add", "sub", "div"):
             want = O.binary_op_reduce("sum", op, og, 0, 2, x, b, nd)
             got = impl.binary_op_reduce("sum", op, gg, 0, 2, x, b, nd, None, None, None)
-            assert impl.last == "spmm"
+            assert impl.last.startswith("spmm")
             golden_util.check("u_%s_e_%s_d%d" % (op, name, d), got, want, "sum",
                               scale=_abs_sum(og, np.abs(x) + 1.5, nd))
     # backward of copy_u+sum and u_mul_e+sum w.r.t. u: transposed SpMM over the out-CSR
@@ -74,13 +77,15 @@ def test_spmm_widths_vs_oracle(impl, d):
     gout = cases.grad_out_for(out.shape)
     want = O.backward_copy_reduce("sum", og, 0, x, out, gout)
     got = impl.backward_copy_reduce("sum", gg, 0, x, out, gout, None, None)
-    assert impl.last == "spmm"
+    assert impl.last.startswith("spmm")
     golden_util.check("bwd_copy_u_d%d" % d, got, want, "sum", grad=True)
     out = O.binary_op_reduce("sum", "mul", og, 0, 2, x, w1, nd)
     want = O.backward_lhs_binary_op_reduce("sum", "mul", og, 0, 2, x, w1, out, gout)
     got = impl.backward_lhs_binary_op_reduce("sum", "mul", gg, 0, 2, x, w1, out, gout,
                                              None, None, None)
     golden_util.check("bwd_u_mul_e_d%d" % d, got, want, "sum", grad=True)
+    if path == "tma" and d >= 33:
+        assert impl.last == "spmm_tma"
 
 
 def _abs_sum(og, x, nd):
@@ -88,17 +93,44 @@ def _abs_sum(og, x, nd):
     return O.copy_reduce("sum", og, 0, np.abs(x).astype(np.float32), nd).astype(np.float64)
 
 
-def test_skewed_graph_uses_schedule(impl):
-    """A hub row far above the mean degree goes through the heavy-rows-first schedule."""
+@pytest.mark.parametrize("seg", ["0", "64", "4096"])
+@pytest.mark.parametrize("path", ["reg", "tma"])
+def test_hub_rows_are_segmented(impl, path, seg, monkeypatch):
+    """A hub row far above the segment length is cut into segments reduced by separate warps and
+    folded in order (deterministic; within the 1e-5 tolerance). With segmentation off
+    (B200_SPMM_SEG=0) the whole row is reduced sequentially and must be bit-identical."""
     from oracle import oracle as O
+    monkeypatch.setenv("B200_SPMM_PATH", path)
+    monkeypatch.setenv("B200_SPMM_SEG", seg)
     rs = np.random.RandomState(5)
     ns = nd = 3000
     src = rs.randint(0, ns, 60000)
     dst = rs.randint(0, nd, 60000)
     dst[:20000] = 17  # hub: in-degree >= 20000 vs mean 20
+    src[40000:] = 5   # and an out-degree hub for the transposed (backward) SpMM
     og, gg = O.Graph(ns, nd, src, dst), impl.make_graph(ns, nd, src, dst)
-    x = rs.uniform(-1, 1, (ns, 64)).astype(np.float32)
-    want = O.copy_reduce("sum", og, 0, x, nd)
-    got = impl.copy_reduce("sum", gg, 0, x, nd, None, None)
-    golden_util.check("hub", got, want, "sum", scale=_abs_sum(og, x, nd))
-    assert np.array_equal(got, want), "sequential in-CSR-order sums should be bit-exact"
+    for d in (64, 602, 5):
+        x = rs.uniform(-1, 1, (ns, d)).astype(np.float32)
+        w = rs.uniform(0.5, 1.5, (60000, 1)).astype(np.float32)
+        for red in ("sum", "max", "prod"):
+            xx = (np.abs(x) * 0.2 + 0.9).astype(np.float32) if red == "prod" else x
+            want = O.copy_reduce(red, og, 0, xx, nd)
+            got = impl.copy_reduce(red, gg, 0, xx, nd, None, None)
+            if red == "sum":
+                golden_util.check("hub", got, want, "sum", scale=_abs_sum(og, xx, nd))
+            elif red == "max":
+                assert np.array_equal(got, want)
+            else:
+                np.testing.assert_allclose(got, want, rtol=5e-3)  # 20000-term product, regrouped
+            if seg == "0":
+                assert np.array_equal(got, want), "sequential in-order reduce must be bit-exact"
+        want = O.binary_op_reduce("sum", "mul", og, 0, 2, x, w, nd)
+        got = impl.binary_op_reduce("sum", "mul", gg, 0, 2, x, w, nd, None, None, None)
+        golden_util.check("hub_w", got, want, "sum", scale=_abs_sum(og, np.abs(x) * 1.5, nd))
+        gout = cases.grad_out_for(want.shape)
+        want = O.backward_copy_reduce("sum", og, 0, x, want, gout)
+        got = impl.backward_copy_reduce("sum", gg, 0, x, want, gout, None, None)
+        golden_util.check("hub_bwd", got, want, "sum",
+                          scale=O.backward_copy_reduce("sum", og, 0, x, want, np.abs(gout)))
+        if seg == "0":
+            assert np.array_equal(got, want)
