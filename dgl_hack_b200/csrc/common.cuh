@@ -175,11 +175,13 @@ struct Csr {
   int32_t* seg_end = nullptr;   // [n_seg] one past the last CSR position
   int32_t* heavy_row = nullptr; // [n_heavy]
   int32_t* heavy_ptr = nullptr; // [n_heavy + 1] segment range of each heavy row
+  int32_t* sched = nullptr;     // [n_rows] rows by descending degree class (NULL = natural order)
 };
 
 struct SegPlan {
   int seg_len, n_seg, n_heavy;
   const int32_t *seg_row, *seg_beg, *seg_end, *heavy_row, *heavy_ptr;
+  const int32_t* sched;  // row order for the non-segment work items (may be NULL)
 };
 
 }  // namespace b200

@@ -383,15 +383,31 @@ const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s) {
 }
 
 // ---------------------------------------------------------------- segment plan
+// Also emits the scheduling key of every row (degree class, longest first: rows that take the
+// longest sequential walk start first, so the kernel's tail is made of the shortest rows; rows of
+// one class keep their natural order) and the largest degree.
 __global__ void seg_count_kernel(const int32_t* __restrict__ indptr, int64_t n_rows, int seg_len,
-                                 int32_t* __restrict__ nseg, int32_t* __restrict__ heavy) {
+                                 int32_t* __restrict__ nseg, int32_t* __restrict__ heavy,
+                                 int32_t* __restrict__ key, int32_t* __restrict__ max_deg) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int m = 0;
   for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += stride) {
     const int deg = indptr[r + 1] - indptr[r];
     const bool h = deg > seg_len;
     nseg[r] = h ? (deg + seg_len - 1) / seg_len : 0;
     heavy[r] = h ? 1 : 0;
+    // 4 classes per octave of degree; heavy rows (they only exit) go last
+    int cls = 0;
+    if (deg > 0) {
+      const int lg = 31 - __clz(deg);
+      cls = 4 * lg + (lg >= 2 ? ((deg >> (lg - 2)) & 3) : 0);
+    }
+    key[r] = h ? 255 : (127 - cls);
+    m = max(m, deg);
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(max_deg, m);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     nseg[n_rows] = 0;
     heavy[n_rows] = 0;
@@ -426,23 +442,38 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
   Csr& c = (walk == kWalkOut) ? g->out : g->in;  // in_sorted has the in-CSR's degrees
   if (c.seg_len != seg_len) {
     cudaFree(c.seg_row); cudaFree(c.seg_beg); cudaFree(c.seg_end);
-    cudaFree(c.heavy_row); cudaFree(c.heavy_ptr);
-    c.seg_row = c.seg_beg = c.seg_end = c.heavy_row = c.heavy_ptr = nullptr;
+    cudaFree(c.heavy_row); cudaFree(c.heavy_ptr); cudaFree(c.sched);
+    c.seg_row = c.seg_beg = c.seg_end = c.heavy_row = c.heavy_ptr = c.sched = nullptr;
     c.n_seg = c.n_heavy = 0;
     if (c.n_rows > 0) {
       Scratch nseg((size_t)(c.n_rows + 1) * 4, s), heavy((size_t)(c.n_rows + 1) * 4, s);
+      Scratch key((size_t)c.n_rows * 4, s), mdeg(4, s);
+      B200_CUDA(cudaMemsetAsync(mdeg.ptr, 0, 4, s));
       int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 8);
       seg_count_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, seg_len, nseg.as<int32_t>(),
-                                              heavy.as<int32_t>());
+                                              heavy.as<int32_t>(), key.as<int32_t>(),
+                                              mdeg.as<int32_t>());
       note_kernel(nullptr, 1);
       exclusive_scan_i32(nseg.as<int32_t>(), c.n_rows + 1, s);
       exclusive_scan_i32(heavy.as<int32_t>(), c.n_rows + 1, s);
-      int32_t tot[2] = {0, 0};
+      int32_t tot[3] = {0, 0, 0};
+      B200_CUDA(cudaMemcpyAsync(&tot[2], mdeg.ptr, 4, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaMemcpyAsync(&tot[0], nseg.as<int32_t>() + c.n_rows, 4, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaMemcpyAsync(&tot[1], heavy.as<int32_t>() + c.n_rows, 4, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaStreamSynchronize(s));
       c.n_seg = tot[0];
       c.n_heavy = tot[1];
+      // Skewed degrees: order the row work items by degree class. (Uniform-ish graphs keep the
+      // natural order and with it whatever locality the node numbering has.)
+      const int64_t mean = (g->num_edges + c.n_rows - 1) / c.n_rows;
+      if ((int64_t)tot[2] > 4 * std::max<int64_t>(mean, 1) && c.n_rows > 1) {
+        Scratch kb((size_t)c.n_rows * 4, s), va((size_t)c.n_rows * 4, s), vb((size_t)c.n_rows * 4, s);
+        int32_t *sk, *sv;
+        radix_sort_pairs(key.as<int32_t>(), kb.as<int32_t>(), nullptr, va.as<int32_t>(),
+                         vb.as<int32_t>(), c.n_rows, 256, &sk, &sv, s);
+        B200_CUDA(cudaMalloc(&c.sched, (size_t)c.n_rows * 4));
+        B200_CUDA(cudaMemcpyAsync(c.sched, sv, (size_t)c.n_rows * 4, cudaMemcpyDeviceToDevice, s));
+      }
       if (c.n_seg > 0) {
         B200_CUDA(cudaMalloc(&c.seg_row, (size_t)c.n_seg * 4));
         B200_CUDA(cudaMalloc(&c.seg_beg, (size_t)c.n_seg * 4));
@@ -466,6 +497,7 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
   p.seg_end = c.seg_end;
   p.heavy_row = c.heavy_row;
   p.heavy_ptr = c.heavy_ptr;
+  p.sched = c.sched;
   return p;
 }
 
@@ -480,6 +512,7 @@ static void free_csr(Csr& c) {
   cudaFree(c.seg_end);
   cudaFree(c.heavy_row);
   cudaFree(c.heavy_ptr);
+  cudaFree(c.sched);
   c = Csr();
 }
 

@@ -31,9 +31,9 @@ namespace b200 {
 extern template void launch_vec<1>(const SpmmArgs&, int, int, bool, int, cudaStream_t);
 extern template void launch_vec<2>(const SpmmArgs&, int, int, bool, int, cudaStream_t);
 extern template void launch_vec<4>(const SpmmArgs&, int, int, bool, int, cudaStream_t);
-extern template void launch_tma_vec<1>(const TmaArgs&, int, bool, bool, int, size_t, cudaStream_t);
-extern template void launch_tma_vec<2>(const TmaArgs&, int, bool, bool, int, size_t, cudaStream_t);
-extern template void launch_tma_vec<4>(const TmaArgs&, int, bool, bool, int, size_t, cudaStream_t);
+extern template void launch_tma_vec<1>(const TmaArgs&, int, bool, bool, int, int, size_t, cudaStream_t);
+extern template void launch_tma_vec<2>(const TmaArgs&, int, bool, bool, int, int, size_t, cudaStream_t);
+extern template void launch_tma_vec<4>(const TmaArgs&, int, bool, bool, int, int, size_t, cudaStream_t);
 
 // B200_SPMM_PATH=reg|tma forces one SpMM implementation (profiling / A-B runs); default: auto.
 static int forced_path() {
@@ -44,14 +44,19 @@ static int forced_path() {
   return 0;
 }
 
-// B200_SPMM_SEG=<edges per segment> (0 = never split rows). Default 4096.
-static int segment_length() {
+// Edges per segment of a heavy row. B200_SPMM_SEG=<n> overrides (0 = never split rows).
+// Default: the longest sequential walk may take about a quarter of the work one resident warp
+// slot gets (E / (148 SMs x 32 warps x 4)), rounded up to a power of two, at least 4096 -- rows
+// up to that many edges are reduced strictly sequentially (bit-exact vs the reference).
+static int segment_length(int64_t num_edges) {
   const char* e = std::getenv("B200_SPMM_SEG");
   if (e) {
     const long v = std::atol(e);
     return v <= 0 ? 0x7fffffff : (int)std::min<long>(v, 0x7fffffff);
   }
-  return 4096;
+  int len = 4096;
+  while (len < 65536 && (int64_t)len * (148 * 32 * 4) < num_edges) len <<= 1;
+  return len;
 }
 
 // out[row] = fold of the row's partial rows in segment order (+ mean division)
@@ -82,9 +87,10 @@ static int round_tma_ch(int ch) {
 }
 
 static int round_ch(int ch) {
-  if (ch <= 4) return ch;
-  if (ch <= 6) return 6;
-  return 8;
+  const int allowed[] = {1, 2, 3, 4, 5, 6, 8, 10, 12};
+  for (int v : allowed)
+    if (ch <= v) return v;
+  return 12;
 }
 
 __global__ void compose_ids_kernel(const int32_t* __restrict__ map,
@@ -246,7 +252,7 @@ bool try_spmm(const KernelCall& c) {
   while (lpr < 32 && lpr < nvec) lpr <<= 1;
   int slabs = 1, ch = 1;
   if (lpr == 32) {
-    slabs = (nvec + 32 * 8 - 1) / (32 * 8);
+    slabs = (nvec + 32 * 12 - 1) / (32 * 12);
     ch = round_ch((nvec + 32 * slabs - 1) / (32 * slabs));
     slabs = (nvec + 32 * ch - 1) / (32 * ch);
   }
@@ -303,7 +309,7 @@ bool try_spmm(const KernelCall& c) {
   // reduced by its own warp into a partial row; combine_partials_kernel folds the partials of a
   // row in segment order. Rows up to seg_len edges keep the strictly sequential (bit-exact vs the
   // single-threaded reference) reduction; B200_SPMM_SEG=0 disables segmentation altogether.
-  const SegPlan plan = csr_segments(g, walk, segment_length(), s);
+  const SegPlan plan = csr_segments(g, walk, segment_length(E), s);
   Scratch partial;
   if (plan.n_seg > 0) partial.alloc((size_t)plan.n_seg * D * 4, s);
   a.n_seg = plan.n_seg;
@@ -311,6 +317,7 @@ bool try_spmm(const KernelCall& c) {
   a.seg_row = plan.seg_row;
   a.seg_beg = plan.seg_beg;
   a.seg_end = plan.seg_end;
+  a.sched = plan.sched;
   a.partial = partial.as<float>();
   const int64_t n_items = (int64_t)plan.n_seg + csr.n_rows;
   auto combine = [&]() {
@@ -330,7 +337,10 @@ bool try_spmm(const KernelCall& c) {
     bool ok = (lpr == 32) && (bmode == kBNone || scalar_w) && tch > 0 && row_bytes <= 8192 &&
               aligned(A, 16);
     const int64_t mean_deg = E / std::max<int64_t>(csr.n_rows, 1);
-    const bool want = (force == 2) || (force == 0 && row_bytes >= 256 && mean_deg >= 4);
+    // Measured on B200 (profiles/r1_spmm_paths.md): the LDG path beats the bulk-copy path on
+    // this gather (TMA 1-D copies of 2.4 KB rows top out near 20-30 B/clk/SM), so it is opt-in.
+    (void)mean_deg;
+    const bool want = (force == 2);
     if (ok && want) {
       TmaArgs t;
       t.indptr = csr.indptr;
@@ -341,6 +351,7 @@ bool try_spmm(const KernelCall& c) {
       t.seg_row = a.seg_row;
       t.seg_beg = a.seg_beg;
       t.seg_end = a.seg_end;
+      t.sched = a.sched;
       t.partial = a.partial;
       t.n_rows = a.n_rows;
       t.D = (int)D;
@@ -356,13 +367,17 @@ bool try_spmm(const KernelCall& c) {
       t.out = a.out;
       t.out_map = a.out_map;
       t.slot_bytes = (int)((row_bytes + 30) & ~(int64_t)15);
-      t.stages = (int)std::min<int64_t>(16, std::max<int64_t>(2, 24576 / t.slot_bytes));
-      const size_t smem = (size_t)kTmaWarps * t.stages * (t.slot_bytes + 8);
-      const int tblocks = (int)((n_items + kTmaWarps - 1) / kTmaWarps);
+      int twarps = 8;
+      t.stages = 2;
+      if (const char* e = std::getenv("B200_TMA_WARPS")) twarps = std::max(1, std::min(16, std::atoi(e)));
+      if (const char* e = std::getenv("B200_TMA_STAGES")) t.stages = std::max(2, std::min(16, std::atoi(e)));
+      while (twarps > 1 && (size_t)twarps * t.stages * (t.slot_bytes + 8) > 200 * 1024) twarps >>= 1;
+      const size_t smem = (size_t)twarps * t.stages * (t.slot_bytes + 8);
+      const int tblocks = (int)((n_items + twarps - 1) / twarps);
       const bool tsum = (c.red == kSum);
-      if (vec == 4) launch_tma_vec<4>(t, tch, tsum, scalar_w, tblocks, smem, s);
-      else if (vec == 2) launch_tma_vec<2>(t, tch, tsum, scalar_w, tblocks, smem, s);
-      else launch_tma_vec<1>(t, tch, tsum, scalar_w, tblocks, smem, s);
+      if (vec == 4) launch_tma_vec<4>(t, tch, tsum, scalar_w, tblocks, twarps, smem, s);
+      else if (vec == 2) launch_tma_vec<2>(t, tch, tsum, scalar_w, tblocks, twarps, smem, s);
+      else launch_tma_vec<1>(t, tch, tsum, scalar_w, tblocks, twarps, smem, s);
       note_kernel("spmm_tma", 1);
       combine();
       return true;

@@ -17,6 +17,7 @@ struct SpmmArgs {
   int n_seg;
   int seg_len;
   const int32_t *seg_row, *seg_beg, *seg_end;
+  const int32_t* sched;  // order of the row work items (NULL = natural)
   float* partial;  // [n_seg, D]
   int n_rows;
   int lpr;    // lanes per row (power of two <= 32)
@@ -118,6 +119,7 @@ __global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
       deg = __ldg(a.seg_end + item) - beg;
     } else {
       r = (int)(item - a.n_seg);
+      if (a.sched) r = __ldg(a.sched + r);
       beg = __ldg(a.indptr + r);
       deg = __ldg(a.indptr + r + 1) - beg;
       if (a.n_seg > 0 && deg > a.seg_len) {  // heavy row: served by its segments
@@ -243,6 +245,15 @@ __global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
 }
 
 // ---------------------------------------------------------------- host side
+// Neighbours whose feature loads are issued back to back. Measured on B200
+// (profiles/microbench): a random-row gather runs fastest with ~64 KB of loads in flight per SM;
+// more (deeper unrolling) thrashes L1 and is up to 3x slower. With 32-64 resident warps that is
+// ~1-2 KB per warp, i.e. U = 1 once a warp moves >= 1 KB per neighbour.
+constexpr int unroll_for(int vec, int ch) {
+  const int bytes = ch * vec * 128;  // per neighbour per warp
+  return bytes >= 1024 ? 1 : (bytes >= 512 ? 2 : (bytes >= 256 ? 4 : 8));
+}
+
 template <int VEC, int CH, int U>
 static void launch_shape(const SpmmArgs& a, int bmode, bool sum, int blocks, cudaStream_t s) {
 #define B200_SPMM_LAUNCH(SUMV, BM) \
@@ -263,12 +274,15 @@ template <int VEC>
 void launch_vec(const SpmmArgs& a, int ch, int bmode, bool sum, int blocks,
                        cudaStream_t s) {
   switch (ch) {
-    case 1: launch_shape<VEC, 1, 8>(a, bmode, sum, blocks, s); break;
-    case 2: launch_shape<VEC, 2, 8>(a, bmode, sum, blocks, s); break;
-    case 3: launch_shape<VEC, 3, 4>(a, bmode, sum, blocks, s); break;
-    case 4: launch_shape<VEC, 4, 4>(a, bmode, sum, blocks, s); break;
-    case 6: launch_shape<VEC, 6, 2>(a, bmode, sum, blocks, s); break;
-    default: launch_shape<VEC, 8, 2>(a, bmode, sum, blocks, s); break;
+    case 1: launch_shape<VEC, 1, unroll_for(VEC, 1)>(a, bmode, sum, blocks, s); break;
+    case 2: launch_shape<VEC, 2, unroll_for(VEC, 2)>(a, bmode, sum, blocks, s); break;
+    case 3: launch_shape<VEC, 3, unroll_for(VEC, 3)>(a, bmode, sum, blocks, s); break;
+    case 4: launch_shape<VEC, 4, unroll_for(VEC, 4)>(a, bmode, sum, blocks, s); break;
+    case 5: launch_shape<VEC, 5, unroll_for(VEC, 5)>(a, bmode, sum, blocks, s); break;
+    case 6: launch_shape<VEC, 6, unroll_for(VEC, 6)>(a, bmode, sum, blocks, s); break;
+    case 8: launch_shape<VEC, 8, unroll_for(VEC, 8)>(a, bmode, sum, blocks, s); break;
+    case 10: launch_shape<VEC, 10, unroll_for(VEC, 10)>(a, bmode, sum, blocks, s); break;
+    default: launch_shape<VEC, 12, unroll_for(VEC, 12)>(a, bmode, sum, blocks, s); break;
   }
 }
 

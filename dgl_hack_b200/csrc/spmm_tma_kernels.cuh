@@ -27,6 +27,7 @@ struct TmaArgs {
   int n_seg;  // work items [0, n_seg) are heavy-row segments, see SpmmArgs
   int seg_len;
   const int32_t *seg_row, *seg_beg, *seg_end;
+  const int32_t* sched;  // order of the row work items (NULL = natural)
   float* partial;
   int n_rows;
   int D;       // floats per row
@@ -107,13 +108,14 @@ __device__ __forceinline__ Vec<4> lds_vec<4>(const unsigned char* p) {
   return r;
 }
 
-constexpr int kTmaWarps = 4;  // warps per CTA, each with a private ring
+constexpr int kTmaMaxWarps = 16;  // warps per CTA (runtime: blockDim.x / 32), each with a private ring
 
 template <int VEC, int CH, bool SUM, bool HAS_W>
-__global__ void __launch_bounds__(kTmaWarps * 32) spmm_tma_kernel(const TmaArgs a) {
+__global__ void __launch_bounds__(kTmaMaxWarps * 32) spmm_tma_kernel(const TmaArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int S = a.stages;
+  const int kTmaWarps = blockDim.x >> 5;
   unsigned char* ring = smem + (size_t)wid * S * a.slot_bytes;
   const uint32_t ring_u32 = smem_u32(ring);
   const uint32_t bars_u32 =
@@ -134,6 +136,7 @@ __global__ void __launch_bounds__(kTmaWarps * 32) spmm_tma_kernel(const TmaArgs 
     deg = __ldg(a.seg_end + item) - beg;
   } else {
     r = (int)(item - a.n_seg);
+    if (a.sched) r = __ldg(a.sched + r);
     beg = __ldg(a.indptr + r);
     deg = __ldg(a.indptr + r + 1) - beg;
     if (a.n_seg > 0 && deg > a.seg_len) return;  // heavy row: served by its segments
@@ -253,13 +256,13 @@ __global__ void __launch_bounds__(kTmaWarps * 32) spmm_tma_kernel(const TmaArgs 
 }
 
 template <int VEC, int CH>
-void launch_tma_shape(const TmaArgs& a, bool sum, bool has_w, int blocks, size_t smem,
+void launch_tma_shape(const TmaArgs& a, bool sum, bool has_w, int blocks, int warps, size_t smem,
                       cudaStream_t s) {
 #define B200_TMA_LAUNCH(SUMV, WV)                                                          \
   do {                                                                                     \
     auto kfn = spmm_tma_kernel<VEC, CH, SUMV, WV>;                                         \
     cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);     \
-    kfn<<<blocks, kTmaWarps * 32, smem, s>>>(a);                                           \
+    kfn<<<blocks, warps * 32, smem, s>>>(a);                                           \
   } while (0)
   if (sum) {
     if (has_w) B200_TMA_LAUNCH(true, true);
@@ -273,19 +276,19 @@ void launch_tma_shape(const TmaArgs& a, bool sum, bool has_w, int blocks, size_t
 
 // ch must be one of {1,2,3,4,5,6,8,10,12,16}
 template <int VEC>
-void launch_tma_vec(const TmaArgs& a, int ch, bool sum, bool has_w, int blocks, size_t smem,
-                    cudaStream_t s) {
+void launch_tma_vec(const TmaArgs& a, int ch, bool sum, bool has_w, int blocks, int warps,
+                    size_t smem, cudaStream_t s) {
   switch (ch) {
-    case 1: launch_tma_shape<VEC, 1>(a, sum, has_w, blocks, smem, s); break;
-    case 2: launch_tma_shape<VEC, 2>(a, sum, has_w, blocks, smem, s); break;
-    case 3: launch_tma_shape<VEC, 3>(a, sum, has_w, blocks, smem, s); break;
-    case 4: launch_tma_shape<VEC, 4>(a, sum, has_w, blocks, smem, s); break;
-    case 5: launch_tma_shape<VEC, 5>(a, sum, has_w, blocks, smem, s); break;
-    case 6: launch_tma_shape<VEC, 6>(a, sum, has_w, blocks, smem, s); break;
-    case 8: launch_tma_shape<VEC, 8>(a, sum, has_w, blocks, smem, s); break;
-    case 10: launch_tma_shape<VEC, 10>(a, sum, has_w, blocks, smem, s); break;
-    case 12: launch_tma_shape<VEC, 12>(a, sum, has_w, blocks, smem, s); break;
-    default: launch_tma_shape<VEC, 16>(a, sum, has_w, blocks, smem, s); break;
+    case 1: launch_tma_shape<VEC, 1>(a, sum, has_w, blocks, warps, smem, s); break;
+    case 2: launch_tma_shape<VEC, 2>(a, sum, has_w, blocks, warps, smem, s); break;
+    case 3: launch_tma_shape<VEC, 3>(a, sum, has_w, blocks, warps, smem, s); break;
+    case 4: launch_tma_shape<VEC, 4>(a, sum, has_w, blocks, warps, smem, s); break;
+    case 5: launch_tma_shape<VEC, 5>(a, sum, has_w, blocks, warps, smem, s); break;
+    case 6: launch_tma_shape<VEC, 6>(a, sum, has_w, blocks, warps, smem, s); break;
+    case 8: launch_tma_shape<VEC, 8>(a, sum, has_w, blocks, warps, smem, s); break;
+    case 10: launch_tma_shape<VEC, 10>(a, sum, has_w, blocks, warps, smem, s); break;
+    case 12: launch_tma_shape<VEC, 12>(a, sum, has_w, blocks, warps, smem, s); break;
+    default: launch_tma_shape<VEC, 16>(a, sum, has_w, blocks, warps, smem, s); break;
   }
 }
 

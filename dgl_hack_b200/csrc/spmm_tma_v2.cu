@@ -1,4 +1,4 @@
 #include "spmm_tma_kernels.cuh"
 namespace b200 {
-template void launch_tma_vec<2>(const TmaArgs&, int, bool, bool, int, size_t, cudaStream_t);
+template void launch_tma_vec<2>(const TmaArgs&, int, bool, bool, int, int, size_t, cudaStream_t);
 }

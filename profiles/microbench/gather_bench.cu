@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstdint>
 #include <vector>
+#include <cmath>
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA %s at %d\n", cudaGetErrorString(e), __LINE__); exit(1);} } while (0)
 
@@ -23,7 +24,12 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 }
 
 // ---------------- variant A: register staged, warp per (row, slab), U neighbours in flight
-template <int CH, int U>
+__device__ __forceinline__ float2 ld_na(const float2* p) {
+  float2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0, %1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
+  return r;
+}
+template <int CH, int U, int NA>
 __global__ void __launch_bounds__(256) k_reg(const int* __restrict__ indptr, const int* __restrict__ idx,
                                              const float* __restrict__ X, float* __restrict__ out,
                                              int n_rows, int D, int slabs) {
@@ -46,7 +52,7 @@ __global__ void __launch_bounds__(256) k_reg(const int* __restrict__ indptr, con
         int ia = __shfl_sync(0xffffffffu, mine, (i + k) & 31);
         bool on = i + k < cnt;
 #pragma unroll
-        for (int c = 0; c < CH; ++c) if (on && ok[c]) v[k][c] = __ldg((const float2*)(X + (long)ia * D + col[c]));
+        for (int c = 0; c < CH; ++c) if (on && ok[c]) v[k][c] = NA ? ld_na((const float2*)(X + (long)ia * D + col[c])) : __ldg((const float2*)(X + (long)ia * D + col[c]));
       }
 #pragma unroll
       for (int k = 0; k < U; ++k) if (i + k < cnt) {
@@ -128,12 +134,14 @@ __global__ void k_tma(const int* __restrict__ indptr, const int* __restrict__ id
 
 int main(int argc, char** argv) {
   int N = argc > 1 ? atoi(argv[1]) : 232965, D = argc > 2 ? atoi(argv[2]) : 602, deg = argc > 3 ? atoi(argv[3]) : 492;
+  double alpha = argc > 4 ? atof(argv[4]) : 0.0; int do_tma = argc > 5 ? atoi(argv[5]) : 1;
   long E = (long)N * deg;
   printf("N=%d D=%d deg=%d E=%ld bytes gathered=%.1f GB\n", N, D, deg, E, E * D * 4.0 / 1e9);
   std::vector<int> indptr(N + 1), idx(E);
   uint64_t s = 88172645463325252ull;
   for (int i = 0; i <= N; ++i) indptr[i] = (int)((long)i * deg);
-  for (long e = 0; e < E; ++e) { s ^= s << 13; s ^= s >> 7; s ^= s << 17; idx[e] = (int)(s % N); }
+  for (long e = 0; e < E; ++e) { s ^= s << 13; s ^= s >> 7; s ^= s << 17; double u = (s >> 11) * (1.0 / 9007199254740992.0); idx[e] = alpha > 0 ? (int)fmin(N - 1.0, pow((pow((double)N, 1 - alpha) - 1) * u + 1, 1 / (1 - alpha)) - 1) : (int)(s % N); }
+  if (alpha > 0) for (long e = 0; e < E; ++e) idx[e] = (int)(((unsigned long)idx[e] * 2654435761ul) % N);
   int *d_ip, *d_idx; float *X, *out;
   CK(cudaMalloc(&d_ip, (N + 1) * 4)); CK(cudaMalloc(&d_idx, E * 4));
   CK(cudaMalloc(&X, (size_t)N * D * 4 + 64)); CK(cudaMalloc(&out, (size_t)N * D * 4));
@@ -149,18 +157,24 @@ int main(int argc, char** argv) {
   };
   char nm[128];
   const int nvec = D / 2;
-#define REG(CHV, UV) { int slabs = (nvec + 32 * CHV - 1) / (32 * CHV); long warps = (long)N * slabs; int blocks = (int)((warps + 7) / 8); \
-    sprintf(nm, "reg CH=%d U=%d slabs=%d", CHV, UV, slabs); timeit(nm, [&] { k_reg<CHV, UV><<<blocks, 256>>>(d_ip, d_idx, X, out, N, D, slabs); }); }
+#define REG(CHV, UV, NA, TPB) { int slabs = (nvec + 32 * CHV - 1) / (32 * CHV); long warps = (long)N * slabs; int wpb = TPB / 32; int blocks = (int)((warps + wpb - 1) / wpb); \
+    sprintf(nm, "reg CH=%d U=%d slabs=%d na=%d tpb=%d", CHV, UV, slabs, NA, TPB); timeit(nm, [&] { k_reg<CHV, UV, NA><<<blocks, TPB>>>(d_ip, d_idx, X, out, N, D, slabs); }); }
   if (nvec <= 32 * 10 * 4) {
-    REG(5, 2) REG(5, 4) REG(6, 2) REG(10, 2) REG(10, 1) REG(3, 4) REG(3, 8) REG(2, 8)
+    REG(10, 1, 0, 256) REG(10, 1, 1, 256) REG(10, 1, 0, 128) REG(10, 2, 1, 256)
+    REG(5, 1, 0, 256) REG(5, 1, 1, 256) REG(5, 2, 0, 256) REG(5, 2, 1, 256) REG(5, 4, 1, 256) REG(5, 2, 0, 128)
+    REG(3, 1, 0, 256) REG(3, 2, 0, 256) REG(3, 2, 1, 256) REG(3, 4, 1, 256)
+    REG(2, 1, 0, 256) REG(2, 2, 0, 256) REG(2, 4, 0, 256) REG(2, 4, 1, 256) REG(2, 8, 1, 256)
+    REG(1, 2, 0, 256) REG(1, 4, 0, 256) REG(1, 8, 0, 256) REG(1, 8, 1, 256)
   }
   const int slot = (D * 4 + 30) & ~15;
 #define TMA(CHV, SV, GV, WV, MODE) if (nvec <= 32 * CHV) { size_t smem = (size_t)WV * SV * GV * slot + WV * SV * 8; \
     if (smem <= 227 * 1024) { auto kf = k_tma<CHV>; cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     int blocks = (N + WV - 1) / WV; sprintf(nm, "tma CH=%d S=%d G=%d warps=%d mode=%d smem=%zuK", CHV, SV, GV, WV, MODE, smem / 1024); \
     timeit(nm, [&] { kf<<<blocks, WV * 32, smem>>>(d_ip, d_idx, X, out, N, D, SV, GV, slot, WV, MODE); }); } }
+  if (do_tma) {
   TMA(10, 9, 1, 4, 0) TMA(10, 4, 1, 4, 0) TMA(10, 2, 1, 4, 0) TMA(10, 16, 1, 4, 0) TMA(10, 8, 1, 8, 0) TMA(10, 4, 1, 16, 0)
   TMA(10, 4, 2, 4, 0) TMA(10, 2, 4, 4, 0) TMA(10, 3, 4, 4, 1) TMA(10, 2, 8, 4, 1) TMA(10, 4, 2, 4, 1) TMA(10, 4, 1, 2, 0) TMA(10, 8, 1, 1, 0)
   TMA(10, 2, 2, 16, 1) TMA(10, 3, 1, 24, 0)
+  }
   return 0;
 }

@@ -113,7 +113,7 @@ def test_hub_rows_are_segmented(impl, path, seg, monkeypatch):
         x = rs.uniform(-1, 1, (ns, d)).astype(np.float32)
         w = rs.uniform(0.5, 1.5, (60000, 1)).astype(np.float32)
         for red in ("sum", "max", "prod"):
-            xx = (np.abs(x) * 0.2 + 0.9).astype(np.float32) if red == "prod" else x
+            xx = (np.abs(x) * 0.02 + 0.99).astype(np.float32) if red == "prod" else x
             want = O.copy_reduce(red, og, 0, xx, nd)
             got = impl.copy_reduce(red, gg, 0, xx, nd, None, None)
             if red == "sum":
@@ -121,7 +121,7 @@ def test_hub_rows_are_segmented(impl, path, seg, monkeypatch):
             elif red == "max":
                 assert np.array_equal(got, want)
             else:
-                np.testing.assert_allclose(got, want, rtol=5e-3)  # 20000-term product, regrouped
+                np.testing.assert_allclose(got, want, rtol=5e-3, atol=1e-30)  # 20000 terms, regrouped
             if seg == "0":
                 assert np.array_equal(got, want), "sequential in-order reduce must be bit-exact"
         want = O.binary_op_reduce("sum", "mul", og, 0, 2, x, w, nd)
