@@ -93,17 +93,27 @@ __device__ __forceinline__ float spmm_value(int op, int b_is_lhs, float av, floa
   return b_is_lhs ? op_scalar(op, bv, av) : op_scalar(op, av, bv);
 }
 
-template <int VEC, int CH, int U, bool SUM, int BMODE>
-__global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
+// Minimum resident CTAs the compiler should budget registers for: the gather is latency bound
+// and wants 32+ resident warps whenever accumulators + one neighbour's loads fit in ~60 registers.
+constexpr int min_blocks_for(int vec, int ch, int u, int bmode) {
+  const int live = ch * vec * (1 + u * (bmode == kBFull ? 2 : 1)) + (bmode == kBHead ? ch * u : 0);
+  return live <= 40 ? 4 : (live <= 100 ? 2 : 1);
+}
+
+// FULL: a row is served by whole warps (lpr == 32) so every column offset is a compile-time
+// constant; otherwise lpr (< 32, CH == 1) lanes serve a row and a warp handles 32 / lpr rows.
+template <int VEC, int CH, int U, bool SUM, int BMODE, bool FULL>
+__global__ void __launch_bounds__(256, min_blocks_for(VEC, CH, U, BMODE))
+spmm_kernel(const SpmmArgs a) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lpr = a.lpr;
-  const int sub = lane & (lpr - 1);
+  const int lpr = FULL ? 32 : a.lpr;
+  const int sub = FULL ? lane : (lane & (lpr - 1));
 
   // ---- work item -> (row or heavy-row segment, slab)
   int64_t item;
   int slab = 0;
-  if (lpr == 32) {
+  if (FULL) {
     item = warp / a.slabs;
     slab = (int)(warp - item * a.slabs);
   } else {
@@ -129,17 +139,10 @@ __global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
     }
   }
 
-  // ---- the vector columns this lane owns
-  int col[CH];   // float offset inside a feature row
-  bool cok[CH];
-  int bcol[CH];  // kBHead: B column
-#pragma unroll
-  for (int c = 0; c < CH; ++c) {
-    const int vc = slab * (32 * CH) + c * lpr + sub;
-    cok[c] = vc < a.nvec;
-    col[c] = vc * VEC;
-    bcol[c] = (BMODE == kBHead) ? col[c] / a.b_head_div : 0;
-  }
+  // ---- this lane's first vector column; column c of the lane is vc0 + c * lpr
+  const int vc0 = slab * (32 * CH) + sub;
+  const int cbase = vc0 * VEC;  // float offset of the lane's first column inside a row
+  auto col_ok = [&](int c) -> bool { return vc0 + c * lpr < a.nvec; };
 
   const float ident = SUM ? 0.f : red_identity(a.red);
   Vec<VEC> acc[CH];
@@ -152,13 +155,12 @@ __global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
   if (BMODE != kBNone && a.b_src == kFromRow)
     b_row_const = (int64_t)(a.b_node_map ? __ldg(a.b_node_map + r) : r) * a.b_width;
 
-  const int maxdeg = __reduce_max_sync(0xffffffffu, deg);
+  const int maxdeg = FULL ? deg : __reduce_max_sync(0xffffffffu, deg);
   for (int base = 0; base < maxdeg; base += lpr) {
     // ---- cooperative fetch of up to lpr neighbour ids per row
     const int my = base + sub;
-    const bool okp = my < deg;
     int pa = 0, pb = 0;
-    if (okp) {
+    if (my < deg) {
       const int p = beg + my;
       int cidx = 0;
       if (a.need_col) cidx = __ldg(a.indices + p);
@@ -180,33 +182,32 @@ __global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
       Vec<VEC> va[U][CH];
       Vec<VEC> vb[U][CH];
       float sb[U][CH];
-      bool on[U];
 #pragma unroll
       for (int k = 0; k < U; ++k) {
         const int srcl = (i + k) & (lpr - 1);
         const int ia = __shfl_sync(0xffffffffu, pa, srcl, lpr);
         int ib = 0;
         if (BMODE != kBNone) ib = __shfl_sync(0xffffffffu, pb, srcl, lpr);
-        on[k] = (i + k < lpr) && (base + i + k < deg);
-        const float* ap = a.A + (int64_t)ia * a.D;
+        const bool on = (i + k < lpr) && (base + i + k < deg);
+        const float* ap = a.A + (int64_t)ia * a.D + cbase;
         const float* bp = nullptr;
         if (BMODE != kBNone)
           bp = a.B + ((a.b_src == kFromRow) ? b_row_const : (int64_t)ib * a.b_width);
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
-          if (on[k] && cok[c]) {
-            va[k][c] = ld_vec<VEC>(ap + col[c]);
-            if (BMODE == kBFull) vb[k][c] = ld_vec<VEC>(bp + col[c]);
-            if (BMODE == kBHead) sb[k][c] = __ldg(bp + bcol[c]);
+          if (on && col_ok(c)) {
+            va[k][c] = ld_vec<VEC>(ap + c * lpr * VEC);
+            if (BMODE == kBFull) vb[k][c] = ld_vec<VEC>(bp + cbase + c * lpr * VEC);
+            if (BMODE == kBHead) sb[k][c] = __ldg(bp + (cbase + c * lpr * VEC) / a.b_head_div);
           }
         }
       }
 #pragma unroll
       for (int k = 0; k < U; ++k) {
-        if (on[k]) {
+        if ((i + k < lpr) && (base + i + k < deg)) {
 #pragma unroll
           for (int c = 0; c < CH; ++c) {
-            if (cok[c]) {
+            if (col_ok(c)) {
 #pragma unroll
               for (int e = 0; e < VEC; ++e) {
                 float val = va[k][c].v[e];
@@ -230,15 +231,16 @@ __global__ void __launch_bounds__(256) spmm_kernel(const SpmmArgs a) {
       const int64_t orow = a.out_map ? __ldg(a.out_map + r) : r;
       op = a.out + orow * a.D;
     }
+    op += cbase;
     const float dn = (float)(deg > 1 ? deg : 1);
 #pragma unroll
     for (int c = 0; c < CH; ++c) {
-      if (cok[c]) {
+      if (col_ok(c)) {
         if (a.mean && !is_seg) {
 #pragma unroll
           for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fdiv_rn(acc[c].v[e], dn);
         }
-        st_vec<VEC>(op + col[c], acc[c]);
+        st_vec<VEC>(op + c * lpr * VEC, acc[c]);
       }
     }
   }
@@ -256,8 +258,15 @@ constexpr int unroll_for(int vec, int ch) {
 
 template <int VEC, int CH, int U>
 static void launch_shape(const SpmmArgs& a, int bmode, bool sum, int blocks, cudaStream_t s) {
-#define B200_SPMM_LAUNCH(SUMV, BM) \
-  spmm_kernel<VEC, CH, U, SUMV, BM><<<blocks, 256, 0, s>>>(a)
+#define B200_SPMM_LAUNCH(SUMV, BM)                                             \
+  do {                                                                         \
+    if (a.lpr == 32) {                                                         \
+      spmm_kernel<VEC, CH, U, SUMV, BM, true><<<blocks, 256, 0, s>>>(a);       \
+    } else {                                                                   \
+      if constexpr (CH == 1)                                                   \
+        spmm_kernel<VEC, CH, U, SUMV, BM, false><<<blocks, 256, 0, s>>>(a);    \
+    }                                                                          \
+  } while (0)
   if (sum) {
     if (bmode == kBNone) B200_SPMM_LAUNCH(true, kBNone);
     else if (bmode == kBFull) B200_SPMM_LAUNCH(true, kBFull);
