@@ -79,6 +79,10 @@ SYMBOLS = {
                                                           TensorP, TensorP, _c.c_void_p]),
     "DGLB200KernelCopyReduce": (_c.c_int, [_c.c_char_p, GraphHandle, _c.c_int, TensorP, TensorP,
                                            TensorP, TensorP, _c.c_void_p]),
+    "DGLB200FusedGatKernel": (_c.c_int, [GraphHandle, TensorP, TensorP, TensorP, TensorP, TensorP,
+                                         TensorP, _c.c_float, _c.c_void_p]),
+    "DGLB200KernelBackwardFusedGat": (_c.c_int, [GraphHandle] + [TensorP] * 10 +
+                                      [_c.c_float, _c.c_void_p]),
     "DGLB200KernelCopyReduceMean": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP,
                                                _c.c_void_p]),
     "DGLB200KernelBackwardCopyReduce": (_c.c_int, [_c.c_char_p, GraphHandle, _c.c_int, TensorP,

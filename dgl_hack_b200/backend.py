@@ -143,3 +143,32 @@ def copy_reduce(reducer, graph, target, in_data, out_size, in_map=(None, None),
     in_data = in_data.contiguous()
     out_data = in_data.new_empty((out_size,) + in_data.shape[1:])
     return CopyReduce.apply(reducer, graph, target, in_data, out_data, out_size, in_map, out_map)
+
+
+class FusedGat(th.autograd.Function):
+    """tensor.py:383-413 FusedGat (the fork's fused attention op), same saved state."""
+
+    @staticmethod
+    def forward(ctx, graph, feat_src, el, er, s, exp, ret, slope):
+        ctx.backward_cache = graph, feat_src, el, er, s, exp, ret, slope
+        K.fused_gat_kernel(graph, feat_src, el, er, s, exp, ret, slope)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        graph, feat_src, el, er, s, exp, ret, slope = ctx.backward_cache
+        gradout = gradout.contiguous()
+        grad_el, grad_er = th.empty_like(el), th.empty_like(er)
+        grad_feat_src = th.empty_like(feat_src)
+        K.backward_fused_gat(graph, feat_src, el, er, s, exp, ret, gradout, grad_feat_src,
+                             grad_el, grad_er, slope)
+        return None, grad_feat_src, grad_el, grad_er, None, None, None, None
+
+
+def fused_gat(graph, feat_src, el, er, slope):
+    """tensor.py:415-420 fused_gat; `graph` is a GraphIndex on feat_src's device."""
+    feat_src, el, er = feat_src.contiguous(), el.contiguous(), er.contiguous()
+    exp = el.new_empty([graph.number_of_edges()] + list(el.size()[1:]))
+    s = th.empty_like(er)
+    ret = feat_src.new_empty((graph.num_dst,) + tuple(feat_src.shape[1:]))
+    return FusedGat.apply(graph, feat_src, el, er, s, exp, ret, slope)

@@ -614,4 +614,75 @@ int DGLB200KernelBackwardCopyReduce(const char* reducer, DGLB200GraphHandle grap
   API_END();
 }
 
+// ---- fused GAT (hack ops of the fork)
+static void gat_shapes(DGLB200Graph* g, const DGLB200Tensor* ft, const DGLB200Tensor* el,
+                       const DGLB200Tensor* er, const DGLB200Tensor* sum,
+                       const DGLB200Tensor* exp, const DGLB200Tensor* ret, int64_t* H,
+                       int64_t* F) {
+  *H = feat_len(el);
+  const int64_t D = feat_len(ft);
+  B200_CHECK(*H >= 1 && D % *H == 0, "fused GAT: feat_src width is not a multiple of the heads");
+  *F = D / *H;
+  B200_CHECK(feat_len(er) == *H && feat_len(sum) == *H && feat_len(exp) == *H,
+             "fused GAT: el / er / sum / exp must have one value per head");
+  B200_CHECK(feat_len(ret) == D, "fused GAT: ret must have the shape of feat_src");
+  B200_CHECK(ft->shape[0] >= g->num_src && el->shape[0] >= g->num_src &&
+                 er->shape[0] >= g->num_dst && sum->shape[0] >= g->num_dst &&
+                 ret->shape[0] >= g->num_dst && exp->shape[0] >= g->num_edges,
+             "fused GAT: a tensor has fewer rows than the graph has nodes / edges");
+}
+
+int DGLB200FusedGatKernel(DGLB200GraphHandle graph, const DGLB200Tensor* feat_src,
+                          const DGLB200Tensor* el, const DGLB200Tensor* er, DGLB200Tensor* sum,
+                          DGLB200Tensor* exp, DGLB200Tensor* ret, float slope, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && feat_src && el && er && sum && exp && ret, "NULL argument");
+  check_ctx(graph, {feat_src, el, er, sum, exp, ret},
+            {"feat_src", "el", "er", "sum", "exp", "ret"});
+  for (const DGLB200Tensor* t : {feat_src, el, er, (const DGLB200Tensor*)sum,
+                                 (const DGLB200Tensor*)exp, (const DGLB200Tensor*)ret})
+    check_float(t, "fused GAT tensor");
+  int64_t H, F;
+  gat_shapes(graph, feat_src, el, er, sum, exp, ret, &H, &F);
+  B200_CUDA(cudaSetDevice(graph->device));
+  fused_gat_forward(graph, data_ptr<const float>(feat_src), data_ptr<const float>(el),
+                    data_ptr<const float>(er), data_ptr<float>(sum), data_ptr<float>(exp),
+                    data_ptr<float>(ret), H, F, slope, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200KernelBackwardFusedGat(DGLB200GraphHandle graph, const DGLB200Tensor* feat_src,
+                                  const DGLB200Tensor* el, const DGLB200Tensor* er,
+                                  const DGLB200Tensor* sum, const DGLB200Tensor* exp,
+                                  const DGLB200Tensor* ret, const DGLB200Tensor* grad_out,
+                                  DGLB200Tensor* grad_feat_src, DGLB200Tensor* grad_el,
+                                  DGLB200Tensor* grad_er, float slope, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && feat_src && el && er && sum && exp && ret && grad_out && grad_feat_src &&
+                 grad_el && grad_er, "NULL argument");
+  check_ctx(graph, {feat_src, el, er, sum, exp, ret, grad_out, grad_feat_src, grad_el, grad_er},
+            {"feat_src", "el", "er", "sum", "exp", "ret", "grad_out", "grad_feat_src", "grad_el",
+             "grad_er"});
+  for (const DGLB200Tensor* t :
+       {feat_src, el, er, sum, exp, ret, grad_out, (const DGLB200Tensor*)grad_feat_src,
+        (const DGLB200Tensor*)grad_el, (const DGLB200Tensor*)grad_er})
+    check_float(t, "fused GAT tensor");
+  int64_t H, F;
+  gat_shapes(graph, feat_src, el, er, sum, exp, ret, &H, &F);
+  B200_CHECK(feat_len(grad_out) == H * F && feat_len(grad_feat_src) == H * F &&
+                 feat_len(grad_el) == H && feat_len(grad_er) == H,
+             "fused GAT: gradient tensors have the wrong feature shape");
+  B200_CHECK(grad_out->shape[0] >= graph->num_dst && grad_feat_src->shape[0] >= graph->num_src &&
+                 grad_el->shape[0] >= graph->num_src && grad_er->shape[0] >= graph->num_dst,
+             "fused GAT: a gradient tensor has too few rows");
+  B200_CUDA(cudaSetDevice(graph->device));
+  fused_gat_backward(graph, data_ptr<const float>(feat_src), data_ptr<const float>(el),
+                     data_ptr<const float>(er), data_ptr<const float>(sum),
+                     data_ptr<const float>(exp), data_ptr<const float>(ret),
+                     data_ptr<const float>(grad_out), data_ptr<float>(grad_feat_src),
+                     data_ptr<float>(grad_el), data_ptr<float>(grad_er), H, F, slope,
+                     static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
 }  // extern "C"

@@ -230,6 +230,14 @@ struct KernelCall {
 };
 
 void run_generic(const KernelCall& c);
+// gat.cu
+void fused_gat_forward(DGLB200Graph* g, const float* ft, const float* el, const float* er,
+                       float* sum, float* exp, float* ret, int64_t H, int64_t F, float slope,
+                       cudaStream_t s);
+void fused_gat_backward(DGLB200Graph* g, const float* ft, const float* el, const float* er,
+                        const float* sum, const float* exp, const float* ret, const float* gout,
+                        float* grad_ft, float* grad_el, float* grad_er, int64_t H, int64_t F,
+                        float slope, cudaStream_t s);
 bool try_spmm(const KernelCall& c);  // returns false if the call is not an SpMM-shaped case
 bool try_sddmm(const KernelCall& c);
 

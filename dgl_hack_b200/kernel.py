@@ -93,6 +93,24 @@ def backward_copy_reduce(reducer, G, target, X, out, grad_out, grad_X, X_rows=No
             xr.ptr, orr.ptr, _stream(G)))
 
 
+def fused_gat_kernel(G, feat_src, el, er, s, exp, ret, slope):
+    """python/dgl/kernel.py fused_gat_kernel -> kernel._CAPI_DGLFusedGatKernel."""
+    t = [_nd(x) for x in (feat_src, el, er, s, exp, ret)]
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200FusedGatKernel(G.handle, *[x.ptr for x in t], float(slope),
+                                             _stream(G)))
+
+
+def backward_fused_gat(G, feat_src, el, er, s, exp, ret, grad_out, grad_feat_src, grad_el,
+                       grad_er, slope):
+    """python/dgl/kernel.py backward_fused_gat -> kernel._CAPI_DGLKernelBackwardFusedGat."""
+    t = [_nd(x) for x in (feat_src, el, er, s, exp, ret, grad_out, grad_feat_src, grad_el,
+                          grad_er)]
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelBackwardFusedGat(G.handle, *[x.ptr for x in t],
+                                                     float(slope), _stream(G)))
+
+
 def copy_reduce_mean(G, target, X, out):
     """Extension (no reference PackedFunc): copy + mean in one pass, see
     DGLB200KernelCopyReduceMean in include/dgl_b200.h."""

@@ -184,6 +184,27 @@ int DGLB200KernelBackwardCopyReduce(const char* reducer, DGLB200GraphHandle grap
                                     const DGLB200Tensor* in_mapping,
                                     const DGLB200Tensor* out_mapping, void* stream);
 
+/* kernel._CAPI_DGLFusedGatKernel(graph, feat_src, el, er, sum, exp, ret, slope)
+ * (src/kernel/binary_reduce.cc:380-396; kernels src/kernel/cuda/binary_reduce_impl.cu:51-113,
+ * 359-422). feat_src [N,H,F], el/er [N,H,1] (any shape with H elements per row), outputs
+ * sum [N,H,1], exp [E,H,1] (indexed by edge id), ret [N,H,F]:
+ *   exp = v > 0 ? e^v : e^(slope v), v = el[src] + er[dst];  sum = sum over in-edges;
+ *   ret = sum over in-edges of (exp / sum) * feat_src[src]   (no max-subtraction, as the reference). */
+int DGLB200FusedGatKernel(DGLB200GraphHandle graph, const DGLB200Tensor* feat_src,
+                          const DGLB200Tensor* el, const DGLB200Tensor* er, DGLB200Tensor* sum,
+                          DGLB200Tensor* exp, DGLB200Tensor* ret, float slope, void* stream);
+
+/* kernel._CAPI_DGLKernelBackwardFusedGat(graph, feat_src, el, er, sum, exp, ret, grad_out,
+ *   grad_feat_src, grad_el, grad_er, slope)  (binary_reduce.cc:529-549; kernels
+ * binary_reduce_impl.cu:123-213, 1248-1308). The three gradients are fully overwritten
+ * (the reference accumulates with atomics into zero-filled buffers; same values). */
+int DGLB200KernelBackwardFusedGat(DGLB200GraphHandle graph, const DGLB200Tensor* feat_src,
+                                  const DGLB200Tensor* el, const DGLB200Tensor* er,
+                                  const DGLB200Tensor* sum, const DGLB200Tensor* exp,
+                                  const DGLB200Tensor* ret, const DGLB200Tensor* grad_out,
+                                  DGLB200Tensor* grad_feat_src, DGLB200Tensor* grad_el,
+                                  DGLB200Tensor* grad_er, float slope, void* stream);
+
 /* ---- extensions (no reference PackedFunc; they replace multi-call sequences the reference's
  *      torch backend performs around the kernels) ---- */
 

@@ -290,3 +290,74 @@ void orc_backward_binary_reduce(int mode, int red, int op, int lhs_tgt, int rhs_
     }
   }
 }
+
+/* ---------------------------------------------------------------- fused GAT (hack ops)
+ * CPU restatement of the fork's CUDA-only kernels. PARITY: pinned only through the builtin
+ * composition the reference itself checks against (examples/pytorch/gat/fused_gat_unit_test.py:
+ * 36-52: u_add_v -> leaky_relu -> exp -> copy_e+sum -> e_div_v -> u_mul_e+sum, no
+ * max-subtraction); the reference kernels cannot run without a GPU build. */
+#include <math.h>
+
+static float gat_leaky_exp(float v, float slope) {
+  /* gatLeakyReluExp, src/kernel/cuda/binary_reduce_impl.cu:46-49 */
+  return v > 0 ? expf(v) : expf(slope * v);
+}
+
+/* gatExpLeakyReluSumKernel + gatSumProdZipDivKernel (binary_reduce_impl.cu:51-113) over the
+ * in-CSR (row = dst). exp is indexed by edge id. */
+void orc_fused_gat_forward(idx_t n_dst, const idx_t* indptr, const idx_t* indices,
+                           const idx_t* eids, int64_t H, int64_t F, const float* ft,
+                           const float* el, const float* er, float slope, float* sum,
+                           float* exp_out, float* ret) {
+  idx_t v, p;
+  int64_t h, f;
+  for (v = 0; v < n_dst; ++v) {
+    for (h = 0; h < H; ++h) {
+      float s = 0.f;
+      for (p = indptr[v]; p < indptr[v + 1]; ++p) {
+        float t = gat_leaky_exp(el[indices[p] * H + h] + er[v * H + h], slope);
+        exp_out[eids[p] * H + h] = t;
+        s += t;
+      }
+      sum[v * H + h] = s;
+    }
+    for (h = 0; h < H; ++h)
+      for (f = 0; f < F; ++f) {
+        float s = 0.f;
+        for (p = indptr[v]; p < indptr[v + 1]; ++p)
+          s += exp_out[eids[p] * H + h] / sum[v * H + h] * ft[(indices[p] * H + h) * F + f];
+        ret[(v * H + h) * F + f] = s;
+      }
+  }
+}
+
+/* fusedGatBackwardGradFeatSrc + fusedGatBackwardGradElEr (binary_reduce_impl.cu:123-213) over the
+ * out-CSR (row = src). grad_el / grad_er are zero-filled here (the torch side passes zeros). */
+void orc_fused_gat_backward(idx_t n_src, idx_t n_dst, const idx_t* indptr, const idx_t* indices,
+                            const idx_t* eids, int64_t H, int64_t F, const float* ft,
+                            const float* el, const float* er, const float* sum,
+                            const float* exp_in, const float* ret, const float* gout, float slope,
+                            float* grad_ft, float* grad_el, float* grad_er) {
+  idx_t u, p;
+  int64_t h, f, i;
+  for (i = 0; i < n_src * H; ++i) grad_el[i] = 0.f;
+  for (i = 0; i < n_dst * H; ++i) grad_er[i] = 0.f;
+  for (u = 0; u < n_src; ++u)
+    for (h = 0; h < H; ++h)
+      for (f = 0; f < F; ++f) {
+        float s = 0.f, s2 = 0.f;
+        for (p = indptr[u]; p < indptr[u + 1]; ++p) {
+          idx_t d = indices[p], e = eids[p];
+          float grad_exp, tmp_sum, tmp2;
+          s += exp_in[e * H + h] / sum[d * H + h] * gout[(d * H + h) * F + f];
+          grad_exp = gout[(d * H + h) * F + f] *
+                     (ft[(u * H + h) * F + f] - ret[(d * H + h) * F + f]) / sum[d * H + h];
+          tmp_sum = el[u * H + h] + er[d * H + h];
+          tmp2 = grad_exp * exp_in[e * H + h] * (tmp_sum > 0 ? 1.f : slope);
+          s2 += tmp2;
+          grad_er[d * H + h] += tmp2;
+        }
+        grad_ft[(u * H + h) * F + f] = s;
+        grad_el[u * H + h] += s2;
+      }
+}

@@ -31,7 +31,7 @@ def build(force=False):
     """Compile the C restatement with gcc (seconds)."""
     if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(_SRC):
         subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-std=c99",
-                               "-fno-fast-math", "-ffp-contract=off", "-o", _SO, _SRC])
+                               "-fno-fast-math", "-ffp-contract=off", "-o", _SO, _SRC, "-lm"])
     return _SO
 
 
@@ -307,3 +307,34 @@ def reduce_grad(grad, shape):
     pad = (1,) * (len(grad_shape) - len(in_shape)) + in_shape
     axes = tuple(i + 1 for i, (a, b) in enumerate(zip(grad_shape, pad)) if a != b)
     return grad.sum(axis=axes, keepdims=True).reshape(shape)
+
+
+# ------------------------------------------------------------------ fused GAT (hack ops)
+def fused_gat_forward(g, ft, el, er, slope):
+    """FusedGatKernelImpl (src/kernel/cuda/binary_reduce_impl.cu:51-113, 359-422).
+    ft [N,H,F], el/er [N,H,1] -> (sum [N,H,1], exp [E,H,1], ret [N,H,F])."""
+    ft, el, er = _f32(ft), _f32(el), _f32(er)
+    H = int(np.prod(el.shape[1:]))
+    F = int(np.prod(ft.shape[1:])) // H
+    s = np.empty((g.num_dst,) + el.shape[1:], np.float32)
+    ex = np.empty((g.num_edges,) + el.shape[1:], np.float32)
+    ret = np.empty((g.num_dst,) + ft.shape[1:], np.float32)
+    ip, ix, ei = g.in_csr
+    lib().orc_fused_gat_forward(ctypes.c_int64(g.num_dst), _p(ip), _p(ix), _p(ei),
+                                ctypes.c_int64(H), ctypes.c_int64(F), _p(ft), _p(el), _p(er),
+                                ctypes.c_float(slope), _p(s), _p(ex), _p(ret))
+    return s, ex, ret
+
+
+def fused_gat_backward(g, ft, el, er, s, ex, ret, gout, slope):
+    """BackwardFusedGatKernelImpl (binary_reduce_impl.cu:123-213, 1248-1308)."""
+    ft, el, er, s, ex, ret, gout = [_f32(a) for a in (ft, el, er, s, ex, ret, gout)]
+    H = int(np.prod(el.shape[1:]))
+    F = int(np.prod(ft.shape[1:])) // H
+    gft, gel, ger = np.empty_like(ft), np.empty_like(el), np.empty_like(er)
+    ip, ix, ei = g.out_csr
+    lib().orc_fused_gat_backward(ctypes.c_int64(g.num_src), ctypes.c_int64(g.num_dst), _p(ip),
+                                 _p(ix), _p(ei), ctypes.c_int64(H), ctypes.c_int64(F), _p(ft),
+                                 _p(el), _p(er), _p(s), _p(ex), _p(ret), _p(gout),
+                                 ctypes.c_float(slope), _p(gft), _p(gel), _p(ger))
+    return gft, gel, ger
