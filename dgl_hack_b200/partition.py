@@ -1,0 +1,194 @@
+"""Destination-node partitioning with 1-hop halo exchange (multi-GPU message passing).
+
+Host-side logic of SURVEY 8(e), mirroring the reference's partitioning semantics
+(`dgl.transform.partition_graph_with_halo`, python/dgl/transform.py:551-640 ->
+GraphOp::GetSubgraphWithHalo, src/graph/graph_op.cc:403-509): rank r owns a set of destination
+nodes ("inner" nodes, `inner_node` mask) together with all their in-edges; the sources of those
+edges that live on other ranks are its 1-hop halo. Local ids: inner nodes first (ascending
+global id, as the reference's subgraphs preserve parent order), then halo nodes grouped by owner.
+
+The reference has no GPU collective at all (its multi-GPU story is DDP over sampled
+mini-batches); here each layer does ONE exchange of halo source rows over NCCL (grouped
+send/recv = all-to-all-v over NVLink/NVSwitch), overlapped with the aggregation over the edges
+whose sources are local:
+
+    forward :  post exchange(X_inner -> X_halo) | SpMM(inner-source edges)  ; wait ; SpMM(halo edges)
+    backward:  transposed SpMM(halo edges) ; post reverse exchange | transposed SpMM(inner edges) ;
+               wait ; add the received halo gradients into their owners' rows (fixed peer order)
+
+Everything here is torch + torch.distributed and device agnostic, so the exchange logic is tested
+on CPU with gloo (world_size 2); the aggregation itself is the CUDA kernel library.
+"""
+import torch
+import torch.distributed as dist
+
+
+def range_partition(num_nodes, dst, k):
+    """Contiguous node ranges balanced by in-edge count (the default when the node numbering has
+    community structure; METIS assignments from the reference's `metis_partition` can be passed to
+    `Partition.build` instead -- any node -> part vector works)."""
+    deg = torch.bincount(dst, minlength=num_nodes).to(torch.float64)
+    cum = torch.cumsum(deg + 1e-3, 0)  # +eps: isolated nodes still spread
+    bounds = cum[-1] * torch.arange(1, k, dtype=torch.float64, device=dst.device) / k
+    cuts = torch.searchsorted(cum, bounds)
+    part = torch.bucketize(torch.arange(num_nodes, device=dst.device), cuts, right=True)
+    return part
+
+
+class Partition(object):
+    """One rank's share of a graph: inner nodes, halo nodes, local COO split by source locality."""
+
+    def __init__(self):
+        self.rank = self.world = 0
+        self.inner_global = self.halo_global = None
+        self.halo_counts = self.send_idx = None
+        self.edges_inner = self.edges_halo = None  # (src_local, dst_local) pairs
+        self.n_inner = self.n_halo = 0
+        self.cut_edges = self.local_edges = 0
+
+    @classmethod
+    def build(cls, num_nodes, src, dst, part, rank, world):
+        """src/dst: global COO (int64, any device), part: owner of every node. Deterministic and
+        communication free: every rank derives its send lists from the same global COO."""
+        p = cls()
+        p.rank, p.world = rank, world
+        dev = src.device
+        part = part.to(dev)
+        own_dst = part[dst] == rank
+        e_src, e_dst = src[own_dst], dst[own_dst]
+        p.inner_global = torch.nonzero(part == rank).flatten()
+        p.n_inner = int(p.inner_global.numel())
+        g2l = torch.full((num_nodes,), -1, dtype=torch.int64, device=dev)
+        g2l[p.inner_global] = torch.arange(p.n_inner, device=dev)
+        remote = part[e_src] != rank
+        halo = torch.unique(e_src[remote])
+        owner = part[halo]
+        order = torch.argsort(owner * num_nodes + halo)
+        p.halo_global = halo[order]
+        p.n_halo = int(halo.numel())
+        p.halo_counts = torch.bincount(part[p.halo_global], minlength=world).tolist()
+        g2l[p.halo_global] = p.n_inner + torch.arange(p.n_halo, device=dev)
+        ls, ld = g2l[e_src], g2l[e_dst]
+        # edges keep their global order inside each class (edge id order = reduction order)
+        p.edges_inner = (ls[~remote], ld[~remote])
+        p.edges_halo = (ls[remote] - p.n_inner, ld[remote])
+        p.local_edges = int(e_src.numel())
+        p.cut_edges = int(remote.sum())
+        # what each peer needs from me: sources I own of edges whose destination the peer owns
+        mine_src = part[src] == rank
+        p.send_idx = []
+        for q in range(world):
+            if q == rank:
+                p.send_idx.append(torch.empty(0, dtype=torch.int64, device=dev))
+                continue
+            need = torch.unique(src[mine_src & (part[dst] == q)])  # ascending = peer's halo order
+            p.send_idx.append(g2l[need])
+        return p
+
+    # ---- exchanges (grouped isend/irecv: works on gloo and NCCL)
+    def start_forward_exchange(self, x_inner):
+        """Posts the halo exchange; returns (requests, x_halo, keepalive)."""
+        d = x_inner.shape[1:]
+        x_halo = x_inner.new_empty((self.n_halo,) + tuple(d))
+        ops, keep, off = [], [], 0
+        for q in range(self.world):
+            cnt = self.halo_counts[q]
+            if q != self.rank and cnt > 0:
+                ops.append(dist.P2POp(dist.irecv, x_halo[off:off + cnt], q))
+            off += cnt
+        for q in range(self.world):
+            if q != self.rank and self.send_idx[q].numel() > 0:
+                buf = x_inner.index_select(0, self.send_idx[q])
+                keep.append(buf)
+                ops.append(dist.P2POp(dist.isend, buf, q))
+        reqs = dist.batch_isend_irecv(ops) if ops else []
+        return reqs, x_halo, keep
+
+    def start_backward_exchange(self, g_halo):
+        """Sends halo gradients back to their owners; returns (requests, per-peer recv buffers)."""
+        d = g_halo.shape[1:]
+        ops, recv, off = [], [], 0
+        for q in range(self.world):
+            n = self.send_idx[q].numel()
+            buf = g_halo.new_empty((n,) + tuple(d)) if (q != self.rank and n > 0) else None
+            recv.append(buf)
+            if buf is not None:
+                ops.append(dist.P2POp(dist.irecv, buf, q))
+        for q in range(self.world):
+            cnt = self.halo_counts[q]
+            if q != self.rank and cnt > 0:
+                ops.append(dist.P2POp(dist.isend, g_halo[off:off + cnt].contiguous(), q))
+            off += cnt
+        reqs = dist.batch_isend_irecv(ops) if ops else []
+        return reqs, recv
+
+    def exchange_bytes(self, row_bytes):
+        sent = sum(int(s.numel()) for s in self.send_idx) * row_bytes
+        return {"send": sent, "recv": self.n_halo * row_bytes}
+
+
+class _HaloCopySum(torch.autograd.Function):
+    """out[v] = sum over in-edges of X[src] for the rank's inner destinations, sources local or
+    halo. `agg(which, x)` / `agg_t(which, grad_out)` are the aggregation and its transpose for
+    the inner-source ("inner") and halo-source ("halo") edge sets."""
+
+    @staticmethod
+    def forward(ctx, part, agg, agg_t, x_inner):
+        reqs, x_halo, keep = part.start_forward_exchange(x_inner)
+        out = agg("inner", x_inner)            # overlaps the exchange
+        for r in reqs:
+            r.wait()
+        if part.n_halo > 0:
+            out = out + agg("halo", x_halo)
+        ctx.part, ctx.agg_t = part, agg_t
+        del keep
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        part, agg_t = ctx.part, ctx.agg_t
+        grad_out = grad_out.contiguous()
+        g_halo = agg_t("halo", grad_out) if part.n_halo > 0 else \
+            grad_out.new_empty((0,) + tuple(grad_out.shape[1:]))
+        reqs, recv = part.start_backward_exchange(g_halo)
+        g_inner = agg_t("inner", grad_out)     # overlaps the exchange
+        for r in reqs:
+            r.wait()
+        for q in range(part.world):            # fixed peer order; ids unique within a peer
+            if recv[q] is not None:
+                g_inner.index_add_(0, part.send_idx[q], recv[q])
+        return None, None, None, g_inner
+
+
+class PartitionedGraph(object):
+    """A Partition bound to the CUDA kernels: two GraphIndex objects (inner-source and
+    halo-source edges, destinations = inner nodes) and the halo-exchanging aggregation."""
+
+    def __init__(self, part, device):
+        from .graph_index import GraphIndex
+        self.part = part
+        self.device = torch.device(device)
+        si, di = part.edges_inner
+        sh, dh = part.edges_halo
+        self.g_inner = GraphIndex.from_coo(part.n_inner, part.n_inner, si, di, device)
+        self.g_halo = GraphIndex.from_coo(max(part.n_halo, 1), part.n_inner, sh, dh, device)
+
+    def _agg(self, which, x):
+        from . import kernel as K
+        g = self.g_inner if which == "inner" else self.g_halo
+        out = x.new_empty((self.part.n_inner,) + tuple(x.shape[1:]))
+        K.copy_reduce("sum", g, 0, x.contiguous(), out)
+        return out
+
+    def _agg_t(self, which, grad_out):
+        from . import kernel as K
+        g = self.g_inner if which == "inner" else self.g_halo
+        n_src = self.part.n_inner if which == "inner" else self.part.n_halo
+        rows = max(n_src, 1) if which == "halo" else n_src
+        grad = grad_out.new_empty((rows,) + tuple(grad_out.shape[1:]))
+        K.backward_copy_reduce("sum", g, 0, grad, grad_out, grad_out, grad)
+        return grad[:n_src]
+
+    def copy_src_sum(self, x_inner):
+        """Halo-exchanging `update_all(copy_src, sum)` for this rank's inner nodes."""
+        return _HaloCopySum.apply(self.part, self._agg, self._agg_t, x_inner)

@@ -1,0 +1,196 @@
+"""Per-config kernel timings for BASELINE.json configs 1, 3, 4, 5 (config 2 is bench.py).
+
+    python profiles/bench_configs.py [--out gpurun_out/r1_configs.json] [--only c3,c5]
+
+Every op goes through the public API (dgl_hack_b200.backend / kernel); time = CUDA events around
+`reps` back-to-back calls after warm-up, on the current stream. Algorithmic bytes follow
+SURVEY.md 8(d). Synthetic graphs are generated on the device with fixed seeds.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+import dgl_hack_b200 as B  # noqa: E402
+from dgl_hack_b200 import backend as F  # noqa: E402
+from dgl_hack_b200 import kernel as K  # noqa: E402
+
+DEV = torch.device("cuda:0")
+PEAK, _ = bench.measured_peak()
+L2 = None
+
+
+def timeit(fn, reps=20, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+def gather_bytes(n_src, e, d):
+    s = n_src * d * 4
+    return e * d * 4 if s > L2 else s
+
+
+def rec(out, cfg, op, ms, e, nbytes, note=""):
+    row = {"config": cfg, "op": op, "ms": round(ms, 4), "gedges_per_s": round(e / ms / 1e6, 3),
+           "algorithmic_gb": round(nbytes / 1e9, 4), "gb_per_s": round(nbytes / ms / 1e6, 1),
+           "frac_of_measured_hbm": round(nbytes / ms / 1e6 / PEAK, 3), "kernel": K.last_kernel(),
+           "note": note}
+    out.append(row)
+    print(json.dumps(row), flush=True)
+
+
+def rand(*shape):
+    return torch.rand(*shape, device=DEV) * 2 - 1
+
+
+def c1(out):
+    n, e = 2708, 10556
+    gen = torch.Generator(device=DEV)
+    gen.manual_seed(1)
+    src = torch.randint(0, n, (e,), generator=gen, device=DEV)
+    dst = torch.randint(0, n, (e,), generator=gen, device=DEV)
+    g = B.GraphIndex.from_coo(n, n, src, dst, DEV)
+    for d in (16, 7):
+        x = rand(n, d)
+        ms = timeit(lambda: F.copy_reduce("sum", g, 0, x, n), reps=200)
+        rec(out, "C1 cora", "copy_src+sum D=%d" % d, ms, e,
+            gather_bytes(n, e, d) + e * 4 + n * d * 4 + (n + 1) * 4, "launch/latency bound")
+
+
+def c3(out):
+    n, e, H, Fw = 169343, 1166243, 8, 16
+    src, dst = bench.make_graph_coo(n, e, 0.4, 3, DEV)
+    g = B.GraphIndex.from_coo(n, n, src, dst, DEV)
+    ft, el, er = rand(n, H, Fw), rand(n, H, 1), rand(n, H, 1)
+    ee = rand(e, H, 1)
+    a = torch.rand(e, H, 1, device=DEV)
+    gout = rand(n, H, Fw)
+    ms = timeit(lambda: F.binary_reduce("none", "add", g, 0, 1, el, er, e))
+    rec(out, "C3 arxiv", "u_add_v SDDMM [N,8,1]", ms, e, e * 8 + 2 * n * H * 4 + e * H * 4)
+
+    def edge_softmax():
+        # nn/pytorch/softmax.py:69-78 : 4 kernel calls + exp
+        smax = F.copy_reduce("max", g, 2, ee, n)
+        o = F.binary_reduce("none", "sub", g, 2, 1, ee, smax, e)
+        o = torch.exp(o)
+        ssum = F.copy_reduce("sum", g, 2, o, n)
+        return F.binary_reduce("none", "div", g, 2, 1, o, ssum, e)
+    ms = timeit(edge_softmax)
+    rec(out, "C3 arxiv", "edge_softmax (reference 4-call form)", ms, e,
+        4 * (e * 8 + e * H * 4 * 2 + n * H * 4), "4 kernels + torch.exp")
+    ms = timeit(lambda: F.binary_reduce("sum", "mul", g, 0, 2, ft, a, n))
+    rec(out, "C3 arxiv", "u_mul_e+sum [N,8,16]x[E,8,1]", ms, e,
+        gather_bytes(n, e, H * Fw) + e * 8 + e * H * 4 + n * H * Fw * 4)
+    ms = timeit(lambda: F.fused_gat(g, ft, el, er, 0.2))
+    rec(out, "C3 arxiv", "fused GAT forward (u_add_v+leaky+exp+sum+div+u_mul_e)", ms, e,
+        gather_bytes(n, e, H * Fw) + e * 8 + e * H * 4 + n * H * Fw * 4 + 3 * n * H * 4,
+        "one kernel")
+    ftg, elg, erg = [t.clone().requires_grad_(True) for t in (ft, el, er)]
+
+    def gat_fb():
+        o = F.fused_gat(g, ftg, elg, erg, 0.2)
+        o.backward(gout)
+        ftg.grad = elg.grad = erg.grad = None
+    ms = timeit(gat_fb)
+    rec(out, "C3 arxiv", "fused GAT fwd+bwd", ms, 2 * e,
+        2 * (gather_bytes(n, e, H * Fw) * 2 + e * 8 + e * H * 8 + n * H * Fw * 4), "3 kernels")
+
+
+def c4(out):
+    n, e, R, d = 1885136, 5668682, 133, 16
+    gen = torch.Generator(device=DEV)
+    gen.manual_seed(4)
+    src = torch.randint(0, n, (e,), generator=gen, device=DEV)
+    dst = torch.randint(0, n, (e,), generator=gen, device=DEV)
+    w = (torch.arange(1, R + 1, device=DEV, dtype=torch.float64)) ** -1.1
+    et = torch.multinomial(w, e, replacement=True, generator=gen)
+    x = rand(n, d)
+    graphs = []
+    for r in range(R):
+        m = et == r
+        graphs.append(B.GraphIndex.from_coo(n, n, src[m], dst[m], DEV))
+
+    def loop():
+        acc = None
+        for gr in graphs:
+            o = F.copy_reduce("sum", gr, 0, x, n)
+            acc = o if acc is None else acc + o
+        return acc
+    ms = timeit(loop, reps=3, warm=1)
+    rec(out, "C4 AM", "133 x copy_src+sum D=16 (per-relation loop, HeteroGraphConv style)", ms, e,
+        R * (n * d * 4 * 2) + e * 4, "one launch per relation + torch add")
+    g = B.GraphIndex.from_coo(n, n, src, dst, DEV)
+    msg = rand(e, d)
+    ms = timeit(lambda: F.copy_reduce("sum", g, 2, msg, n))
+    rec(out, "C4 AM", "copy_e+sum [E,16] (RelGraphConv message reduce)", ms, e,
+        e * d * 4 + e * 4 + n * d * 4 + (n + 1) * 4)
+
+
+def sbm_graph(n, e, blocks, p_in, alpha, seed):
+    gen = torch.Generator(device=DEV)
+    gen.manual_seed(seed)
+    bsz = n // blocks
+    sb = torch.randint(0, blocks, (e,), generator=gen, device=DEV)
+    same = torch.rand(e, generator=gen, device=DEV) < p_in
+    db = torch.where(same, sb, torch.randint(0, blocks, (e,), generator=gen, device=DEV))
+
+    def within(_):
+        u = torch.rand(e, generator=gen, device=DEV, dtype=torch.float64)
+        r = ((bsz ** (1.0 - alpha) - 1.0) * u + 1.0) ** (1.0 / (1.0 - alpha)) - 1.0
+        return r.floor().clamp_(0, bsz - 1).to(torch.int64)
+    perm = torch.randperm(bsz, generator=gen, device=DEV)
+    src = sb * bsz + perm[within(0)]
+    dst = db * bsz + perm[within(1)]
+    return src, dst
+
+
+def c5(out):
+    n, e = 2449029, 61859140
+    src, dst = sbm_graph(n, e, 64, 0.85, 0.5, 5)
+    g = B.GraphIndex.from_coo(n, n, src, dst, DEV)
+    del src, dst
+    for d in (100, 256, 47):
+        x = rand(n, d).requires_grad_(True)
+        gout = rand(n, d)
+        ms = timeit(lambda: F.copy_reduce("sum", g, 0, x.detach(), n), reps=10, warm=3)
+        nb = gather_bytes(n, e, d) + e * 4 + n * d * 4 + (n + 1) * 4
+        rec(out, "C5 products", "copy_src+sum fwd D=%d" % d, ms, e, nb)
+
+        def fb():
+            o = F.copy_reduce("sum", g, 0, x, n)
+            o.backward(gout)
+            x.grad = None
+        ms = timeit(fb, reps=10, warm=3)
+        rec(out, "C5 products", "copy_src+sum fwd+bwd D=%d" % d, ms, 2 * e, 2 * nb)
+
+
+def main():
+    global L2
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "r1_configs.json"))
+    ap.add_argument("--only", default="c1,c3,c4,c5")
+    args = ap.parse_args()
+    L2 = torch.cuda.get_device_properties(DEV).L2_cache_size
+    out = []
+    for name in args.only.split(","):
+        {"c1": c1, "c3": c3, "c4": c4, "c5": c5}[name](out)
+        torch.cuda.empty_cache()
+    os.makedirs(os.path.dirname(args.out), exist_ok=True)
+    json.dump(out, open(args.out, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
