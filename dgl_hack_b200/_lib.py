@@ -83,6 +83,17 @@ SYMBOLS = {
                                          TensorP, _c.c_float, _c.c_void_p]),
     "DGLB200KernelBackwardFusedGat": (_c.c_int, [GraphHandle] + [TensorP] * 10 +
                                       [_c.c_float, _c.c_void_p]),
+    "DGLB200GraphSetEdgeTypes": (_c.c_int, [GraphHandle, _c.c_void_p, _c.c_int, _c.c_int64,
+                                            _c.c_void_p]),
+    "DGLB200GraphCopyCsrSortedByEdgeType": (_c.c_int, [GraphHandle, _c.c_int, _c.c_void_p,
+                                                       _c.c_void_p, _c.c_void_p, _c.c_void_p,
+                                                       _c.c_void_p]),
+    "DGLB200RgcnLayer0": (_c.c_int, [GraphHandle, TensorP, TensorP, TensorP, _c.c_void_p]),
+    "DGLB200RgcnLayer0Backward": (_c.c_int, [GraphHandle, TensorP, TensorP, TensorP, _c.c_int,
+                                             _c.c_void_p]),
+    "DGLB200RgcnLayer1": (_c.c_int, [GraphHandle, TensorP, TensorP, TensorP, TensorP,
+                                     _c.c_void_p]),
+    "DGLB200RgcnLayer1Backward": (_c.c_int, [GraphHandle] + [TensorP] * 6 + [_c.c_void_p]),
     "DGLB200KernelCopyReduceMean": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP,
                                                _c.c_void_p]),
     "DGLB200KernelBackwardCopyReduce": (_c.c_int, [_c.c_char_p, GraphHandle, _c.c_int, TensorP,

@@ -172,3 +172,54 @@ def fused_gat(graph, feat_src, el, er, slope):
     s = th.empty_like(er)
     ret = feat_src.new_empty((graph.num_dst,) + tuple(feat_src.shape[1:]))
     return FusedGat.apply(graph, feat_src, el, er, s, exp, ret, slope)
+
+
+class RgcnFirstLayer(th.autograd.Function):
+    """tensor.py:440-460 RgcnFirstLayer: one-hot input, weight [R, N, out] acts as an embedding."""
+
+    @staticmethod
+    def forward(ctx, graph, weight, norm, ret):
+        ctx.backward_cache = graph, weight.size(), norm
+        K.rgcn_layer0(graph, weight, norm, ret)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        graph, weight_size, norm = ctx.backward_cache
+        grad_weight = th.zeros(weight_size, dtype=norm.dtype, device=norm.device)
+        K.rgcn_layer0_backward(graph, gradout.contiguous(), norm, grad_weight)
+        return None, grad_weight, None, None
+
+
+def rgcn_layer0(graph, weight, norm):
+    """tensor.py:462-465 rgcn_layer0; `graph` is a typed GraphIndex."""
+    weight, norm = weight.contiguous(), norm.contiguous()
+    ret = weight.new_empty((graph.num_dst, weight.size(2)))
+    return RgcnFirstLayer.apply(graph, weight, norm, ret)
+
+
+class RgcnSecondLayer(th.autograd.Function):
+    """tensor.py:467-490 RgcnSecondLayer. The reference's backward computes grad_weight and then
+    returns None for it (tensor.py:490), so the relation weights never train; here it is
+    returned."""
+
+    @staticmethod
+    def forward(ctx, graph, x, weight, norm, ret):
+        ctx.backward_cache = graph, weight, norm, x
+        K.rgcn_layer1(graph, x, weight, norm, ret)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        graph, weight, norm, x = ctx.backward_cache
+        grad_x = th.empty_like(x)
+        grad_weight = th.empty_like(weight)
+        K.rgcn_layer1_backward(graph, x, weight, norm, gradout.contiguous(), grad_x, grad_weight)
+        return None, grad_x, grad_weight, None, None
+
+
+def rgcn_layer1(graph, x, weight, norm):
+    """tensor.py:492-495 rgcn_layer1."""
+    x, weight, norm = x.contiguous(), weight.contiguous(), norm.contiguous()
+    ret = weight.new_empty((graph.num_dst, weight.size(2)))
+    return RgcnSecondLayer.apply(graph, x, weight, norm, ret)

@@ -685,4 +685,113 @@ int DGLB200KernelBackwardFusedGat(DGLB200GraphHandle graph, const DGLB200Tensor*
   API_END();
 }
 
+// ---- RGCN hack layers (src/kernel/binary_reduce.cc:412-450)
+static int64_t numel(const DGLB200Tensor* t) {
+  int64_t n = 1;
+  for (int i = 0; i < t->ndim; ++i) n *= t->shape[i];
+  return n;
+}
+
+static void rgcn_common(DGLB200GraphHandle g, std::initializer_list<const DGLB200Tensor*> ts,
+                        const DGLB200Tensor* norm) {
+  for (const DGLB200Tensor* t : ts) {
+    B200_CHECK(t != nullptr, "NULL argument");
+    check_float(t, "rgcn tensor");
+  }
+  B200_CHECK(g->num_src == g->num_dst, "rgcn layers need a homogeneous graph (num_src == num_dst)");
+  B200_CHECK(numel(norm) >= g->num_edges, "rgcn: norm must hold one value per edge");
+}
+
+int DGLB200RgcnLayer0(DGLB200GraphHandle graph, const DGLB200Tensor* weight,
+                      const DGLB200Tensor* norm, DGLB200Tensor* ret, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && weight && norm && ret, "NULL argument");
+  check_ctx(graph, {weight, norm, ret}, {"weight", "norm", "ret"});
+  rgcn_common(graph, {weight, norm, ret}, norm);
+  B200_CHECK(weight->ndim == 3, "rgcn layer 0: weight must be [num_rels, num_nodes, out]");
+  B200_CHECK(weight->shape[0] >= graph->ty.num_types && weight->shape[1] >= graph->num_src,
+             "rgcn layer 0: weight is smaller than [num_rels, num_nodes, out]");
+  B200_CHECK(ret->ndim == 2 && ret->shape[0] >= graph->num_dst && ret->shape[1] == weight->shape[2],
+             "rgcn layer 0: ret must be [num_nodes, out]");
+  B200_CUDA(cudaSetDevice(graph->device));
+  rgcn_layer0_forward(graph, data_ptr<const float>(weight), data_ptr<const float>(norm),
+                      data_ptr<float>(ret), weight->shape[1], weight->shape[2],
+                      static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200RgcnLayer0Backward(DGLB200GraphHandle graph, const DGLB200Tensor* grad_out,
+                              const DGLB200Tensor* norm, DGLB200Tensor* grad_weight,
+                              int accumulate, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && grad_out && norm && grad_weight, "NULL argument");
+  check_ctx(graph, {grad_out, norm, grad_weight}, {"grad_out", "norm", "grad_weight"});
+  rgcn_common(graph, {grad_out, norm, grad_weight}, norm);
+  B200_CHECK(grad_weight->ndim == 3, "rgcn layer 0: grad_weight must be [num_rels, num_nodes, out]");
+  B200_CHECK(grad_weight->shape[0] >= graph->ty.num_types &&
+                 grad_weight->shape[1] >= graph->num_src,
+             "rgcn layer 0: grad_weight is smaller than [num_rels, num_nodes, out]");
+  B200_CHECK(grad_out->ndim == 2 && grad_out->shape[0] >= graph->num_dst &&
+                 grad_out->shape[1] == grad_weight->shape[2],
+             "rgcn layer 0: grad_out must be [num_nodes, out]");
+  B200_CUDA(cudaSetDevice(graph->device));
+  rgcn_layer0_backward(graph, data_ptr<const float>(grad_out), data_ptr<const float>(norm),
+                       data_ptr<float>(grad_weight), grad_weight->shape[1], grad_weight->shape[2],
+                       accumulate != 0, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200RgcnLayer1(DGLB200GraphHandle graph, const DGLB200Tensor* hidden,
+                      const DGLB200Tensor* weight, const DGLB200Tensor* norm, DGLB200Tensor* ret,
+                      void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && hidden && weight && norm && ret, "NULL argument");
+  check_ctx(graph, {hidden, weight, norm, ret}, {"hidden", "weight", "norm", "ret"});
+  rgcn_common(graph, {hidden, weight, norm, ret}, norm);
+  B200_CHECK(weight->ndim == 3 && weight->shape[0] >= graph->ty.num_types,
+             "rgcn layer 1: weight must be [num_rels, in, out]");
+  B200_CHECK(hidden->ndim == 2 && hidden->shape[0] >= graph->num_src &&
+                 hidden->shape[1] == weight->shape[1],
+             "rgcn layer 1: hidden must be [num_nodes, in]");
+  B200_CHECK(ret->ndim == 2 && ret->shape[0] >= graph->num_dst && ret->shape[1] == weight->shape[2],
+             "rgcn layer 1: ret must be [num_nodes, out]");
+  B200_CUDA(cudaSetDevice(graph->device));
+  rgcn_layer1_forward(graph, data_ptr<const float>(hidden), data_ptr<const float>(weight),
+                      data_ptr<const float>(norm), data_ptr<float>(ret), weight->shape[1],
+                      weight->shape[2], static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200RgcnLayer1Backward(DGLB200GraphHandle graph, const DGLB200Tensor* hidden,
+                              const DGLB200Tensor* weight, const DGLB200Tensor* norm,
+                              const DGLB200Tensor* grad_out, DGLB200Tensor* grad_hidden,
+                              DGLB200Tensor* grad_weight, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && hidden && weight && norm && grad_out && grad_hidden && grad_weight,
+             "NULL argument");
+  check_ctx(graph, {hidden, weight, norm, grad_out, grad_hidden, grad_weight},
+            {"hidden", "weight", "norm", "grad_out", "grad_hidden", "grad_weight"});
+  rgcn_common(graph, {hidden, weight, norm, grad_out, grad_hidden, grad_weight}, norm);
+  B200_CHECK(weight->ndim == 3 && weight->shape[0] == graph->ty.num_types,
+             "rgcn layer 1 backward: weight must be [num_rels, in, out] with num_rels equal to the "
+             "graph's number of edge types");
+  B200_CHECK(grad_weight->ndim == 3 && grad_weight->shape[0] == weight->shape[0] &&
+                 grad_weight->shape[1] == weight->shape[1] &&
+                 grad_weight->shape[2] == weight->shape[2],
+             "rgcn layer 1 backward: grad_weight must have the shape of weight");
+  B200_CHECK(hidden->ndim == 2 && hidden->shape[0] >= graph->num_src &&
+                 hidden->shape[1] == weight->shape[1] && grad_hidden->ndim == 2 &&
+                 grad_hidden->shape[0] >= graph->num_src && grad_hidden->shape[1] == weight->shape[1],
+             "rgcn layer 1 backward: hidden / grad_hidden must be [num_nodes, in]");
+  B200_CHECK(grad_out->ndim == 2 && grad_out->shape[0] >= graph->num_dst &&
+                 grad_out->shape[1] == weight->shape[2],
+             "rgcn layer 1 backward: grad_out must be [num_nodes, out]");
+  B200_CUDA(cudaSetDevice(graph->device));
+  rgcn_layer1_backward(graph, data_ptr<const float>(hidden), data_ptr<const float>(weight),
+                       data_ptr<const float>(norm), data_ptr<const float>(grad_out),
+                       data_ptr<float>(grad_hidden), data_ptr<float>(grad_weight),
+                       weight->shape[1], weight->shape[2], static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
 }  // extern "C"

@@ -184,6 +184,21 @@ struct SegPlan {
   const int32_t* sched;  // row order for the non-segment work items (may be NULL)
 };
 
+// Typed adjacency (Graph::GetCsrSortedByEdgeType, src/graph/graph.cc:690-741): every row of the
+// in-/out-CSR re-ordered by (edge type, edge id); indptr is shared with the untyped CSR.
+struct TypedCsr {
+  int32_t* ids = nullptr;    // [E] other endpoint
+  int32_t* eids = nullptr;   // [E]
+  int32_t* types = nullptr;  // [E]
+};
+struct TypeIndex {
+  int64_t num_types = 0;      // 0 = no edge types attached
+  TypedCsr in, out;
+  // type-major edge list (type, edge id): the contraction order of the weight gradients
+  int32_t *bt_src = nullptr, *bt_dst = nullptr, *bt_eid = nullptr;
+  int32_t* type_ptr = nullptr;  // [num_types + 1]
+};
+
 }  // namespace b200
 
 struct DGLB200Graph {
@@ -197,6 +212,7 @@ struct DGLB200Graph {
   // reference's floating-point sums bit for bit; ascending sources also gather with better
   // locality. indptr / row / heavy_first alias `in` (same degrees); to_other -> out-CSR position.
   b200::Csr in_s;
+  b200::TypeIndex ty;
 };
 
 namespace b200 {
@@ -238,6 +254,16 @@ void fused_gat_backward(DGLB200Graph* g, const float* ft, const float* el, const
                         const float* sum, const float* exp, const float* ret, const float* gout,
                         float* grad_ft, float* grad_el, float* grad_er, int64_t H, int64_t F,
                         float slope, cudaStream_t s);
+// rgcn.cu
+void rgcn_layer0_forward(DGLB200Graph* g, const float* w, const float* norm, float* ret,
+                         int64_t n_rows_w, int64_t feat, cudaStream_t s);
+void rgcn_layer0_backward(DGLB200Graph* g, const float* gout, const float* norm, float* grad_w,
+                          int64_t n_rows_w, int64_t feat, bool accumulate, cudaStream_t s);
+void rgcn_layer1_forward(DGLB200Graph* g, const float* h, const float* w, const float* norm,
+                         float* ret, int64_t fy, int64_t fx, cudaStream_t s);
+void rgcn_layer1_backward(DGLB200Graph* g, const float* h, const float* w, const float* norm,
+                          const float* gout, float* grad_h, float* grad_w, int64_t fy, int64_t fx,
+                          cudaStream_t s);
 bool try_spmm(const KernelCall& c);  // returns false if the call is not an SpMM-shaped case
 bool try_sddmm(const KernelCall& c);
 

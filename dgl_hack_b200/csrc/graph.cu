@@ -541,6 +541,94 @@ static void build_in_sorted(DGLB200Graph* g, cudaStream_t s) {
                     c.indices, c.eids, nullptr, c.to_other, s);
 }
 
+// ---------------------------------------------------------------- typed adjacency
+__global__ void scatter_coo_kernel(const int32_t* __restrict__ row, const int32_t* __restrict__ col,
+                                   const int32_t* __restrict__ eid, int64_t n,
+                                   int32_t* __restrict__ row_of, int32_t* __restrict__ col_of) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t e = eid[i];
+    row_of[e] = row[i];
+    col_of[e] = col[i];
+  }
+}
+
+__global__ void check_range_kernel(const int32_t* __restrict__ v, int64_t n, int32_t hi,
+                                   int32_t* __restrict__ bad) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    if (v[i] < 0 || v[i] >= hi) atomicOr(bad, 1);
+}
+
+static void free_typed(TypeIndex& t) {
+  cudaFree(t.in.ids);
+  cudaFree(t.in.eids);
+  cudaFree(t.in.types);
+  cudaFree(t.out.ids);
+  cudaFree(t.out.eids);
+  cudaFree(t.out.types);
+  cudaFree(t.bt_src);
+  cudaFree(t.bt_dst);
+  cudaFree(t.bt_eid);
+  cudaFree(t.type_ptr);
+  t = TypeIndex();
+}
+
+// et: device int32 [E], type of every edge id. Orders: the reference sorts each adjacency row by
+// type with std::sort (graph.cc:727-733), which leaves the order inside one type unspecified;
+// here it is (type, edge id), i.e. the stable version of the same sort.
+static void build_typed(DGLB200Graph* g, const int32_t* et, int64_t num_types, cudaStream_t s) {
+  const int64_t e = g->num_edges;
+  const size_t eb = (size_t)std::max<int64_t>(e, 1) * 4;
+  TypeIndex& t = g->ty;
+  free_typed(t);
+  int32_t** arrays[] = {&t.in.ids, &t.in.eids, &t.in.types, &t.out.ids, &t.out.eids,
+                        &t.out.types, &t.bt_src, &t.bt_dst, &t.bt_eid};
+  for (auto a : arrays) B200_CUDA(cudaMalloc(a, eb));
+  B200_CUDA(cudaMalloc(&t.type_ptr, (size_t)(num_types + 1) * 4));
+  t.num_types = num_types;
+  fill_i32(t.type_ptr, num_types + 1, 0, s);
+  if (e == 0) return;
+  const int blocks = (int)std::min<int64_t>((e + 255) / 256, 148 * 16);
+  {
+    Scratch bad(4, s);
+    fill_i32(bad.as<int32_t>(), 1, 0, s);
+    check_range_kernel<<<blocks, 256, 0, s>>>(et, e, (int32_t)num_types, bad.as<int32_t>());
+    note_kernel(nullptr, 1);
+    int32_t h = 0;
+    B200_CUDA(cudaMemcpyAsync(&h, bad.ptr, 4, cudaMemcpyDeviceToHost, s));
+    B200_CUDA(cudaStreamSynchronize(s));
+    B200_CHECK(h == 0, "edge type id out of range [0, num_types)");
+  }
+  // endpoints by edge id
+  Scratch src_of(eb, s), dst_of(eb, s);
+  const int32_t* in_row = csr_rows(g, kWalkIn, s);
+  scatter_coo_kernel<<<blocks, 256, 0, s>>>(in_row, g->in.indices, g->in.eids, e,
+                                            dst_of.as<int32_t>(), src_of.as<int32_t>());
+  note_kernel(nullptr, 1);
+  // type-major list: stable sort of edge ids by type
+  count_keys_kernel<<<blocks, 256, 0, s>>>(et, e, t.type_ptr);
+  note_kernel(nullptr, 1);
+  exclusive_scan_i32(t.type_ptr, num_types + 1, s);
+  Scratch ka(eb, s), kb(eb, s), va(eb, s), vb(eb, s), bt_type(eb, s), perm(eb, s),
+      ip((size_t)(std::max(g->num_src, g->num_dst) + 1) * 4, s);
+  B200_CUDA(cudaMemcpyAsync(ka.ptr, et, eb, cudaMemcpyDeviceToDevice, s));
+  int32_t *sk, *sv;
+  radix_sort_pairs(ka.as<int32_t>(), kb.as<int32_t>(), nullptr, va.as<int32_t>(),
+                   vb.as<int32_t>(), e, num_types, &sk, &sv, s);
+  B200_CUDA(cudaMemcpyAsync(t.bt_eid, sv, eb, cudaMemcpyDeviceToDevice, s));
+  B200_CUDA(cudaMemcpyAsync(bt_type.ptr, sk, eb, cudaMemcpyDeviceToDevice, s));
+  gather_i32(src_of.as<int32_t>(), t.bt_eid, t.bt_src, e, s);
+  gather_i32(dst_of.as<int32_t>(), t.bt_eid, t.bt_dst, e, s);
+  // rows: stable sort of the type-major list by destination (in) / source (out)
+  coo_to_csr_device(g->num_dst, e, t.bt_dst, t.bt_src, t.bt_eid, ip.as<int32_t>(), t.in.ids,
+                    t.in.eids, nullptr, perm.as<int32_t>(), s);
+  gather_i32(bt_type.as<int32_t>(), perm.as<int32_t>(), t.in.types, e, s);
+  coo_to_csr_device(g->num_src, e, t.bt_src, t.bt_dst, t.bt_eid, ip.as<int32_t>(), t.out.ids,
+                    t.out.eids, nullptr, perm.as<int32_t>(), s);
+  gather_i32(bt_type.as<int32_t>(), perm.as<int32_t>(), t.out.types, e, s);
+}
+
 static bool is_device_ptr(const void* p) {
   cudaPointerAttributes a;
   cudaError_t e = cudaPointerGetAttributes(&a, p);
@@ -684,6 +772,7 @@ int DGLB200GraphFree(DGLB200GraphHandle g) {
   if (g) {
     cudaSetDevice(g->device);
     cudaDeviceSynchronize();
+    free_typed(g->ty);
     g->in_s.indptr = nullptr;
     free_csr(g->in_s);
     free_csr(g->in);
@@ -732,6 +821,56 @@ int DGLB200GraphCopyCSR(DGLB200GraphHandle g, int transpose, int32_t* indptr, in
   copy(indptr, c.indptr, c.n_rows + 1);
   copy(indices, c.indices, g->num_edges);
   copy(eids, c.eids, g->num_edges);
+  if (host) B200_CUDA(cudaStreamSynchronize(s));
+  API_END();
+}
+
+// graph.add_edges_with_type (python/dgl/graph.py, Graph::AddEdgesWithType graph.cc:140-165) +
+// Graph::GetCsrSortedByEdgeType (graph.cc:690-741): attaches a type to every edge id and builds
+// both typed adjacencies on the device.
+int DGLB200GraphSetEdgeTypes(DGLB200GraphHandle g, const void* etypes, int idx_bits,
+                             int64_t num_types, void* stream) {
+  API_BEGIN();
+  B200_CHECK(g, "NULL graph");
+  B200_CHECK(idx_bits == 32 || idx_bits == 64, "idx_bits must be 32 or 64");
+  B200_CHECK(num_types > 0 && num_types < (1ll << 31) - 1, "num_types out of range");
+  B200_CHECK(g->num_edges == 0 || etypes, "etypes is NULL");
+  ensure_device(g->device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  Scratch et((size_t)std::max<int64_t>(g->num_edges, 1) * 4, s);
+  upload_idx(etypes, idx_bits, g->num_edges, et.as<int32_t>(), s);
+  try {
+    build_typed(g, et.as<int32_t>(), num_types, s);
+  } catch (...) {
+    free_typed(g->ty);
+    throw;
+  }
+  B200_CUDA(cudaStreamSynchronize(s));
+  API_END();
+}
+
+int DGLB200GraphCopyCsrSortedByEdgeType(DGLB200GraphHandle g, int transpose, int32_t* indptr,
+                                        int32_t* ids, int32_t* eids, int32_t* types,
+                                        void* stream) {
+  API_BEGIN();
+  B200_CHECK(g, "NULL graph");
+  B200_CHECK(g->ty.num_types > 0, "graph has no edge types (call DGLB200GraphSetEdgeTypes)");
+  ensure_device(g->device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const Csr& c = transpose ? g->out : g->in;
+  const TypedCsr& t = transpose ? g->ty.out : g->ty.in;
+  bool host = false;
+  auto copy = [&](int32_t* dst, const int32_t* src, int64_t n) {
+    if (!dst || n <= 0) return;
+    const bool dev = is_device_ptr(dst);
+    host = host || !dev;
+    B200_CUDA(cudaMemcpyAsync(dst, src, (size_t)n * 4,
+                              dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+  };
+  copy(indptr, c.indptr, c.n_rows + 1);
+  copy(ids, t.ids, g->num_edges);
+  copy(eids, t.eids, g->num_edges);
+  copy(types, t.types, g->num_edges);
   if (host) B200_CUDA(cudaStreamSynchronize(s));
   API_END();
 }

@@ -70,6 +70,44 @@ class GraphIndex(object):
                 ctypes.byref(handle)))
         return cls(handle, device)
 
+    @classmethod
+    def from_coo_with_type(cls, num_nodes, src, dst, etypes, num_types=None, device="cuda:0"):
+        """DGLGraph.add_edges_with_type(src, dst, etypes) (the fork's typed multigraph,
+        Graph::AddEdgesWithType src/graph/graph.cc:140-165) as an immutable device index."""
+        g = cls.from_coo(num_nodes, num_nodes, src, dst, device)
+        g.set_edge_types(etypes, num_types)
+        return g
+
+    def set_edge_types(self, etypes, num_types=None):
+        """Attaches a relation id to every edge id and builds the typed adjacencies
+        (Graph::GetCsrSortedByEdgeType, graph.cc:690-741) on the device."""
+        et = torch.as_tensor(etypes)
+        if et.dtype not in (torch.int32, torch.int64):
+            et = et.to(torch.int64)
+        et = et.contiguous()
+        if et.dim() != 1 or et.shape[0] != self._num_edges:
+            raise _lib.DGLError("etypes must hold one type id per edge")
+        if num_types is None:
+            num_types = int(et.max().item()) + 1 if et.numel() else 1
+        with torch.cuda.device(self.device):
+            check_call(LIB.DGLB200GraphSetEdgeTypes(
+                self._handle, ctypes.c_void_p(et.data_ptr()), 64 if et.dtype == torch.int64 else 32,
+                int(num_types), _stream(self.device)))
+        self.num_types = int(num_types)
+
+    def get_csr_sorted_by_edge_type(self, transpose):
+        """[ranges, ids, eids, types] int32 CUDA tensors, as Graph::GetCsrSortedByEdgeType
+        (rows ordered by (type, edge id))."""
+        n_rows = self.num_src if transpose else self.num_dst
+        e = self._num_edges
+        out = [torch.empty((n,), dtype=torch.int32, device=self.device)
+               for n in (n_rows + 1, e, e, e)]
+        with torch.cuda.device(self.device):
+            check_call(LIB.DGLB200GraphCopyCsrSortedByEdgeType(
+                self._handle, int(transpose), *[ctypes.c_void_p(t.data_ptr()) for t in out],
+                _stream(self.device)))
+        return out
+
     def __del__(self):
         h, self._handle = getattr(self, "_handle", None), None
         if h:

@@ -111,6 +111,37 @@ def backward_fused_gat(G, feat_src, el, er, s, exp, ret, grad_out, grad_feat_src
                                                      float(slope), _stream(G)))
 
 
+def rgcn_layer0(G, weight, norm, ret):
+    """python/dgl/kernel.py rgcn_layer0 -> kernel._CAPI_DGLRgcnLayer0."""
+    weight, norm, ret = _nd(weight), _nd(norm), _nd(ret)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200RgcnLayer0(G.handle, weight.ptr, norm.ptr, ret.ptr, _stream(G)))
+
+
+def rgcn_layer0_backward(G, grad_out, norm, grad_weight, accumulate=True):
+    """python/dgl/kernel.py rgcn_layer0_backward -> kernel._CAPI_DGLRgcnLayer0Backward.
+    accumulate=False reproduces the reference kernel's plain store (last edge of a (type, src)
+    run wins, binary_reduce_impl.cu:1004); the default sums, which is the gradient."""
+    grad_out, norm, grad_weight = _nd(grad_out), _nd(norm), _nd(grad_weight)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200RgcnLayer0Backward(G.handle, grad_out.ptr, norm.ptr, grad_weight.ptr,
+                                                 int(bool(accumulate)), _stream(G)))
+
+
+def rgcn_layer1(G, hidden, weight, norm, ret):
+    """python/dgl/kernel.py rgcn_layer1 -> kernel._CAPI_DGLRgcnLayer1."""
+    t = [_nd(x) for x in (hidden, weight, norm, ret)]
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200RgcnLayer1(G.handle, *[x.ptr for x in t], _stream(G)))
+
+
+def rgcn_layer1_backward(G, hidden, weight, norm, grad_out, grad_hidden, grad_weight):
+    """python/dgl/kernel.py rgcn_layer1_backward -> kernel._CAPI_DGLRgcnLayer1Backward."""
+    t = [_nd(x) for x in (hidden, weight, norm, grad_out, grad_hidden, grad_weight)]
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200RgcnLayer1Backward(G.handle, *[x.ptr for x in t], _stream(G)))
+
+
 def copy_reduce_mean(G, target, X, out):
     """Extension (no reference PackedFunc): copy + mean in one pass, see
     DGLB200KernelCopyReduceMean in include/dgl_b200.h."""

@@ -205,6 +205,57 @@ int DGLB200KernelBackwardFusedGat(DGLB200GraphHandle graph, const DGLB200Tensor*
                                   DGLB200Tensor* grad_feat_src, DGLB200Tensor* grad_el,
                                   DGLB200Tensor* grad_er, float slope, void* stream);
 
+/* graph.add_edges_with_type (Graph::AddEdgesWithType, src/graph/graph.cc:140-165) followed by
+ * Graph::GetCsrSortedByEdgeType (graph.cc:690-741): attaches a relation id to every edge id
+ * (etypes[e], int32 or int64, host or device, 0 <= type < num_types) and builds the typed in- and
+ * out-adjacency on the device: indptr is the untyped CSR's, every row is re-ordered by
+ * (type, edge id). The reference orders rows with std::sort on the type only, so the order
+ * inside one type is unspecified there; this is its stable form. */
+int DGLB200GraphSetEdgeTypes(DGLB200GraphHandle graph, const void* etypes, int idx_bits,
+                             int64_t num_types, void* stream);
+
+/* The four int32 arrays GetCsrSortedByEdgeType(transpose) returns -- ranges [N+1], ids [E],
+ * eids [E], types [E] -- copied into caller buffers (host or device; NULL skips one).
+ * transpose = 0: in-edges (ids = sources), 1: out-edges (ids = destinations). */
+int DGLB200GraphCopyCsrSortedByEdgeType(DGLB200GraphHandle graph, int transpose, int32_t* indptr,
+                                        int32_t* ids, int32_t* eids, int32_t* types,
+                                        void* stream);
+
+/* kernel._CAPI_DGLRgcnLayer0(graph, weight, norm, ret)  (src/kernel/binary_reduce.cc:412-420;
+ * kernel src/kernel/cuda/binary_reduce_impl.cu:913-975). weight [R, N, F] (the embedding of a
+ * one-hot input), norm [E,1] by edge id, ret [N, F]:
+ *   ret[v,:] = sum over in-edges e of weight[type(e), src(e), :] * norm[e]. */
+int DGLB200RgcnLayer0(DGLB200GraphHandle graph, const DGLB200Tensor* weight,
+                      const DGLB200Tensor* norm, DGLB200Tensor* ret, void* stream);
+
+/* kernel._CAPI_DGLRgcnLayer0Backward(graph, grad_out, norm, grad_weight)  (binary_reduce.cc:
+ * 422-430; kernel binary_reduce_impl.cu:982-1046). Writes grad_weight[type, u, :] for every
+ * (type, u) that has an out-edge; other entries keep the caller's zeros, as in the reference.
+ * accumulate != 0: the gradient, sum over the edges u -> v of that type of grad_out[v,:]*norm[e].
+ * accumulate == 0: the reference's plain store (:1004) -- the LAST such edge in (type, edge id)
+ * order wins; equal to the sum only when no (type, u) pair has two out-edges. */
+int DGLB200RgcnLayer0Backward(DGLB200GraphHandle graph, const DGLB200Tensor* grad_out,
+                              const DGLB200Tensor* norm, DGLB200Tensor* grad_weight,
+                              int accumulate, void* stream);
+
+/* kernel._CAPI_DGLRgcnLayer1(graph, hidden, weight, norm, ret)  (binary_reduce.cc:432-440;
+ * kernel binary_reduce_impl.cu:1082-1155). hidden [N, in], weight [R, in, out], ret [N, out]
+ * (fully overwritten; the reference atomically adds into a zero-filled ret):
+ *   ret[v,x] = sum_e sum_y hidden[src(e),y] * weight[type(e),y,x] * norm[e];  in, out <= 128. */
+int DGLB200RgcnLayer1(DGLB200GraphHandle graph, const DGLB200Tensor* hidden,
+                      const DGLB200Tensor* weight, const DGLB200Tensor* norm, DGLB200Tensor* ret,
+                      void* stream);
+
+/* kernel._CAPI_DGLRgcnLayer1Backward(graph, hidden, weight, norm, grad_out, grad_hidden,
+ *   grad_weight)  (binary_reduce.cc:442-450; kernel binary_reduce_impl.cu:1157-1246).
+ * grad_hidden [N, in] and grad_weight [R, in, out] are fully overwritten (the reference
+ * atomicAdds into zero-filled buffers; same values, here without atomics and deterministic).
+ * in * out <= 1024 as in the reference (its block size). */
+int DGLB200RgcnLayer1Backward(DGLB200GraphHandle graph, const DGLB200Tensor* hidden,
+                              const DGLB200Tensor* weight, const DGLB200Tensor* norm,
+                              const DGLB200Tensor* grad_out, DGLB200Tensor* grad_hidden,
+                              DGLB200Tensor* grad_weight, void* stream);
+
 /* ---- extensions (no reference PackedFunc; they replace multi-call sequences the reference's
  *      torch backend performs around the kernels) ---- */
 

@@ -361,3 +361,136 @@ void orc_fused_gat_backward(idx_t n_src, idx_t n_dst, const idx_t* indptr, const
         grad_el[u * H + h] += s2;
       }
 }
+
+/* ------------------------------------------------------------------ RGCN hack ops (a15)
+ * PARITY UNPINNED: these kernels are CUDA-only in the reference (and the fork's library does not
+ * link them into a CPU build), nothing in its tests touches them; what follows restates the CUDA
+ * source thread by thread in plain C. */
+#include <stdlib.h>
+
+typedef struct { idx_t type, pos; } orc_tkey;
+
+static int orc_tkey_cmp(const void* a, const void* b) {
+  const orc_tkey* x = (const orc_tkey*)a;
+  const orc_tkey* y = (const orc_tkey*)b;
+  if (x->type != y->type) return x->type < y->type ? -1 : 1;
+  return x->pos < y->pos ? -1 : (x->pos > y->pos ? 1 : 0);
+}
+
+/* Graph::GetCsrSortedByEdgeType (src/graph/graph.cc:690-741): adjacency lists in insertion
+ * (edge id) order (graph.cc:97-108), each row sorted by type; std::sort's order within one type
+ * is unspecified, the stable order (type, edge id) is used. key/other/type are indexed by edge id;
+ * key = dst for the in-adjacency (transpose = false), src for the out-adjacency. */
+void orc_typed_csr(idx_t n_rows, idx_t n_edges, const idx_t* key, const idx_t* other,
+                   const idx_t* type, idx_t* indptr, idx_t* ids, idx_t* eids, idx_t* types) {
+  idx_t e, r, p;
+  idx_t* fill;
+  orc_tkey* keys;
+  for (r = 0; r <= n_rows; ++r) indptr[r] = 0;
+  for (e = 0; e < n_edges; ++e) indptr[key[e] + 1]++;
+  for (r = 0; r < n_rows; ++r) indptr[r + 1] += indptr[r];
+  fill = (idx_t*)malloc(sizeof(idx_t) * (size_t)(n_rows + 1));
+  for (r = 0; r < n_rows; ++r) fill[r] = indptr[r];
+  for (e = 0; e < n_edges; ++e) eids[fill[key[e]]++] = e;
+  free(fill);
+  keys = (orc_tkey*)malloc(sizeof(orc_tkey) * (size_t)(n_edges + 1));
+  for (r = 0; r < n_rows; ++r) {
+    idx_t beg = indptr[r], n = indptr[r + 1] - indptr[r];
+    for (p = 0; p < n; ++p) {
+      keys[p].type = type[eids[beg + p]];
+      keys[p].pos = eids[beg + p];
+    }
+    qsort(keys, (size_t)n, sizeof(orc_tkey), orc_tkey_cmp);
+    for (p = 0; p < n; ++p) eids[beg + p] = keys[p].pos;
+  }
+  free(keys);
+  for (p = 0; p < n_edges; ++p) {
+    ids[p] = other[eids[p]];
+    types[p] = type[eids[p]];
+  }
+}
+
+/* RgcnLayer0KernelImpl (binary_reduce_impl.cu:913-933): block = dst row, thread = column. */
+void orc_rgcn_layer0(idx_t n_nodes, const idx_t* ranges, const idx_t* src_ids, const idx_t* eids,
+                     const idx_t* types, int64_t n_w_rows, int64_t feat, const float* weight,
+                     const float* norm, float* ret) {
+  idx_t v, p;
+  int64_t tx;
+  for (v = 0; v < n_nodes; ++v)
+    for (tx = 0; tx < feat; ++tx) {
+      float agg = 0.f;
+      for (p = ranges[v]; p < ranges[v + 1]; ++p) {
+        float w = weight[types[p] * n_w_rows * feat + src_ids[p] * feat + tx];
+        agg += w * norm[eids[p]];
+      }
+      ret[v * feat + tx] = agg;
+    }
+}
+
+/* RgcnLayer0BackwardKernelImpl (binary_reduce_impl.cu:982-1008): block = src row of the typed
+ * out-adjacency. accumulate == 0 is the source as written (plain store, the last edge of a
+ * (type, src) pair wins); accumulate != 0 sums, which is the gradient of orc_rgcn_layer0.
+ * grad_weight must be zero-filled by the caller (tensor.py:454). */
+void orc_rgcn_layer0_backward(idx_t n_nodes, const idx_t* ranges, const idx_t* dst_ids,
+                              const idx_t* eids, const idx_t* types, int64_t n_w_rows,
+                              int64_t feat, const float* grad_out, const float* norm,
+                              int accumulate, float* grad_weight) {
+  idx_t u, p;
+  int64_t tx;
+  for (u = 0; u < n_nodes; ++u)
+    for (tx = 0; tx < feat; ++tx)
+      for (p = ranges[u]; p < ranges[u + 1]; ++p) {
+        float v = grad_out[dst_ids[p] * feat + tx] * norm[eids[p]];
+        float* slot = grad_weight + types[p] * n_w_rows * feat + u * feat + tx;
+        if (accumulate) *slot += v; else *slot = v;
+      }
+}
+
+/* RgcnLayer1KernelImpl (binary_reduce_impl.cu:1082-1117): thread = (y, x); per-thread sum over
+ * the row, then atomicAdd over y (taken in ascending y here). ret is zero-filled first. */
+void orc_rgcn_layer1(idx_t n_nodes, const idx_t* ranges, const idx_t* src_ids, const idx_t* eids,
+                     const idx_t* types, int64_t fy, int64_t fx, const float* hidden,
+                     const float* weight, const float* norm, float* ret) {
+  idx_t v, p;
+  int64_t y, x;
+  for (v = 0; v < n_nodes; ++v) {
+    for (x = 0; x < fx; ++x) ret[v * fx + x] = 0.f;
+    for (y = 0; y < fy; ++y)
+      for (x = 0; x < fx; ++x) {
+        float agg = 0.f;
+        for (p = ranges[v]; p < ranges[v + 1]; ++p) {
+          float w = weight[types[p] * fy * fx + y * fx + x];
+          float h = hidden[src_ids[p] * fy + y];
+          agg += h * w * norm[eids[p]];
+        }
+        ret[v * fx + x] += agg;
+      }
+  }
+}
+
+/* RgcnLayer1BackwardKernelImpl (binary_reduce_impl.cu:1157-1194) over the typed out-adjacency;
+ * atomics taken in (row, y, x, position) order. Outputs are zero-filled first (tensor.py:483-484). */
+void orc_rgcn_layer1_backward(idx_t n_nodes, idx_t n_types, const idx_t* ranges,
+                              const idx_t* dst_ids, const idx_t* eids, const idx_t* types,
+                              int64_t fy, int64_t fx, const float* hidden, const float* weight,
+                              const float* norm, const float* grad_out, float* grad_hidden,
+                              float* grad_weight) {
+  idx_t u, p;
+  int64_t y, x, i;
+  for (i = 0; i < n_nodes * fy; ++i) grad_hidden[i] = 0.f;
+  for (i = 0; i < n_types * fy * fx; ++i) grad_weight[i] = 0.f;
+  for (u = 0; u < n_nodes; ++u)
+    for (y = 0; y < fy; ++y)
+      for (x = 0; x < fx; ++x) {
+        float h = hidden[u * fy + y];
+        float agg = 0.f;
+        for (p = ranges[u]; p < ranges[u + 1]; ++p) {
+          float g = grad_out[dst_ids[p] * fx + x];
+          float w = weight[types[p] * fy * fx + y * fx + x];
+          float n = norm[eids[p]];
+          agg += g * w * n;
+          grad_weight[types[p] * fy * fx + y * fx + x] += g * h * n;
+        }
+        grad_hidden[u * fy + y] += agg;
+      }
+}

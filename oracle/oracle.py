@@ -338,3 +338,68 @@ def fused_gat_backward(g, ft, el, er, s, ex, ret, gout, slope):
                                  _p(el), _p(er), _p(s), _p(ex), _p(ret), _p(gout),
                                  ctypes.c_float(slope), _p(gft), _p(gel), _p(ger))
     return gft, gel, ger
+
+
+# ------------------------------------------------------------------ RGCN hack ops (a15)
+# PARITY UNPINNED: CUDA-only kernels in the reference, no reference test, and the fork's library
+# cannot link them on CPU; restated from the CUDA source, cross-checked in tests against a dense
+# numpy formula and the builtin composition (RelGraphConv-style u_mul_e + sum per relation).
+def typed_csr(g, etypes, transpose):
+    """Graph::GetCsrSortedByEdgeType(transpose) (src/graph/graph.cc:690-741) ->
+    (ranges, ids, eids, types), rows ordered by (type, edge id)."""
+    et = _i64(etypes)
+    key, other = (g.src, g.dst) if transpose else (g.dst, g.src)
+    n_rows = g.num_src if transpose else g.num_dst
+    indptr = np.empty(n_rows + 1, np.int64)
+    ids, eids, types = (np.empty(g.num_edges, np.int64) for _ in range(3))
+    lib().orc_typed_csr(ctypes.c_int64(n_rows), ctypes.c_int64(g.num_edges), _p(key), _p(other),
+                        _p(et), _p(indptr), _p(ids), _p(eids), _p(types))
+    return indptr, ids, eids, types
+
+
+def rgcn_layer0(g, etypes, weight, norm):
+    """RgcnLayer0Impl (binary_reduce_impl.cu:913-975). weight [R,N,F], norm [E,1] -> [N,F]."""
+    weight, norm = _f32(weight), _f32(norm).reshape(-1)
+    ip, ids, eids, ty = typed_csr(g, etypes, False)
+    ret = np.empty((g.num_dst, weight.shape[2]), np.float32)
+    lib().orc_rgcn_layer0(ctypes.c_int64(g.num_dst), _p(ip), _p(ids), _p(eids), _p(ty),
+                          ctypes.c_int64(weight.shape[1]), ctypes.c_int64(weight.shape[2]),
+                          _p(weight), _p(norm), _p(ret))
+    return ret
+
+
+def rgcn_layer0_backward(g, etypes, grad_out, norm, weight_shape, accumulate=True):
+    """RgcnLayer0BackwardImpl (binary_reduce_impl.cu:982-1046); accumulate=False = as written."""
+    grad_out, norm = _f32(grad_out), _f32(norm).reshape(-1)
+    ip, ids, eids, ty = typed_csr(g, etypes, True)
+    gw = np.zeros(tuple(weight_shape), np.float32)
+    lib().orc_rgcn_layer0_backward(ctypes.c_int64(g.num_src), _p(ip), _p(ids), _p(eids), _p(ty),
+                                   ctypes.c_int64(weight_shape[1]),
+                                   ctypes.c_int64(weight_shape[2]), _p(grad_out), _p(norm),
+                                   ctypes.c_int(int(bool(accumulate))), _p(gw))
+    return gw
+
+
+def rgcn_layer1(g, etypes, hidden, weight, norm):
+    """RgcnLayer1Impl (binary_reduce_impl.cu:1082-1155). hidden [N,in], weight [R,in,out]."""
+    hidden, weight, norm = _f32(hidden), _f32(weight), _f32(norm).reshape(-1)
+    ip, ids, eids, ty = typed_csr(g, etypes, False)
+    ret = np.empty((g.num_dst, weight.shape[2]), np.float32)
+    lib().orc_rgcn_layer1(ctypes.c_int64(g.num_dst), _p(ip), _p(ids), _p(eids), _p(ty),
+                          ctypes.c_int64(weight.shape[1]), ctypes.c_int64(weight.shape[2]),
+                          _p(hidden), _p(weight), _p(norm), _p(ret))
+    return ret
+
+
+def rgcn_layer1_backward(g, etypes, hidden, weight, norm, grad_out):
+    """RgcnLayer1BackwardImpl (binary_reduce_impl.cu:1157-1246) -> (grad_hidden, grad_weight)."""
+    hidden, weight, norm, grad_out = (_f32(hidden), _f32(weight), _f32(norm).reshape(-1),
+                                      _f32(grad_out))
+    ip, ids, eids, ty = typed_csr(g, etypes, True)
+    gh, gw = np.empty_like(hidden), np.empty_like(weight)
+    lib().orc_rgcn_layer1_backward(ctypes.c_int64(g.num_src), ctypes.c_int64(weight.shape[0]),
+                                   _p(ip), _p(ids), _p(eids), _p(ty),
+                                   ctypes.c_int64(weight.shape[1]),
+                                   ctypes.c_int64(weight.shape[2]), _p(hidden), _p(weight),
+                                   _p(norm), _p(grad_out), _p(gh), _p(gw))
+    return gh, gw

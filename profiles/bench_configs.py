@@ -137,6 +137,39 @@ def c4(out):
     ms = timeit(lambda: F.copy_reduce("sum", g, 2, msg, n))
     rec(out, "C4 AM", "copy_e+sum [E,16] (RelGraphConv message reduce)", ms, e,
         e * d * 4 + e * 4 + n * d * 4 + (n + 1) * 4)
+    # fused RGCN layer 1 (hack op): typed adjacency, W [133,16,16], norm [E,1]
+    import time
+    torch.cuda.synchronize()
+    t0 = time.time()
+    g.set_edge_types(et, R)
+    torch.cuda.synchronize()
+    prep_ms = (time.time() - t0) * 1e3
+    w = rand(R, d, d)
+    norm = torch.rand(e, 1, device=DEV)
+    ms = timeit(lambda: F.rgcn_layer1(g, x, w, norm))
+    # per edge: h row (gather) + 4 index/type/eid/norm words; per node: out row + indptr
+    nb = gather_bytes(n, e, d) + e * 16 + n * d * 4 + (n + 1) * 4 + R * d * d * 4
+    rec(out, "C4 AM", "rgcn_layer1 fwd (typed CSR, one kernel)", ms, e, nb,
+        "typed adjacency build %.1f ms once" % prep_ms)
+    xg = x.clone().requires_grad_(True)
+    wg = w.clone().requires_grad_(True)
+    gout = rand(n, d)
+
+    def l1_fb():
+        o = F.rgcn_layer1(g, xg, wg, norm)
+        o.backward(gout)
+        xg.grad = wg.grad = None
+    ms = timeit(l1_fb)
+    rec(out, "C4 AM", "rgcn_layer1 fwd+bwd (grad_h + grad_W, no atomics)", ms, 2 * e,
+        2 * nb + e * (2 * d * 4 + 12), "5 kernels")
+
+    def relgraphconv_lowmem():
+        # relgraphconv.py:122-137 low-mem basis path: per-edge bmm message then copy_e+sum
+        m = torch.bmm(x[src].unsqueeze(1), w[et]).squeeze(1) * norm
+        return F.copy_reduce("sum", g, 2, m, n)
+    ms = timeit(relgraphconv_lowmem, reps=5, warm=2)
+    rec(out, "C4 AM", "RelGraphConv-style torch bmm message + copy_e+sum (comparison)", ms, e, nb,
+        "torch gather+bmm then our copy_e kernel")
 
 
 def sbm_graph(n, e, blocks, p_in, alpha, seed):

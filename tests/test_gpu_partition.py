@@ -44,7 +44,8 @@ def test_partitioned_kernels_match_whole_graph(world, d):
         out = pg._agg("inner", x[p.inner_global].contiguous())
         if p.n_halo:
             out = out + pg._agg("halo", x[p.halo_global].contiguous())
-        torch.testing.assert_close(out, ref.detach()[p.inner_global], rtol=1e-5, atol=1e-5)
+        # the hub row sums 6000 terms of +-1 in a different (inner, then halo) order
+        torch.testing.assert_close(out, ref.detach()[p.inner_global], rtol=1e-5, atol=5e-4)
         go = w[p.inner_global].contiguous()
         grad.index_add_(0, p.inner_global, pg._agg_t("inner", go))
         if p.n_halo:
@@ -57,7 +58,7 @@ def test_partitioned_kernels_match_whole_graph(world, d):
                 got.append(pq.inner_global[pq.send_idx[r]])
         got = torch.cat(got) if got else torch.empty(0, dtype=torch.int64, device=dev)
         assert torch.equal(got, p.halo_global)
-    torch.testing.assert_close(grad, xg.grad, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(grad, xg.grad, rtol=1e-5, atol=5e-4)
 
 
 def _nccl_worker(rank, world, port, q):
@@ -86,8 +87,8 @@ def _nccl_worker(rank, world, port, q):
         xi = x[p.inner_global].clone().requires_grad_(True)
         out = pg.copy_src_sum(xi)
         out.backward(w[p.inner_global].contiguous())
-        ok_f = torch.allclose(out.detach(), ref.detach()[p.inner_global], rtol=1e-5, atol=1e-5)
-        ok_b = torch.allclose(xi.grad, xg.grad[p.inner_global], rtol=1e-5, atol=1e-5)
+        ok_f = torch.allclose(out.detach(), ref.detach()[p.inner_global], rtol=1e-5, atol=5e-4)
+        ok_b = torch.allclose(xi.grad, xg.grad[p.inner_global], rtol=1e-5, atol=5e-4)
         q.put((rank, bool(ok_f), bool(ok_b)))
     finally:
         dist.destroy_process_group()
