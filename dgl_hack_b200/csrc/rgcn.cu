@@ -212,6 +212,86 @@ __global__ void __launch_bounds__(256) rgcn_l1_kernel(const L1Args a) {
   }
 }
 
+// d = s * b + c on both halves (FFMA2, one issue slot for two fp32 FMAs)
+__device__ __forceinline__ float2 ffma2(float s, float2 b, float2 c) {
+  unsigned long long sa, bb, cc, d;
+  asm("mov.b64 %0, {%1,%1};" : "=l"(sa) : "f"(s));
+  asm("mov.b64 %0, {%1,%2};" : "=l"(bb) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1,%2};" : "=l"(cc) : "f"(c.x), "f"(c.y));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(sa), "l"(bb), "l"(cc));
+  float2 r;
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(d));
+  return r;
+}
+
+// Same contraction with compile-time widths (A, B in {16, 32, 64}): max(A,B)/2 lanes per row,
+// every lane owns two adjacent feat columns and two adjacent out columns (64-bit loads, FFMA2).
+// The run sum t[] is exchanged through shared memory (one STS.64 + A/4 broadcast LDS.128 per
+// lane) instead of A shuffles, and the A loads of M[type] per lane are independent and unrolled.
+// Rows of one warp proceed independently (group-masked shuffles / __syncwarp): measured on B200,
+// letting each row close its runs on its own (0.51 ms on the AM-shaped graph) beats advancing the
+// warp's rows in lockstep with a warp-wide contraction (0.66 ms) -- the kernel is bound by the
+// indptr -> ids -> feature-row latency chain, not by issue slots.
+template <int A, int B>
+__global__ void __launch_bounds__(256) rgcn_l1_fast_kernel(const L1Args a) {
+  constexpr int GL = (A > B ? A : B) / 2;  // lanes per row
+  constexpr int RPW = 32 / GL;             // rows per warp
+  __shared__ __align__(16) float ts[8][RPW][A];
+  const int lane = threadIdx.x % GL;
+  const int grp = (threadIdx.x & 31) / GL;
+  const unsigned mask = group_mask(GL);
+  float* tsm = ts[threadIdx.x >> 5][grp];
+  const bool has_a = 2 * lane < A, has_b = 2 * lane < B;
+  const int64_t n_groups = (int64_t)gridDim.x * blockDim.x / GL;
+  for (int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GL; r < a.n_rows;
+       r += n_groups) {
+    const int beg = __ldg(a.indptr + r), end = __ldg(a.indptr + r + 1);
+    float2 t = make_float2(0.f, 0.f), acc = make_float2(0.f, 0.f);
+    int cur = -1;
+    auto flush = [&]() {
+      if (has_a) *reinterpret_cast<float2*>(tsm + 2 * lane) = t;
+      t = make_float2(0.f, 0.f);
+      __syncwarp(mask);
+      if (has_b) {
+        const float2* wrow = reinterpret_cast<const float2*>(a.m + (int64_t)cur * A * B) + lane;
+#pragma unroll
+        for (int y4 = 0; y4 < A / 4; ++y4) {
+          const float4 tv = *reinterpret_cast<const float4*>(tsm + 4 * y4);
+          acc = ffma2(tv.x, __ldg(wrow + (4 * y4 + 0) * (B / 2)), acc);
+          acc = ffma2(tv.y, __ldg(wrow + (4 * y4 + 1) * (B / 2)), acc);
+          acc = ffma2(tv.z, __ldg(wrow + (4 * y4 + 2) * (B / 2)), acc);
+          acc = ffma2(tv.w, __ldg(wrow + (4 * y4 + 3) * (B / 2)), acc);
+        }
+      }
+      __syncwarp(mask);
+    };
+    for (int p0 = beg; p0 < end; p0 += GL) {
+      int o = 0, ty = 0;
+      float n = 0.f;
+      if (p0 + lane < end) {
+        const int p = p0 + lane;
+        o = __ldg(a.ids + p);
+        ty = __ldg(a.types + p);
+        n = __ldg(a.norm + __ldg(a.eids + p));
+      }
+      const int cnt = min(GL, end - p0);
+      for (int j = 0; j < cnt; ++j) {
+        const int oj = __shfl_sync(mask, o, j, GL);
+        const int tj = __shfl_sync(mask, ty, j, GL);
+        const float nj = __shfl_sync(mask, n, j, GL);
+        if (tj != cur) {
+          if (cur >= 0) flush();
+          cur = tj;
+        }
+        if (has_a)
+          t = ffma2(nj, __ldg(reinterpret_cast<const float2*>(a.feat + (int64_t)oj * A) + lane), t);
+      }
+    }
+    if (cur >= 0) flush();
+    if (has_b) *reinterpret_cast<float2*>(a.out + r * B + 2 * lane) = acc;
+  }
+}
+
 __global__ void transpose_w_kernel(const float* __restrict__ w, float* __restrict__ wt, int R,
                                    int Y, int X) {
   const int64_t n = (int64_t)R * Y * X;
@@ -308,6 +388,68 @@ __global__ void __launch_bounds__(kGwThreads) rgcn_gw_partial_kernel(const GwArg
   }
 }
 
+// X % 4 == 0: a thread owns one y and four adjacent x (one broadcast LDS + one LDS.128 + two
+// FFMA2 per staged edge); Y*X/4 threads per CTA.
+__global__ void __launch_bounds__(kGwThreads) rgcn_gw_partial4_kernel(const GwArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  const int Y = a.Y, X = a.X, X4 = X >> 2;
+  float* hs = sm;                 // [kGwBatch][Y], already scaled by norm
+  float* gs = hs + kGwBatch * Y;  // [kGwBatch][X]  (kGwBatch * Y * 4 bytes is a multiple of 16)
+  __shared__ int s_src[kGwBatch], s_dst[kGwBatch];
+  __shared__ float s_n[kGwBatch];
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const bool active = tid < Y * X4;
+  const int y = tid / X4, x0 = (tid - y * X4) << 2;
+  const int64_t beg = (int64_t)blockIdx.x * kGwChunk;
+  const int64_t end = min(a.E, beg + kGwChunk);
+  int lo = 0, hi = a.R;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(a.type_ptr + mid) <= beg) lo = mid; else hi = mid;
+  }
+  int cur = lo;
+  float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
+  int64_t pos = beg;
+  while (pos < end) {
+    while (__ldg(a.type_ptr + cur + 1) <= pos) ++cur;  // skip empty types
+    const int64_t run_end = min(end, (int64_t)__ldg(a.type_ptr + cur + 1));
+    for (; pos < run_end; pos += kGwBatch) {
+      const int cnt = (int)min((int64_t)kGwBatch, run_end - pos);
+      __syncthreads();  // previous batch consumed
+      if (tid < cnt) {
+        s_src[tid] = __ldg(a.bt_src + pos + tid);
+        s_dst[tid] = __ldg(a.bt_dst + pos + tid);
+        s_n[tid] = __ldg(a.norm + __ldg(a.bt_eid + pos + tid));
+      }
+      __syncthreads();
+      for (int i = tid; i < cnt * Y; i += nthr) {
+        const int e = i / Y, yy = i - e * Y;
+        hs[i] = __fmul_rn(__ldg(a.h + (int64_t)s_src[e] * Y + yy), s_n[e]);
+      }
+      for (int i = tid; i < cnt * X; i += nthr) {
+        const int e = i / X, x = i - e * X;
+        gs[i] = __ldg(a.gout + (int64_t)s_dst[e] * X + x);
+      }
+      __syncthreads();
+      if (active) {
+#pragma unroll 4
+        for (int e = 0; e < cnt; ++e) {
+          const float hv = hs[e * Y + y];
+          const float4 g = *reinterpret_cast<const float4*>(gs + e * X + x0);
+          a01 = ffma2(hv, make_float2(g.x, g.y), a01);
+          a23 = ffma2(hv, make_float2(g.z, g.w), a23);
+        }
+      }
+    }
+    pos = run_end;
+    if (active) {
+      float* slot = a.partial + ((int64_t)blockIdx.x + cur) * (Y * X) + y * X + x0;
+      *reinterpret_cast<float4*>(slot) = make_float4(a01.x, a01.y, a23.x, a23.y);
+    }
+    a01 = a23 = make_float2(0.f, 0.f);
+  }
+}
+
 // one CTA per type: folds the chunk partials of that type in chunk order
 __global__ void rgcn_gw_combine_kernel(const GwArgs a) {
   const int r = blockIdx.x;
@@ -362,6 +504,22 @@ void run_l1(const L1Args& a, const char* name, cudaStream_t s) {
   if (a.n_rows == 0 || a.B == 0) return;
   const int m = std::max(a.A, a.B);
   B200_CHECK(m <= 128, "rgcn layer 1: feature widths above 128 are not supported");
+  const bool aligned = (reinterpret_cast<uintptr_t>(a.feat) % 8 == 0) &&
+                       (reinterpret_cast<uintptr_t>(a.m) % 8 == 0) &&
+                       (reinterpret_cast<uintptr_t>(a.out) % 8 == 0);
+  auto pow2w = [](int v) { return v == 16 || v == 32 || v == 64; };
+  if (aligned && pow2w(a.A) && pow2w(a.B)) {
+    const int grid = grid_for(a.n_rows, m / 2);
+#define B200_L1F(AA, BB) \
+  if (a.A == AA && a.B == BB) rgcn_l1_fast_kernel<AA, BB><<<grid, 256, 0, s>>>(a)
+    B200_L1F(16, 16); B200_L1F(16, 32); B200_L1F(16, 64);
+    B200_L1F(32, 16); B200_L1F(32, 32); B200_L1F(32, 64);
+    B200_L1F(64, 16); B200_L1F(64, 32); B200_L1F(64, 64);
+#undef B200_L1F
+    B200_CUDA(cudaGetLastError());
+    note_kernel(name, 1);
+    return;
+  }
   const int G = group_for(m);
   const int grid = grid_for(a.n_rows, G);
   if (G == 8) rgcn_l1_kernel<8, 1><<<grid, 256, 0, s>>>(a);
@@ -481,7 +639,11 @@ void rgcn_layer1_backward(DGLB200Graph* g, const float* h, const float* w, const
   if (n_chunks > 0) {
     const size_t smem = (size_t)kGwBatch * (Y + X) * 4;
     const int P = (Y * X + kGwThreads - 1) / kGwThreads;
-    if (P <= 1) rgcn_gw_partial_kernel<1><<<(int)n_chunks, kGwThreads, smem, s>>>(ga);
+    const int t4 = ((Y * (X / 4) + 31) / 32) * 32;
+    if (X % 4 == 0 && (kGwBatch * Y) % 4 == 0 && t4 <= kGwThreads &&
+        reinterpret_cast<uintptr_t>(ga.partial) % 16 == 0)
+      rgcn_gw_partial4_kernel<<<(int)n_chunks, t4, smem, s>>>(ga);
+    else if (P <= 1) rgcn_gw_partial_kernel<1><<<(int)n_chunks, kGwThreads, smem, s>>>(ga);
     else if (P == 2) rgcn_gw_partial_kernel<2><<<(int)n_chunks, kGwThreads, smem, s>>>(ga);
     else rgcn_gw_partial_kernel<4><<<(int)n_chunks, kGwThreads, smem, s>>>(ga);
     B200_CUDA(cudaGetLastError());

@@ -116,10 +116,10 @@ static int classify_b(const Bcast& bc, bool b_is_lhs, int* b_width, int* head_di
     *head_div = 1;
     return kBFull;
   }
-  if (bc.ndim == 1 && bs[0] == 1) {  // [.,D] x [.,1]
+  if (blen == 1) {  // [.,D...] x [.,1]: one scalar per neighbour
     *b_width = 1;
     *head_div = (int)bc.out_len;
-    return kBHead;
+    return kBScalar;
   }
   if (bc.ndim == 2 && bs[1] == 1 && bs[0] == bc.out_shape[0] && as[0] == bc.out_shape[0] &&
       as[1] == bc.out_shape[1]) {  // [.,H,F] x [.,H,1]
@@ -331,7 +331,7 @@ bool try_spmm(const KernelCall& c) {
   // ---- TMA bulk-copy staged path: full-warp rows, plain copy or scalar-per-edge weight
   {
     const int force = forced_path();
-    const bool scalar_w = (bmode == kBHead && a.b_width == 1 && a.b_src == kFromEid);
+    const bool scalar_w = (bmode == kBScalar && a.b_src == kFromEid);
     const int tch = round_tma_ch((nvec + 31) / 32);
     const int64_t row_bytes = D * 4;
     bool ok = (lpr == 32) && (bmode == kBNone || scalar_w) && tch > 0 && row_bytes <= 8192 &&

@@ -6,7 +6,8 @@
 namespace b200 {
 
 enum IdSrc { kFromCol = 0, kFromEid = 1, kFromRow = 2 };
-enum BMode { kBNone = 0, kBFull = 1, kBHead = 2 };
+// kBHead: one B value per head (column / b_head_div); kBScalar: one B value per neighbour
+enum BMode { kBNone = 0, kBFull = 1, kBHead = 2, kBScalar = 3 };
 constexpr int kOpNegA = 100;  // internal: value = -A (gradient of the rhs of "sub")
 
 struct SpmmArgs {
@@ -102,7 +103,9 @@ constexpr int min_blocks_for(int vec, int ch, int u, int bmode) {
 
 // FULL: a row is served by whole warps (lpr == 32) so every column offset is a compile-time
 // constant; otherwise lpr (< 32, CH == 1) lanes serve a row and a warp handles 32 / lpr rows.
-template <int VEC, int CH, int U, bool SUM, int BMODE, bool FULL>
+// MUL: the binary op is known to be "mul" (commutative: operand order irrelevant), so the
+// per-element runtime op switch disappears from the inner loop.
+template <int VEC, int CH, int U, bool SUM, int BMODE, bool FULL, bool MUL>
 __global__ void __launch_bounds__(256, min_blocks_for(VEC, CH, U, BMODE))
 spmm_kernel(const SpmmArgs a) {
   const int lane = threadIdx.x & 31;
@@ -151,6 +154,11 @@ spmm_kernel(const SpmmArgs a) {
 #pragma unroll
     for (int e = 0; e < VEC; ++e) acc[c].v[e] = ident;
 
+  int hc[CH];  // kBHead: B column of each of the lane's vector columns (loop invariant)
+  if (BMODE == kBHead) {
+#pragma unroll
+    for (int c = 0; c < CH; ++c) hc[c] = (cbase + c * lpr * VEC) / a.b_head_div;
+  }
   int64_t b_row_const = 0;
   if (BMODE != kBNone && a.b_src == kFromRow)
     b_row_const = (int64_t)(a.b_node_map ? __ldg(a.b_node_map + r) : r) * a.b_width;
@@ -182,6 +190,7 @@ spmm_kernel(const SpmmArgs a) {
       Vec<VEC> va[U][CH];
       Vec<VEC> vb[U][CH];
       float sb[U][CH];
+      float ss[U];
 #pragma unroll
       for (int k = 0; k < U; ++k) {
         const int srcl = (i + k) & (lpr - 1);
@@ -193,12 +202,13 @@ spmm_kernel(const SpmmArgs a) {
         const float* bp = nullptr;
         if (BMODE != kBNone)
           bp = a.B + ((a.b_src == kFromRow) ? b_row_const : (int64_t)ib * a.b_width);
+        if (BMODE == kBScalar) ss[k] = on ? __ldg(bp) : 0.f;
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
           if (on && col_ok(c)) {
             va[k][c] = ld_vec<VEC>(ap + c * lpr * VEC);
             if (BMODE == kBFull) vb[k][c] = ld_vec<VEC>(bp + cbase + c * lpr * VEC);
-            if (BMODE == kBHead) sb[k][c] = __ldg(bp + (cbase + c * lpr * VEC) / a.b_head_div);
+            if (BMODE == kBHead) sb[k][c] = __ldg(bp + hc[c]);
           }
         }
       }
@@ -211,8 +221,15 @@ spmm_kernel(const SpmmArgs a) {
 #pragma unroll
               for (int e = 0; e < VEC; ++e) {
                 float val = va[k][c].v[e];
-                if (BMODE == kBFull) val = spmm_value(a.op, a.b_is_lhs, val, vb[k][c].v[e]);
-                if (BMODE == kBHead) val = spmm_value(a.op, a.b_is_lhs, val, sb[k][c]);
+                if (MUL) {
+                  if (BMODE == kBFull) val = __fmul_rn(val, vb[k][c].v[e]);
+                  if (BMODE == kBHead) val = __fmul_rn(val, sb[k][c]);
+                  if (BMODE == kBScalar) val = __fmul_rn(val, ss[k]);
+                } else {
+                  if (BMODE == kBFull) val = spmm_value(a.op, a.b_is_lhs, val, vb[k][c].v[e]);
+                  if (BMODE == kBHead) val = spmm_value(a.op, a.b_is_lhs, val, sb[k][c]);
+                  if (BMODE == kBScalar) val = spmm_value(a.op, a.b_is_lhs, val, ss[k]);
+                }
                 if (BMODE == kBNone && a.op == kOpNegA) val = __fmul_rn(val, -1.f);
                 acc[c].v[e] = SUM ? __fadd_rn(acc[c].v[e], val) : red_call(a.red, acc[c].v[e], val);
               }
@@ -258,23 +275,27 @@ constexpr int unroll_for(int vec, int ch) {
 
 template <int VEC, int CH, int U>
 static void launch_shape(const SpmmArgs& a, int bmode, bool sum, int blocks, cudaStream_t s) {
-#define B200_SPMM_LAUNCH(SUMV, BM)                                             \
-  do {                                                                         \
-    if (a.lpr == 32) {                                                         \
-      spmm_kernel<VEC, CH, U, SUMV, BM, true><<<blocks, 256, 0, s>>>(a);       \
-    } else {                                                                   \
-      if constexpr (CH == 1)                                                   \
-        spmm_kernel<VEC, CH, U, SUMV, BM, false><<<blocks, 256, 0, s>>>(a);    \
-    }                                                                          \
+#define B200_SPMM_LAUNCH(SUMV, BM, MULV)                                             \
+  do {                                                                               \
+    if (a.lpr == 32) {                                                               \
+      spmm_kernel<VEC, CH, U, SUMV, BM, true, MULV><<<blocks, 256, 0, s>>>(a);       \
+    } else {                                                                         \
+      if constexpr (CH == 1)                                                         \
+        spmm_kernel<VEC, CH, U, SUMV, BM, false, MULV><<<blocks, 256, 0, s>>>(a);    \
+    }                                                                                \
   } while (0)
+  // the mul specialisation exists for the sum reducer only (u_mul_e + sum and its transposes)
+  const bool mul = sum && bmode != kBNone && a.op == kMul;
   if (sum) {
-    if (bmode == kBNone) B200_SPMM_LAUNCH(true, kBNone);
-    else if (bmode == kBFull) B200_SPMM_LAUNCH(true, kBFull);
-    else B200_SPMM_LAUNCH(true, kBHead);
+    if (bmode == kBNone) B200_SPMM_LAUNCH(true, kBNone, false);
+    else if (bmode == kBFull) { if (mul) B200_SPMM_LAUNCH(true, kBFull, true); else B200_SPMM_LAUNCH(true, kBFull, false); }
+    else if (bmode == kBHead) { if (mul) B200_SPMM_LAUNCH(true, kBHead, true); else B200_SPMM_LAUNCH(true, kBHead, false); }
+    else { if (mul) B200_SPMM_LAUNCH(true, kBScalar, true); else B200_SPMM_LAUNCH(true, kBScalar, false); }
   } else {
-    if (bmode == kBNone) B200_SPMM_LAUNCH(false, kBNone);
-    else if (bmode == kBFull) B200_SPMM_LAUNCH(false, kBFull);
-    else B200_SPMM_LAUNCH(false, kBHead);
+    if (bmode == kBNone) B200_SPMM_LAUNCH(false, kBNone, false);
+    else if (bmode == kBFull) B200_SPMM_LAUNCH(false, kBFull, false);
+    else if (bmode == kBHead) B200_SPMM_LAUNCH(false, kBHead, false);
+    else B200_SPMM_LAUNCH(false, kBScalar, false);
   }
 #undef B200_SPMM_LAUNCH
 }

@@ -70,6 +70,42 @@ def c1(out):
             gather_bytes(n, e, d) + e * 4 + n * d * 4 + (n + 1) * 4, "launch/latency bound")
 
 
+def c2(out):
+    """Reddit-shaped operator sweep (bench.py times copy_src+mean fwd+bwd on the same graph)."""
+    n, e, d = 232965, 114615892, 602
+    src, dst = bench.make_graph_coo(n, e, 0.6, 2, DEV)
+    g = B.GraphIndex.from_coo(n, n, src, dst, DEV)
+    del src, dst
+    x = rand(n, d)
+    gout = rand(n, d)
+    w = torch.rand(e, 1, device=DEV)
+    gb = gather_bytes(n, e, d)
+    base = gb + e * 4 + n * d * 4 + (n + 1) * 4
+    ms = timeit(lambda: F.copy_reduce("sum", g, 0, x, n), reps=5, warm=2)
+    rec(out, "C2 reddit", "copy_src+sum fwd D=602", ms, e, base)
+    ms = timeit(lambda: F.binary_reduce("sum", "mul", g, 0, 2, x, w, n), reps=5, warm=2)
+    rec(out, "C2 reddit", "u_mul_e+sum fwd D=602, e [E,1]", ms, e, base + e * 8)
+    out_t = F.binary_reduce("sum", "mul", g, 0, 2, x, w, n)
+    gx = torch.empty_like(x)
+    ms = timeit(lambda: K.backward_lhs_binary_op_reduce("sum", "mul", g, 0, 2, x, w, out_t, gout,
+                                                        gx), reps=5, warm=2)
+    rec(out, "C2 reddit", "u_mul_e+sum backward lhs (grad x)", ms, e, base + e * 8)
+    # grad wrt the edge scalar: unreduced gradient is [E, 602]; the torch side sums it to [E,1].
+    # Timed at 1/16 of the edges' worth of rows is not possible (kernel walks all edges), so the
+    # full call is timed only when its [E,602] buffer fits (276 GB: it does not) -> skipped.
+    ms = timeit(lambda: F.copy_reduce("max", g, 0, x, n), reps=3, warm=1)
+    rec(out, "C2 reddit", "copy_src+max fwd D=602", ms, e, base)
+    xs = rand(n, 1)
+    es = rand(e, 1)
+    ms = timeit(lambda: F.copy_reduce("sum", g, 2, es, n), reps=5, warm=2)
+    rec(out, "C2 reddit", "copy_e+sum [E,1]", ms, e, e * 12 + n * 8)
+    ms = timeit(lambda: F.binary_reduce("none", "add", g, 0, 1, xs, xs, e), reps=5, warm=2)
+    rec(out, "C2 reddit", "u_add_v -> [E,1] (SDDMM)", ms, e, e * 12 + n * 8)
+    x64 = rand(n, 64)
+    ms = timeit(lambda: F.binary_reduce("none", "dot", g, 0, 1, x64, x64, e), reps=3, warm=1)
+    rec(out, "C2 reddit", "u_dot_v D=64 -> [E,1] (SDDMM)", ms, e, e * 12 + 2 * n * 64 * 4)
+
+
 def c3(out):
     n, e, H, Fw = 169343, 1166243, 8, 16
     src, dst = bench.make_graph_coo(n, e, 0.4, 3, DEV)
@@ -219,7 +255,7 @@ def main():
     L2 = torch.cuda.get_device_properties(DEV).L2_cache_size
     out = []
     for name in args.only.split(","):
-        {"c1": c1, "c3": c3, "c4": c4, "c5": c5}[name](out)
+        {"c1": c1, "c2": c2, "c3": c3, "c4": c4, "c5": c5}[name](out)
         torch.cuda.empty_cache()
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(out, open(args.out, "w"), indent=1)
