@@ -213,6 +213,8 @@ struct DGLB200Graph {
   // locality. indptr / row / heavy_first alias `in` (same degrees); to_other -> out-CSR position.
   b200::Csr in_s;
   b200::TypeIndex ty;
+  // endpoints by edge id (lazy; the edge-output kernels walk edges in id order)
+  int32_t *coo_src = nullptr, *coo_dst = nullptr;
 };
 
 namespace b200 {
@@ -246,6 +248,8 @@ struct KernelCall {
 };
 
 void run_generic(const KernelCall& c);
+// graph.cu: source (which = 0) / destination (1) of every edge id, built on first use
+const int32_t* graph_coo(DGLB200Graph* g, int which, cudaStream_t s);
 // gat.cu
 void fused_gat_forward(DGLB200Graph* g, const float* ft, const float* el, const float* er,
                        float* sum, float* exp, float* ret, int64_t H, int64_t F, float slope,

@@ -560,6 +560,25 @@ __global__ void check_range_kernel(const int32_t* __restrict__ v, int64_t n, int
     if (v[i] < 0 || v[i] >= hi) atomicOr(bad, 1);
 }
 
+const int32_t* graph_coo(DGLB200Graph* g, int which, cudaStream_t s) {
+  if (!g->coo_src) {
+    const int64_t e = g->num_edges;
+    const size_t eb = (size_t)std::max<int64_t>(e, 1) * 4;
+    int32_t *cs = nullptr, *cd = nullptr;
+    B200_CUDA(cudaMalloc(&cs, eb));
+    B200_CUDA(cudaMalloc(&cd, eb));
+    if (e > 0) {
+      const int32_t* in_row = csr_rows(g, kWalkIn, s);
+      const int blocks = (int)std::min<int64_t>((e + 255) / 256, 148 * 16);
+      scatter_coo_kernel<<<blocks, 256, 0, s>>>(in_row, g->in.indices, g->in.eids, e, cd, cs);
+      note_kernel(nullptr, 1);
+    }
+    g->coo_dst = cd;
+    g->coo_src = cs;
+  }
+  return which ? g->coo_dst : g->coo_src;
+}
+
 static void free_typed(TypeIndex& t) {
   cudaFree(t.in.ids);
   cudaFree(t.in.eids);
@@ -601,11 +620,8 @@ static void build_typed(DGLB200Graph* g, const int32_t* et, int64_t num_types, c
     B200_CHECK(h == 0, "edge type id out of range [0, num_types)");
   }
   // endpoints by edge id
-  Scratch src_of(eb, s), dst_of(eb, s);
-  const int32_t* in_row = csr_rows(g, kWalkIn, s);
-  scatter_coo_kernel<<<blocks, 256, 0, s>>>(in_row, g->in.indices, g->in.eids, e,
-                                            dst_of.as<int32_t>(), src_of.as<int32_t>());
-  note_kernel(nullptr, 1);
+  const int32_t* src_of_p = graph_coo(g, 0, s);
+  const int32_t* dst_of_p = graph_coo(g, 1, s);
   // type-major list: stable sort of edge ids by type
   count_keys_kernel<<<blocks, 256, 0, s>>>(et, e, t.type_ptr);
   note_kernel(nullptr, 1);
@@ -618,8 +634,8 @@ static void build_typed(DGLB200Graph* g, const int32_t* et, int64_t num_types, c
                    vb.as<int32_t>(), e, num_types, &sk, &sv, s);
   B200_CUDA(cudaMemcpyAsync(t.bt_eid, sv, eb, cudaMemcpyDeviceToDevice, s));
   B200_CUDA(cudaMemcpyAsync(bt_type.ptr, sk, eb, cudaMemcpyDeviceToDevice, s));
-  gather_i32(src_of.as<int32_t>(), t.bt_eid, t.bt_src, e, s);
-  gather_i32(dst_of.as<int32_t>(), t.bt_eid, t.bt_dst, e, s);
+  gather_i32(src_of_p, t.bt_eid, t.bt_src, e, s);
+  gather_i32(dst_of_p, t.bt_eid, t.bt_dst, e, s);
   // rows: stable sort of the type-major list by destination (in) / source (out)
   coo_to_csr_device(g->num_dst, e, t.bt_dst, t.bt_src, t.bt_eid, ip.as<int32_t>(), t.in.ids,
                     t.in.eids, nullptr, perm.as<int32_t>(), s);
@@ -773,6 +789,8 @@ int DGLB200GraphFree(DGLB200GraphHandle g) {
     cudaSetDevice(g->device);
     cudaDeviceSynchronize();
     free_typed(g->ty);
+    cudaFree(g->coo_src);
+    cudaFree(g->coo_dst);
     g->in_s.indptr = nullptr;
     free_csr(g->in_s);
     free_csr(g->in);

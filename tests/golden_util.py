@@ -37,6 +37,9 @@ def check(name, got, want, red, scale=None, grad=False):
         rtol = 1e-5
     if grad and red == "prod":
         rtol = 1e-3
+    if red == "none" and not grad and "dot" in name:
+        # a dot product is itself a sum; the CUDA kernel adds its terms in a fixed butterfly order
+        rtol = 1e-5
     if rtol == 0.0:
         ok = np.array_equal(got, want)
         assert ok, "%s: not bit-exact, max abs diff %g" % (

@@ -134,3 +134,59 @@ def test_hub_rows_are_segmented(impl, path, seg, monkeypatch):
                           scale=O.backward_copy_reduce("sum", og, 0, x, want, np.abs(gout)))
         if seg == "0":
             assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("d", [1, 2, 3, 8, 16, 47, 64, 130, 602])
+def test_sddmm_widths_vs_oracle(impl, d):
+    """Edge-output kernels (reducer none, edge-operand gradients under sum) at every vector width /
+    lanes-per-edge shape and both traversal orders, against the oracle. Element-wise results have
+    one rounding each -> exact; dot is reduced in a butterfly order -> tolerance."""
+    from oracle import oracle as O
+    ns, nd, ne = 300, 280, 5000
+    src, dst = cases.powerlaw_graph(ns, nd, ne, 0.7, 200 + d)
+    og, gg = O.Graph(ns, nd, src, dst), impl.make_graph(ns, nd, src, dst)
+    rs = np.random.RandomState(d)
+    xs = rs.uniform(0.5, 1.5, (ns, d)).astype(np.float32)
+    xd = rs.uniform(0.5, 1.5, (nd, d)).astype(np.float32)
+    xe = rs.uniform(0.5, 1.5, (ne, d)).astype(np.float32)
+    for op in ("add", "sub", "mul", "div"):
+        for (lt, rt, l, r) in ((0, 1, xs, xd), (1, 0, xd, xs), (2, 1, xe, xd), (0, 2, xs, xe)):
+            want = O.binary_op_reduce("none", op, og, lt, rt, l, r, ne)
+            got = impl.binary_op_reduce("none", op, gg, lt, rt, l, r, ne, None, None, None)
+            assert impl.last == "sddmm", impl.last
+            np.testing.assert_array_equal(got, want)
+    for tgt, x in ((0, xs), (1, xd)):
+        want = O.copy_reduce("none", og, tgt, x, ne)
+        got = impl.copy_reduce("none", gg, tgt, x, ne, None, None)
+        assert impl.last == "sddmm"
+        np.testing.assert_array_equal(got, want)
+    # dot over the last axis: [., H, d] . [., H, d] -> [E, H]
+    for H in (1, 4):
+        a = rs.uniform(-1, 1, (ns, H, d)).astype(np.float32)
+        b = rs.uniform(-1, 1, (nd, H, d)).astype(np.float32)
+        want = O.binary_op_reduce("none", "dot", og, 0, 1, a, b, ne)
+        got = impl.binary_op_reduce("none", "dot", gg, 0, 1, a, b, ne, None, None, None)
+        pow2 = (d % 4 == 0 and (d // 4) & (d // 4 - 1) == 0 and d // 4 <= 32) or d in (1, 2)
+        if pow2:
+            assert impl.last == "sddmm", impl.last
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5 * d)
+    # gradients of the edge operand under sum: copy_e, u_mul_e (both sides), u_sub_e
+    out = O.copy_reduce("sum", og, 2, xe, nd)
+    gout = cases.grad_out_for(out.shape)
+    want = O.backward_copy_reduce("sum", og, 2, xe, out, gout)
+    got = impl.backward_copy_reduce("sum", gg, 2, xe, out, gout, None, None)
+    assert impl.last == "sddmm"
+    np.testing.assert_array_equal(got, want)
+    for op in ("mul", "sub", "add"):
+        out = O.binary_op_reduce("sum", op, og, 0, 2, xs, xe, nd)
+        want = O.backward_rhs_binary_op_reduce("sum", op, og, 0, 2, xs, xe, out, gout)
+        got = impl.backward_rhs_binary_op_reduce("sum", op, gg, 0, 2, xs, xe, out, gout,
+                                                 None, None, None)
+        assert impl.last == "sddmm"
+        np.testing.assert_array_equal(got, want)
+        out = O.binary_op_reduce("sum", op, og, 2, 0, xe, xs, nd)
+        want = O.backward_lhs_binary_op_reduce("sum", op, og, 2, 0, xe, xs, out, gout)
+        got = impl.backward_lhs_binary_op_reduce("sum", op, gg, 2, 0, xe, xs, out, gout,
+                                                 None, None, None)
+        assert impl.last == "sddmm"
+        np.testing.assert_array_equal(got, want)
