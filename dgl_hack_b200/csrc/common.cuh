@@ -170,6 +170,7 @@ struct Csr {
   int32_t seg_len = 0;          // 0 = plan not built
   int32_t n_seg = 0;            // total segments of heavy rows
   int32_t n_heavy = 0;          // heavy rows
+  int32_t n_long = 0;           // non-heavy rows with >= kLongRow edges (a prefix of sched)
   int32_t* seg_row = nullptr;   // [n_seg] row of the segment
   int32_t* seg_beg = nullptr;   // [n_seg] first CSR position
   int32_t* seg_end = nullptr;   // [n_seg] one past the last CSR position
@@ -178,8 +179,11 @@ struct Csr {
   int32_t* sched = nullptr;     // [n_rows] rows by descending degree class (NULL = natural order)
 };
 
+constexpr int kLongRow = 64;
+
 struct SegPlan {
   int seg_len, n_seg, n_heavy;
+  int n_long;  // with sched: its first n_long rows have >= kLongRow edges, its last n_heavy are heavy
   const int32_t *seg_row, *seg_beg, *seg_end, *heavy_row, *heavy_ptr;
   const int32_t* sched;  // row order for the non-segment work items (may be NULL)
 };
@@ -229,6 +233,7 @@ const int32_t* csr_rows(DGLB200Graph* g, int walk, cudaStream_t s);      // row-
 const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s);
 // Segment plan of a CSR for segments of `seg_len` positions (built once; synchronises then).
 SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s);
+int segment_length(int64_t num_edges);  // spmm.cu: the segment length every plan is built with
 void exclusive_scan_i32(int32_t* data, int64_t n, cudaStream_t s);
 void fill_f32(float* p, int64_t n, float v, cudaStream_t s);
 

@@ -404,6 +404,7 @@ __global__ void seg_count_kernel(const int32_t* __restrict__ indptr, int64_t n_r
     }
     key[r] = h ? 255 : (127 - cls);
     m = max(m, deg);
+    if (!h && deg >= kLongRow) atomicAdd(max_deg + 1, 1);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
@@ -444,11 +445,11 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
     cudaFree(c.seg_row); cudaFree(c.seg_beg); cudaFree(c.seg_end);
     cudaFree(c.heavy_row); cudaFree(c.heavy_ptr); cudaFree(c.sched);
     c.seg_row = c.seg_beg = c.seg_end = c.heavy_row = c.heavy_ptr = c.sched = nullptr;
-    c.n_seg = c.n_heavy = 0;
+    c.n_seg = c.n_heavy = c.n_long = 0;
     if (c.n_rows > 0) {
       Scratch nseg((size_t)(c.n_rows + 1) * 4, s), heavy((size_t)(c.n_rows + 1) * 4, s);
-      Scratch key((size_t)c.n_rows * 4, s), mdeg(4, s);
-      B200_CUDA(cudaMemsetAsync(mdeg.ptr, 0, 4, s));
+      Scratch key((size_t)c.n_rows * 4, s), mdeg(8, s);  // [max degree, rows >= kLongRow]
+      B200_CUDA(cudaMemsetAsync(mdeg.ptr, 0, 8, s));
       int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 8);
       seg_count_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, seg_len, nseg.as<int32_t>(),
                                               heavy.as<int32_t>(), key.as<int32_t>(),
@@ -456,13 +457,14 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
       note_kernel(nullptr, 1);
       exclusive_scan_i32(nseg.as<int32_t>(), c.n_rows + 1, s);
       exclusive_scan_i32(heavy.as<int32_t>(), c.n_rows + 1, s);
-      int32_t tot[3] = {0, 0, 0};
-      B200_CUDA(cudaMemcpyAsync(&tot[2], mdeg.ptr, 4, cudaMemcpyDeviceToHost, s));
+      int32_t tot[4] = {0, 0, 0, 0};
+      B200_CUDA(cudaMemcpyAsync(&tot[2], mdeg.ptr, 8, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaMemcpyAsync(&tot[0], nseg.as<int32_t>() + c.n_rows, 4, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaMemcpyAsync(&tot[1], heavy.as<int32_t>() + c.n_rows, 4, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaStreamSynchronize(s));
       c.n_seg = tot[0];
       c.n_heavy = tot[1];
+      c.n_long = tot[3];
       // Skewed degrees: order the row work items by degree class. (Uniform-ish graphs keep the
       // natural order and with it whatever locality the node numbering has.)
       const int64_t mean = (g->num_edges + c.n_rows - 1) / c.n_rows;
@@ -492,6 +494,7 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
   p.seg_len = seg_len;
   p.n_seg = c.n_seg;
   p.n_heavy = c.n_heavy;
+  p.n_long = c.sched ? c.n_long : 0;
   p.seg_row = c.seg_row;
   p.seg_beg = c.seg_beg;
   p.seg_end = c.seg_end;

@@ -48,7 +48,7 @@ static int forced_path() {
 // Default: the longest sequential walk may take about a quarter of the work one resident warp
 // slot gets (E / (148 SMs x 32 warps x 4)), rounded up to a power of two, at least 4096 -- rows
 // up to that many edges are reduced strictly sequentially (bit-exact vs the reference).
-static int segment_length(int64_t num_edges) {
+int segment_length(int64_t num_edges) {
   const char* e = std::getenv("B200_SPMM_SEG");
   if (e) {
     const long v = std::atol(e);

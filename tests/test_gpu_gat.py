@@ -19,7 +19,11 @@ def _close(name, got, want, scale):
 @pytest.mark.parametrize("H,F", [(8, 16), (1, 64), (4, 32), (8, 1), (2, 256), (3, 8), (5, 2),
                                  (1, 1), (16, 4)])
 @pytest.mark.parametrize("graph", ["square", "bipartite"])
-def test_fused_gat_vs_oracle(H, F, graph):
+@pytest.mark.parametrize("path", ["lane", "warp"])
+def test_fused_gat_vs_oracle(H, F, graph, path, monkeypatch):
+    # "lane": head-slice-per-lane kernels where the shape allows (F % 4 == 0 ...), "warp": the
+    # warp-per-row kernels for every shape
+    monkeypatch.setenv("B200_GAT_PATH", path)
     import torch
     import dgl_hack_b200 as B
     from dgl_hack_b200 import kernel as K
