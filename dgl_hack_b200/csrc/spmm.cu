@@ -48,6 +48,15 @@ static int forced_path() {
 // Default: the longest sequential walk may take about a quarter of the work one resident warp
 // slot gets (E / (148 SMs x 32 warps x 4)), rounded up to a power of two, at least 4096 -- rows
 // up to that many edges are reduced strictly sequentially (bit-exact vs the reference).
+// B200_SPMM_WIDE=0 (or B200_SPMM_SEG=0, "strictly sequential") keeps every sub-warp row on one
+// lane group.
+static bool wide_rows_enabled() {
+  const char* e = std::getenv("B200_SPMM_WIDE");
+  if (e && e[0] == '0') return false;
+  const char* g = std::getenv("B200_SPMM_SEG");
+  return !(g && std::atol(g) <= 0);
+}
+
 int segment_length(int64_t num_edges) {
   const char* e = std::getenv("B200_SPMM_SEG");
   if (e) {
@@ -384,8 +393,13 @@ bool try_spmm(const KernelCall& c) {
     }
   }
 
+  // sub-warp rows: segments and (with a degree schedule) rows of >= kLongRow edges get a warp each
+  a.n_wide = 0;
+  if (lpr < 32 && wide_rows_enabled())
+    a.n_wide = plan.n_seg + (plan.sched ? plan.n_long : 0);
   const int64_t n_warps =
-      (lpr == 32) ? n_items * slabs : (n_items + (32 / lpr) - 1) / (32 / lpr);
+      (lpr == 32) ? n_items * slabs
+                  : a.n_wide + (n_items - a.n_wide + (32 / lpr) - 1) / (32 / lpr);
   const int blocks = (int)((n_warps + 7) / 8);
   const bool sum = (c.red == kSum);
   if (vec == 4) launch_vec<4>(a, ch, bmode, sum, blocks, s);

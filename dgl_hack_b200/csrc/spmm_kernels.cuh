@@ -40,6 +40,10 @@ struct SpmmArgs {
   float* out;
   const int32_t* out_map;
   int need_col;
+  // sub-warp rows only (lpr < 32): the first n_wide work items (all segments, then the rows of
+  // the schedule with >= kLongRow edges) are served by a whole warp whose 32 / lpr lane groups
+  // take every (32 / lpr)-th edge and fold their partial results at the end
+  int n_wide;
 };
 
 template <int VEC>
@@ -116,12 +120,19 @@ spmm_kernel(const SpmmArgs a) {
   // ---- work item -> (row or heavy-row segment, slab)
   int64_t item;
   int slab = 0;
+  bool wide = false;  // warp-uniform
   if (FULL) {
     item = warp / a.slabs;
     slab = (int)(warp - item * a.slabs);
   } else {
-    item = warp * (32 / lpr) + lane / lpr;
+    wide = warp < a.n_wide;
+    item = wide ? warp : a.n_wide + (warp - a.n_wide) * (32 / lpr) + lane / lpr;
   }
+  // batch width / this lane's slot in the id batch / edge stride and offset of the lane group
+  const int bw = (!FULL && wide) ? 32 : lpr;
+  const int bl = (!FULL && wide) ? lane : sub;
+  const int estride = (!FULL && wide) ? 32 / lpr : 1;
+  const int eoff = (!FULL && wide) ? lane / lpr : 0;
   bool row_ok = item < (int64_t)a.n_seg + a.n_rows;
   const bool is_seg = item < a.n_seg;
   int r = 0, beg = 0, deg = 0;
@@ -164,9 +175,9 @@ spmm_kernel(const SpmmArgs a) {
     b_row_const = (int64_t)(a.b_node_map ? __ldg(a.b_node_map + r) : r) * a.b_width;
 
   const int maxdeg = FULL ? deg : __reduce_max_sync(0xffffffffu, deg);
-  for (int base = 0; base < maxdeg; base += lpr) {
-    // ---- cooperative fetch of up to lpr neighbour ids per row
-    const int my = base + sub;
+  for (int base = 0; base < maxdeg; base += bw) {
+    // ---- cooperative fetch of up to bw neighbour ids per row
+    const int my = base + bl;
     int pa = 0, pb = 0;
     if (my < deg) {
       const int p = beg + my;
@@ -185,19 +196,20 @@ spmm_kernel(const SpmmArgs a) {
         }
       }
     }
-    const int cnt = min(lpr, maxdeg - base);  // warp-uniform
-    for (int i = 0; i < cnt; i += U) {
+    const int cnt = min(bw, maxdeg - base);  // warp-uniform
+    for (int i = 0; i < cnt; i += U * estride) {
       Vec<VEC> va[U][CH];
       Vec<VEC> vb[U][CH];
       float sb[U][CH];
       float ss[U];
 #pragma unroll
       for (int k = 0; k < U; ++k) {
-        const int srcl = (i + k) & (lpr - 1);
-        const int ia = __shfl_sync(0xffffffffu, pa, srcl, lpr);
+        const int ei = i + k * estride + eoff;  // edge of this lane group inside the batch
+        const int srcl = ei & (bw - 1);
+        const int ia = __shfl_sync(0xffffffffu, pa, srcl, bw);
         int ib = 0;
-        if (BMODE != kBNone) ib = __shfl_sync(0xffffffffu, pb, srcl, lpr);
-        const bool on = (i + k < lpr) && (base + i + k < deg);
+        if (BMODE != kBNone) ib = __shfl_sync(0xffffffffu, pb, srcl, bw);
+        const bool on = (ei < bw) && (base + ei < deg);
         const float* ap = a.A + (int64_t)ia * a.D + cbase;
         const float* bp = nullptr;
         if (BMODE != kBNone)
@@ -214,7 +226,8 @@ spmm_kernel(const SpmmArgs a) {
       }
 #pragma unroll
       for (int k = 0; k < U; ++k) {
-        if ((i + k < lpr) && (base + i + k < deg)) {
+        const int ei = i + k * estride + eoff;
+        if ((ei < bw) && (base + ei < deg)) {
 #pragma unroll
           for (int c = 0; c < CH; ++c) {
             if (col_ok(c)) {
@@ -240,6 +253,18 @@ spmm_kernel(const SpmmArgs a) {
     }
   }
 
+  if (!FULL && wide) {
+    // fold the lane groups' partial results (fixed butterfly order); group 0 writes
+#pragma unroll
+    for (int c = 0; c < CH; ++c)
+#pragma unroll
+      for (int e = 0; e < VEC; ++e)
+        for (int o = lpr; o < 32; o <<= 1) {
+          const float other = __shfl_xor_sync(0xffffffffu, acc[c].v[e], o);
+          acc[c].v[e] = SUM ? __fadd_rn(acc[c].v[e], other) : red_call(a.red, acc[c].v[e], other);
+        }
+    if (lane >= lpr) row_ok = false;
+  }
   if (row_ok) {
     float* op;
     if (is_seg) {
