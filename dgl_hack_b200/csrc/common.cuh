@@ -165,18 +165,24 @@ struct Csr {
   int32_t* row = nullptr;      // [nnz] row of each position (lazily built COO expansion)
   int32_t* to_other = nullptr; // [nnz] position of the same edge in the other CSR (lazy)
   int64_t n_rows = 0, n_cols = 0;
-  // Segment plan (lazy): rows with more than seg_len edges are cut into segments of seg_len
-  // consecutive positions so that no single warp walks a hub row alone.
-  int32_t seg_len = 0;          // 0 = plan not built
-  int32_t n_seg = 0;            // total segments of heavy rows
-  int32_t n_heavy = 0;          // heavy rows
-  int32_t n_long = 0;           // non-heavy rows with >= kLongRow edges (a prefix of sched)
-  int32_t* seg_row = nullptr;   // [n_seg] row of the segment
-  int32_t* seg_beg = nullptr;   // [n_seg] first CSR position
-  int32_t* seg_end = nullptr;   // [n_seg] one past the last CSR position
-  int32_t* heavy_row = nullptr; // [n_heavy]
-  int32_t* heavy_ptr = nullptr; // [n_heavy + 1] segment range of each heavy row
-  int32_t* sched = nullptr;     // [n_rows] rows by descending degree class (NULL = natural order)
+  // Segment plans (lazy, one slot per distinct segment length in use): rows with more than
+  // seg_len edges are cut into segments of seg_len consecutive positions so that no single warp
+  // walks a hub row alone.
+  struct Plan {
+    int32_t seg_len = 0;          // 0 = slot empty
+    int32_t n_seg = 0;            // total segments of heavy rows
+    int32_t n_heavy = 0;          // heavy rows
+    int32_t n_long = 0;           // non-heavy rows with >= kLongRow edges (a prefix of sched)
+    int32_t* seg_row = nullptr;   // [n_seg] row of the segment
+    int32_t* seg_beg = nullptr;   // [n_seg] first CSR position
+    int32_t* seg_end = nullptr;   // [n_seg] one past the last CSR position
+    int32_t* heavy_row = nullptr; // [n_heavy]
+    int32_t* heavy_ptr = nullptr; // [n_heavy + 1] segment range of each heavy row
+    int32_t* sched = nullptr;     // [n_rows] rows by descending degree class (NULL = natural order)
+  };
+  static constexpr int kPlanSlots = 4;
+  Plan plan[kPlanSlots];
+  int plan_next = 0;  // slot to evict when all are taken
 };
 
 constexpr int kLongRow = 64;

@@ -439,12 +439,44 @@ __global__ void seg_fill_kernel(const int32_t* __restrict__ indptr, int64_t n_ro
     heavy_ptr[heavy_idx[n_rows]] = seg_off[n_rows];  // sentinel: totals after the scans
 }
 
+static void free_plan(Csr::Plan& p) {
+  cudaFree(p.seg_row);
+  cudaFree(p.seg_beg);
+  cudaFree(p.seg_end);
+  cudaFree(p.heavy_row);
+  cudaFree(p.heavy_ptr);
+  cudaFree(p.sched);
+  p = Csr::Plan();
+}
+
 SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
-  Csr& c = (walk == kWalkOut) ? g->out : g->in;  // in_sorted has the in-CSR's degrees
-  if (c.seg_len != seg_len) {
-    cudaFree(c.seg_row); cudaFree(c.seg_beg); cudaFree(c.seg_end);
-    cudaFree(c.heavy_row); cudaFree(c.heavy_ptr); cudaFree(c.sched);
-    c.seg_row = c.seg_beg = c.seg_end = c.heavy_row = c.heavy_ptr = c.sched = nullptr;
+  Csr& csr = (walk == kWalkOut) ? g->out : g->in;  // in_sorted has the in-CSR's degrees
+  int slot = -1;
+  for (int k = 0; k < Csr::kPlanSlots; ++k)
+    if (csr.plan[k].seg_len == seg_len) slot = k;
+  const bool build = slot < 0;
+  if (build) {
+    for (int k = 0; k < Csr::kPlanSlots && slot < 0; ++k)
+      if (csr.plan[k].seg_len == 0) slot = k;
+    if (slot < 0) {
+      slot = csr.plan_next;
+      csr.plan_next = (csr.plan_next + 1) % Csr::kPlanSlots;
+      // a kernel enqueued earlier may still read the evicted plan
+      B200_CUDA(cudaStreamSynchronize(s));
+      free_plan(csr.plan[slot]);
+    }
+  }
+  struct View {  // the CSR's shape + the chosen slot's fields under the names used below
+    Csr::Plan& p;
+    int32_t*& seg_row; int32_t*& seg_beg; int32_t*& seg_end;
+    int32_t*& heavy_row; int32_t*& heavy_ptr; int32_t*& sched;
+    int32_t& n_seg; int32_t& n_heavy; int32_t& n_long; int32_t& seg_len;
+    const int32_t* indptr; int64_t n_rows;
+  };
+  Csr::Plan& pl = csr.plan[slot];
+  View c{pl, pl.seg_row, pl.seg_beg, pl.seg_end, pl.heavy_row, pl.heavy_ptr, pl.sched,
+         pl.n_seg, pl.n_heavy, pl.n_long, pl.seg_len, csr.indptr, csr.n_rows};
+  if (build) {
     c.n_seg = c.n_heavy = c.n_long = 0;
     if (c.n_rows > 0) {
       Scratch nseg((size_t)(c.n_rows + 1) * 4, s), heavy((size_t)(c.n_rows + 1) * 4, s);
@@ -510,12 +542,7 @@ static void free_csr(Csr& c) {
   cudaFree(c.eids);
   cudaFree(c.row);
   cudaFree(c.to_other);
-  cudaFree(c.seg_row);
-  cudaFree(c.seg_beg);
-  cudaFree(c.seg_end);
-  cudaFree(c.heavy_row);
-  cudaFree(c.heavy_ptr);
-  cudaFree(c.sched);
+  for (int k = 0; k < Csr::kPlanSlots; ++k) free_plan(c.plan[k]);
   c = Csr();
 }
 

@@ -68,6 +68,24 @@ int segment_length(int64_t num_edges) {
   return len;
 }
 
+// Segment length for one SpMM call. A row (or segment) is a chain of dependent steps of U
+// neighbours, ~1 us each under load (measured: a 462-edge row alone took 70 % of a 0.16 ms
+// kernel on the arxiv-shaped graph), while the rest of the grid finishes in about
+// bytes / 6 TB/s. The chain may cost a quarter of that: small graphs get short segments (down to
+// 64 edges), big ones keep the E-based length. Rows up to the segment length are reduced
+// strictly sequentially (bit-identical to the single-threaded reference); B200_SPMM_SEG pins it.
+static int segment_length_for(int64_t num_edges, int64_t row_bytes, int unroll) {
+  const int base = segment_length(num_edges);
+  if (std::getenv("B200_SPMM_SEG")) return base;
+  const double bulk_us = (double)num_edges * (double)row_bytes / 6.0e6;
+  const double target = 0.25 * bulk_us * unroll;
+  int len = 64;
+  for (int cand : {512, 4096})
+    if (cand <= target) len = cand;
+  if (base <= target || len > base) len = base;
+  return len;
+}
+
 // out[row] = fold of the row's partial rows in segment order (+ mean division)
 __global__ void __launch_bounds__(128)
 combine_partials_kernel(const int32_t* __restrict__ heavy_row,
@@ -318,7 +336,9 @@ bool try_spmm(const KernelCall& c) {
   // reduced by its own warp into a partial row; combine_partials_kernel folds the partials of a
   // row in segment order. Rows up to seg_len edges keep the strictly sequential (bit-exact vs the
   // single-threaded reference) reduction; B200_SPMM_SEG=0 disables segmentation altogether.
-  const SegPlan plan = csr_segments(g, walk, segment_length(E), s);
+  const int64_t warp_bytes = (lpr == 32) ? (int64_t)ch * vec * 128 : D * 4;
+  const int unroll = warp_bytes >= 1024 ? 1 : (warp_bytes >= 512 ? 2 : (warp_bytes >= 256 ? 4 : 8));
+  const SegPlan plan = csr_segments(g, walk, segment_length_for(E, D * 4, unroll), s);
   Scratch partial;
   if (plan.n_seg > 0) partial.alloc((size_t)plan.n_seg * D * 4, s);
   a.n_seg = plan.n_seg;

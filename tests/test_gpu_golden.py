@@ -78,12 +78,14 @@ def test_spmm_widths_vs_oracle(impl, d, path, monkeypatch):
     want = O.backward_copy_reduce("sum", og, 0, x, out, gout)
     got = impl.backward_copy_reduce("sum", gg, 0, x, out, gout, None, None)
     assert impl.last.startswith("spmm")
-    golden_util.check("bwd_copy_u_d%d" % d, got, want, "sum", grad=True)
+    # rows above the (size-dependent) segment length are regrouped: error relative to sum |terms|
+    gscale = O.backward_copy_reduce("sum", og, 0, x, out, np.abs(gout))
+    golden_util.check("bwd_copy_u_d%d" % d, got, want, "sum", grad=True, scale=gscale)
     out = O.binary_op_reduce("sum", "mul", og, 0, 2, x, w1, nd)
     want = O.backward_lhs_binary_op_reduce("sum", "mul", og, 0, 2, x, w1, out, gout)
     got = impl.backward_lhs_binary_op_reduce("sum", "mul", gg, 0, 2, x, w1, out, gout,
                                              None, None, None)
-    golden_util.check("bwd_u_mul_e_d%d" % d, got, want, "sum", grad=True)
+    golden_util.check("bwd_u_mul_e_d%d" % d, got, want, "sum", grad=True, scale=gscale * 1.5)
     if path == "tma" and d >= 33:
         assert impl.last == "spmm_tma"
 
