@@ -337,7 +337,7 @@ bool try_spmm(const KernelCall& c) {
   // row in segment order. Rows up to seg_len edges keep the strictly sequential (bit-exact vs the
   // single-threaded reference) reduction; B200_SPMM_SEG=0 disables segmentation altogether.
   const int64_t warp_bytes = (lpr == 32) ? (int64_t)ch * vec * 128 : D * 4;
-  const int unroll = warp_bytes >= 1024 ? 1 : (warp_bytes >= 512 ? 2 : (warp_bytes >= 256 ? 4 : 8));
+  const int unroll = warp_bytes >= 1024 ? 1 : (warp_bytes >= 256 ? 4 : 8);
   const SegPlan plan = csr_segments(g, walk, segment_length_for(E, D * 4, unroll), s);
   Scratch partial;
   if (plan.n_seg > 0) partial.alloc((size_t)plan.n_seg * D * 4, s);

@@ -292,10 +292,12 @@ spmm_kernel(const SpmmArgs a) {
 // Neighbours whose feature loads are issued back to back. Measured on B200
 // (profiles/microbench): a random-row gather runs fastest with ~64 KB of loads in flight per SM;
 // more (deeper unrolling) thrashes L1 and is up to 3x slower. With 32-64 resident warps that is
-// ~1-2 KB per warp, i.e. U = 1 once a warp moves >= 1 KB per neighbour.
+// ~1-2 KB per warp, i.e. U = 1 once a warp moves >= 1 KB per neighbour. Below that, 4 neighbours
+// in flight (products-shaped graph, D=100: U=2 -> 4 took the kernel from 5.72 to 4.89 ms; U=8 at
+// 256 B per neighbour was slower again, 4.66 -> 5.54 ms at D=47).
 constexpr int unroll_for(int vec, int ch) {
   const int bytes = ch * vec * 128;  // per neighbour per warp
-  return bytes >= 1024 ? 1 : (bytes >= 512 ? 2 : (bytes >= 256 ? 4 : 8));
+  return bytes >= 1024 ? 1 : (bytes >= 256 ? 4 : 8);
 }
 
 template <int VEC, int CH, int U>
