@@ -31,7 +31,8 @@ class Tensor(ctypes.Structure):
                 ("strides", ctypes.POINTER(ctypes.c_int64)), ("byte_offset", ctypes.c_uint64)]
 
 
-TensorP = ctypes.POINTER(Tensor)
+# tensors cross the boundary as plain addresses of DLTensor-layout structs (see ndarray.NDArray)
+TensorP = ctypes.c_void_p
 GraphHandle = ctypes.c_void_p
 
 # every symbol include/dgl_b200.h declares: name -> (restype, argtypes)

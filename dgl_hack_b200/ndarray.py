@@ -6,6 +6,7 @@ not contiguous, exactly as the reference's `.contiguous()`), and `null()` is the
 array the reference uses for "no mapping" (python/dgl/ndarray.py:97-106).
 """
 import ctypes
+import struct
 
 import torch
 
@@ -18,32 +19,52 @@ _DTYPES = {
 }
 
 
+_ARR = {}  # ndim -> ctypes array type of the packed view
+_SHP = {}  # ndim -> struct.Struct of the shape array
+_HDR = struct.Struct("<QiiiBBHQQQ")  # DLTensor: data, ctx{type,id}, ndim, dtype{code,bits,lanes},
+#                                       shape*, strides*, byte_offset  (48 bytes)
+
+
 class NDArray(object):
-    """A DLTensor-compatible view of a torch tensor (keeps the tensor alive)."""
+    """A DLTensor-compatible view of a torch tensor (keeps the tensor alive). The 48-byte header
+    and the shape array are packed into one buffer with struct (an order of magnitude cheaper
+    than building ctypes Structures on every kernel call)."""
+    __slots__ = ("tensor", "_buf", "_cbuf", "ptr")
 
     def __init__(self, tensor):
         tensor = tensor.contiguous()
         if tensor.dtype == torch.bfloat16:
             raise _lib.DGLError("bfloat16 tensors are not supported by the fp32 kernels")
         self.tensor = tensor
-        self._shape = (ctypes.c_int64 * max(tensor.dim(), 1))(*tensor.shape)
+        shape = tensor.shape
+        nd = len(shape)
+        buf = bytearray(48 + 8 * max(nd, 1))
+        self._buf = buf
+        arr_t = _ARR.get(nd)
+        if arr_t is None:
+            arr_t = _ARR[nd] = ctypes.c_char * len(buf)
+        self._cbuf = arr_t.from_buffer(buf)
+        addr = ctypes.addressof(self._cbuf)
         code, bits = _DTYPES[tensor.dtype]
         dev = tensor.device
-        self.handle = _lib.Tensor(
-            data=ctypes.c_void_p(tensor.data_ptr()),
-            ctx=_lib.Context(2 if dev.type == "cuda" else 1,
-                             (dev.index or 0) if dev.type == "cuda" else 0),
-            ndim=tensor.dim(), dtype=_lib.DataType(code, bits, 1),
-            shape=ctypes.cast(self._shape, ctypes.POINTER(ctypes.c_int64)),
-            strides=None, byte_offset=0)
+        cuda = dev.type == "cuda"
+        _HDR.pack_into(buf, 0, tensor.data_ptr(), 2 if cuda else 1,
+                       (dev.index or 0) if cuda else 0, nd, code, bits, 1, addr + 48, 0, 0)
+        if nd:
+            shp = _SHP.get(nd)
+            if shp is None:
+                shp = _SHP[nd] = struct.Struct("<%dq" % nd)
+            shp.pack_into(buf, 48, *shape)
+        self.ptr = addr  # passed as void* (DGLB200Tensor*)
 
     @property
     def shape(self):
         return tuple(self.tensor.shape)
 
     @property
-    def ptr(self):
-        return ctypes.byref(self.handle)
+    def handle(self):
+        """The view as a ctypes DLTensor struct (for callers that want field access)."""
+        return _lib.Tensor.from_buffer(self._buf)
 
 
 def zerocopy_to_dgl_ndarray(tensor):
