@@ -402,7 +402,6 @@ __global__ void __launch_bounds__(256) gat_fwd2_kernel(const Gat2Args b) {
     const Gat2Item t = gat2_item(b, w, grp, rpw, short_warps);
     const bool wide = t.wide;  // warp-uniform
     const int r = t.row;
-    const unsigned mask = wide ? 0xffffffffu : gat_group_mask(Gp);
     const int bw = wide ? 32 : Gp;            // ids fetched per batch
     const int bl = wide ? lane : li;          // this lane's slot in the batch
     const int stride = wide ? rpw : 1, off = wide ? grp : 0;
@@ -416,22 +415,27 @@ __global__ void __launch_bounds__(256) gat_fwd2_kernel(const Gat2Args b) {
     float4 acc[W4];
 #pragma unroll
     for (int k = 0; k < W4; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int base = 0; base < deg; base += bw) {
+    // warp-uniform trip counts + compile-time full-warp shuffle masks (a run-time member mask
+    // costs a MATCH/VOTE convergence sequence per shuffle); rows of a warp have similar degrees
+    // (degree-class schedule), so the lockstep wastes little
+    const int maxdeg = __reduce_max_sync(0xffffffffu, deg);
+    for (int base = 0; base < maxdeg; base += bw) {
       int src_l = 0, eid_l = 0;
       if (base + bl < deg) {
         src_l = __ldg(a.indices + beg + base + bl);
         eid_l = __ldg(a.eids + beg + base + bl);
       }
-      const int cnt = min(bw, deg - base);
-      for (int j0 = 0; j0 < cnt; j0 += 2 * stride) {
+      const int cnt = max(0, min(bw, deg - base));
+      const int cmax = min(bw, maxdeg - base);
+      for (int j0 = 0; j0 < cmax; j0 += 2 * stride) {
         float elv[2];
         float4 f[2][W4];
         int eid[2];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           const int j = j0 + u * stride + off;
-          const int src = __shfl_sync(mask, src_l, j & (bw - 1), bw);
-          eid[u] = __shfl_sync(mask, eid_l, j & (bw - 1), bw);
+          const int src = __shfl_sync(0xffffffffu, src_l, j & (bw - 1), bw);
+          eid[u] = __shfl_sync(0xffffffffu, eid_l, j & (bw - 1), bw);
           if (active && j < cnt) {
             elv[u] = __ldg(a.el + (int64_t)src * H + head);
             const float4* fp = reinterpret_cast<const float4*>(a.ft + (int64_t)src * a.D + coff);
@@ -504,7 +508,6 @@ __global__ void __launch_bounds__(256) gat_bwd2_kernel(const Gat2Args b) {
     const Gat2Item t = gat2_item(b, w, grp, rpw, short_warps);
     const bool wide = t.wide;
     const int u = t.row;
-    const unsigned mask = wide ? 0xffffffffu : gat_group_mask(Gp);
     const int bw = wide ? 32 : Gp;
     const int bl = wide ? lane : li;
     const int stride = wide ? rpw : 1, off = wide ? grp : 0;
@@ -523,17 +526,19 @@ __global__ void __launch_bounds__(256) gat_bwd2_kernel(const Gat2Args b) {
 #pragma unroll
       for (int k = 0; k < W4; ++k) ftv[k] = __ldg(fp + k);
     }
-    for (int base = 0; base < deg; base += bw) {
+    const int maxdeg = __reduce_max_sync(0xffffffffu, deg);  // uniform loops, see the forward
+    for (int base = 0; base < maxdeg; base += bw) {
       int dst_l = 0, eid_l = 0;
       if (base + bl < deg) {
         dst_l = __ldg(a.indices + beg + base + bl);
         eid_l = __ldg(a.eids + beg + base + bl);
       }
-      const int cnt = min(bw, deg - base);
-      for (int j0 = 0; j0 < cnt; j0 += stride) {
+      const int cnt = max(0, min(bw, deg - base));
+      const int cmax = min(bw, maxdeg - base);
+      for (int j0 = 0; j0 < cmax; j0 += stride) {
         const int j = j0 + off;
-        const int dst = __shfl_sync(mask, dst_l, j & (bw - 1), bw);
-        const int eid = __shfl_sync(mask, eid_l, j & (bw - 1), bw);
+        const int dst = __shfl_sync(0xffffffffu, dst_l, j & (bw - 1), bw);
+        const int eid = __shfl_sync(0xffffffffu, eid_l, j & (bw - 1), bw);
         const bool on = active && j < cnt;
         float dotp = 0.f, wgt = 0.f, gl = 0.f;
         if (on) {
@@ -564,7 +569,7 @@ __global__ void __launch_bounds__(256) gat_bwd2_kernel(const Gat2Args b) {
         }
         // the lanes of one head sit inside one group: xor offsets < lph never leave it
         for (int o = lph >> 1; o > 0; o >>= 1)
-          dotp = __fadd_rn(dotp, __shfl_xor_sync(mask, dotp, o));
+          dotp = __fadd_rn(dotp, __shfl_xor_sync(0xffffffffu, dotp, o));
         if (on && writer) {
           const float tv = __fmul_rn(__fmul_rn(dotp, wgt), gl);
           a.tbuf[(int64_t)eid * H + head] = tv;

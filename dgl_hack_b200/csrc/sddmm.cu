@@ -18,6 +18,7 @@
 //     edges and sources ascend, halving the gather traffic for wide rows.
 // dot reduces every head inside the lane group with a fixed butterfly (deterministic).
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "spmm_kernels.cuh"
@@ -97,6 +98,123 @@ __global__ void __launch_bounds__(256) sddmm_kernel(const SdArgs a) {
           part = __fadd_rn(part, __shfl_xor_sync(mask, part, o, L));
         if (vc < a.nvec && (sub & (a.lph - 1)) == 0)
           a.out[(int64_t)e * a.heads + vc / a.lph] = part;
+      }
+    }
+  }
+}
+
+// dot with the whole operand row in one pass of the lane group (nvec <= L): two edges per
+// iteration so that four row gathers are in flight per group.
+template <int VEC>
+__global__ void __launch_bounds__(256) sddmm_dot2_kernel(const SdArgs a) {
+  const int L = a.lpe;
+  const int sub = threadIdx.x & (L - 1);
+  const unsigned mask = (L == 32) ? 0xffffffffu
+                                  : (((1u << L) - 1u) << ((threadIdx.x & 31) / L * L));
+  const int64_t n_groups = (int64_t)gridDim.x * blockDim.x / L;
+  const bool lane_on = sub < a.nvec;
+  for (int64_t p0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / L; p0 < a.n_pos;
+       p0 += 2 * n_groups) {
+    int e[2];
+    Vec<VEC> x[2], y[2];
+    bool on[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int64_t p = p0 + k * n_groups;
+      on[k] = p < a.n_pos;
+      e[k] = 0;
+      if (on[k]) {
+        const int u = __ldg(a.u_of + p), v = __ldg(a.v_of + p);
+        e[k] = a.e_of ? __ldg(a.e_of + p) : (int)p;
+        const int pid = a.p_tgt == kSrc ? u : (a.p_tgt == kDst ? v : e[k]);
+        const int qid = a.q_tgt == kSrc ? u : (a.q_tgt == kDst ? v : e[k]);
+        if (lane_on) {
+          x[k] = ld_vec<VEC>(a.P + (int64_t)pid * a.row_len + sub * VEC);
+          y[k] = ld_vec<VEC>(a.Q + (int64_t)qid * a.row_len + sub * VEC);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      float part = 0.f;
+      if (on[k] && lane_on) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) part = __fadd_rn(part, __fmul_rn(x[k].v[j], y[k].v[j]));
+      }
+      // on[k] is uniform inside a lane group
+      if (on[k]) {
+        for (int o = a.lph >> 1; o > 0; o >>= 1)
+          part = __fadd_rn(part, __shfl_xor_sync(mask, part, o, L));
+        if (lane_on && (sub & (a.lph - 1)) == 0)
+          a.out[(int64_t)e[k] * a.heads + sub / a.lph] = part;
+      }
+    }
+  }
+}
+
+// dot over the destination-major walk: a lane group takes a CHUNK of consecutive positions, so
+// the destination's row (constant along a CSR row) is loaded once per run of equal destinations
+// and kept in registers; only the source rows are gathered per edge.
+constexpr int kDotChunk = 64;
+
+template <int VEC>
+__global__ void __launch_bounds__(256) sddmm_dot_rows_kernel(const SdArgs a) {
+  // Every loop below has a warp-uniform trip count and every shuffle names the full warp with a
+  // compile-time mask: a run-time member mask makes ptxas wrap each shuffle in a
+  // MATCH/REDUX/VOTE convergence sequence (measured: 58 -> instructions per edge, issue bound).
+  const int L = a.lpe;
+  const int sub = threadIdx.x & (L - 1);
+  const int64_t n_groups = (int64_t)gridDim.x * blockDim.x / L;
+  const int64_t n_chunks = (a.n_pos + kDotChunk - 1) / kDotChunk;
+  const int64_t n_iter = (n_chunks + n_groups - 1) / n_groups;
+  const bool lane_on = sub < a.nvec;
+  // the operand indexed by the destination is the cached one
+  const bool p_is_dst = a.p_tgt == kDst;
+  const float* row_tab = p_is_dst ? a.P : a.Q;   // indexed by v
+  const float* gat_tab = p_is_dst ? a.Q : a.P;   // indexed by u
+  int64_t ck = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / L;
+  for (int64_t it = 0; it < n_iter; ++it, ck += n_groups) {
+    const int64_t beg = ck * kDotChunk;
+    const int n = ck < n_chunks ? (int)min((int64_t)kDotChunk, a.n_pos - beg) : 0;
+    int prev_v = -1;
+    Vec<VEC> rv;
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) rv.v[j] = 0.f;
+    for (int b0 = 0; b0 < kDotChunk; b0 += L) {
+      int u_l = 0, v_l = 0, e_l = 0;
+      if (b0 + sub < n) {
+        u_l = __ldcs(a.u_of + beg + b0 + sub);  // index streams: evict first, keep the rows in L2
+        v_l = __ldcs(a.v_of + beg + b0 + sub);
+        e_l = __ldcs(a.e_of + beg + b0 + sub);
+      }
+      for (int i = 0; i < L; i += 2) {
+        Vec<VEC> x[2];
+        int v[2], e[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int u = __shfl_sync(0xffffffffu, u_l, i + k, L);
+          v[k] = __shfl_sync(0xffffffffu, v_l, i + k, L);
+          e[k] = __shfl_sync(0xffffffffu, e_l, i + k, L);
+          if (b0 + i + k < n && lane_on)
+            x[k] = ld_vec<VEC>(gat_tab + (int64_t)u * a.row_len + sub * VEC);
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const bool on = b0 + i + k < n;
+          if (on && v[k] != prev_v) {
+            prev_v = v[k];
+            if (lane_on) rv = ld_vec<VEC>(row_tab + (int64_t)prev_v * a.row_len + sub * VEC);
+          }
+          float part = 0.f;
+          if (on && lane_on) {
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) part = __fadd_rn(part, __fmul_rn(x[k].v[j], rv.v[j]));
+          }
+          for (int o = a.lph >> 1; o > 0; o >>= 1)
+            part = __fadd_rn(part, __shfl_xor_sync(0xffffffffu, part, o));
+          if (on && lane_on && (sub & (a.lph - 1)) == 0)
+            __stcs(a.out + (int64_t)e[k] * a.heads + sub / a.lph, part);
+        }
       }
     }
   }
@@ -210,7 +328,8 @@ bool try_sddmm(const KernelCall& c) {
 
   // traversal order
   const bool node_pair = (a.p_tgt != kEdge) && (a.q_tgt != kEdge) && (a.p_tgt != a.q_tgt);
-  const bool wide = row_len * 4 >= 256;
+  bool wide = row_len * 4 >= 256;
+  if (const char* w = std::getenv("B200_SDDMM_WALK")) wide = (w[0] == 'c' && w[1] == 's');  // csr|coo
   if (node_pair && wide) {
     a.u_of = g->in_s.indices;
     a.v_of = csr_rows(g, kWalkIn, s);
@@ -223,7 +342,18 @@ bool try_sddmm(const KernelCall& c) {
   const int64_t per_cta = 256 / lpe;
   const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((E + per_cta - 1) / per_cta,
                                                                 (int64_t)148 * 64));
-  if (vec == 4) launch_sd<4>(a, op, blocks, s);
+  if (op == kSdDot && nvec <= lpe && a.e_of != nullptr) {
+    const int64_t n_chunks = (E + kDotChunk - 1) / kDotChunk;
+    const int cblocks = (int)std::max<int64_t>(
+        1, std::min<int64_t>((n_chunks + per_cta - 1) / per_cta, (int64_t)148 * 64));
+    if (vec == 4) sddmm_dot_rows_kernel<4><<<cblocks, 256, 0, s>>>(a);
+    else if (vec == 2) sddmm_dot_rows_kernel<2><<<cblocks, 256, 0, s>>>(a);
+    else sddmm_dot_rows_kernel<1><<<cblocks, 256, 0, s>>>(a);
+  } else if (op == kSdDot && nvec <= lpe) {
+    if (vec == 4) sddmm_dot2_kernel<4><<<blocks, 256, 0, s>>>(a);
+    else if (vec == 2) sddmm_dot2_kernel<2><<<blocks, 256, 0, s>>>(a);
+    else sddmm_dot2_kernel<1><<<blocks, 256, 0, s>>>(a);
+  } else if (vec == 4) launch_sd<4>(a, op, blocks, s);
   else if (vec == 2) launch_sd<2>(a, op, blocks, s);
   else launch_sd<1>(a, op, blocks, s);
   B200_CUDA(cudaGetLastError());

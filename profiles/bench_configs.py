@@ -246,6 +246,73 @@ def c5(out):
         rec(out, "C5 products", "copy_src+sum fwd+bwd D=%d" % d, ms, 2 * e, 2 * nb)
 
 
+def ref_cpu(out):
+    """The unmodified reference CPU kernels (oracle/_ref/libdgl.so, all host cores) on the same
+    shapes, one warm-up + one timed call each: the 'Ref CPU ms' column of BASELINE.md section 5."""
+    import time
+    import numpy as np
+    sys.path.insert(0, ROOT)
+    from oracle import ref_capi as R
+    if not R.available():
+        print(json.dumps({"ref_cpu": "oracle/_ref/libdgl.so not present"}))
+        return
+    cores = os.cpu_count()
+
+    def t(fn):
+        fn()
+        t0 = time.perf_counter()
+        fn()
+        return (time.perf_counter() - t0) * 1e3
+
+    def row(cfg, op, ms, e):
+        r = {"config": cfg, "op": op, "ref_cpu_ms": round(ms, 2), "cores": cores,
+             "gedges_per_s": round(e / ms / 1e6, 5)}
+        out.append(r)
+        print(json.dumps(r), flush=True)
+
+    rs = np.random.RandomState(0)
+    f32 = lambda *sh: rs.uniform(-1, 1, sh).astype(np.float32)  # noqa: E731
+    # C1
+    n, e = 2708, 10556
+    g = R.RefGraph(n, rs.randint(0, n, e), rs.randint(0, n, e))
+    g.materialize()
+    X, O_ = R.RefArray(f32(n, 16)), R.RefArray(shape=(n, 16), dtype=np.float32)
+    row("C1 cora", "copy_src+sum D=16", t(lambda: R.copy_reduce("sum", g, 0, X, O_)), e)
+    # C3
+    n, e = 169343, 1166243
+    src, dst = bench.make_graph_coo(n, e, 0.4, 3, torch.device("cpu"))
+    g = R.RefGraph(n, src.numpy(), dst.numpy())
+    g.materialize()
+    X, O_ = R.RefArray(f32(n, 128)), R.RefArray(shape=(n, 128), dtype=np.float32)
+    row("C3 arxiv", "copy_src+sum D=128", t(lambda: R.copy_reduce("sum", g, 0, X, O_)), e)
+    FT, A = R.RefArray(f32(n, 8, 16)), R.RefArray(np.abs(f32(e, 8, 1)))
+    O3 = R.RefArray(shape=(n, 8, 16), dtype=np.float32)
+    row("C3 arxiv", "u_mul_e+sum [N,8,16]x[E,8,1]",
+        t(lambda: R.binary_op_reduce("sum", "mul", g, 0, 2, FT, A, O3)), e)
+    EL, ER = R.RefArray(f32(n, 8, 1)), R.RefArray(f32(n, 8, 1))
+    OE = R.RefArray(shape=(e, 8, 1), dtype=np.float32)
+    row("C3 arxiv", "u_add_v SDDMM [N,8,1]",
+        t(lambda: R.binary_op_reduce("none", "add", g, 0, 1, EL, ER, OE)), e)
+    # C4
+    n, e = 1885136, 5668682
+    g = R.RefGraph(n, rs.randint(0, n, e), rs.randint(0, n, e))
+    g.materialize()
+    M, O4 = R.RefArray(f32(e, 16)), R.RefArray(shape=(n, 16), dtype=np.float32)
+    row("C4 AM", "copy_e+sum [E,16]", t(lambda: R.copy_reduce("sum", g, 2, M, O4)), e)
+    # C5 at 1/8 scale (same generator family; the full graph takes minutes on the CPU path)
+    n, e = 2449029 // 8 // 64 * 64, 61859140 // 8
+    dev0, globals()["DEV"] = DEV, torch.device("cpu")
+    try:
+        src, dst = sbm_graph(n, e, 64, 0.85, 0.5, 5)
+    finally:
+        globals()["DEV"] = dev0
+    g = R.RefGraph(n, src.numpy(), dst.numpy())
+    g.materialize()
+    X, O5 = R.RefArray(f32(n, 100)), R.RefArray(shape=(n, 100), dtype=np.float32)
+    row("C5 products (1/8 scale)", "copy_src+sum D=100",
+        t(lambda: R.copy_reduce("sum", g, 0, X, O5)), e)
+
+
 def main():
     global L2
     ap = argparse.ArgumentParser()
@@ -255,7 +322,7 @@ def main():
     L2 = torch.cuda.get_device_properties(DEV).L2_cache_size
     out = []
     for name in args.only.split(","):
-        {"c1": c1, "c2": c2, "c3": c3, "c4": c4, "c5": c5}[name](out)
+        {"ref": ref_cpu, "c1": c1, "c2": c2, "c3": c3, "c4": c4, "c5": c5}[name](out)
         torch.cuda.empty_cache()
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(out, open(args.out, "w"), indent=1)
