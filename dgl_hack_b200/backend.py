@@ -47,6 +47,27 @@ def _reduce_grad(grad, shape):
     return grad.sum(dim=dims, keepdim=True).view(shape)
 
 
+def _edge_scalar_grad(kreducer, binary_op, graph, tgt, other_tgt, data, other, grad_out, maps,
+                      feat_shape):
+    """Gradient of an EDGE operand that broadcasts along the last feature axis under mul + sum
+    (GAT's u_mul_e with ft [N,H,F] x a [E,H,1]): the reference materialises the unreduced
+    gradient [E,H,F] and lets torch sum it over F (tensor.py:345-360, _reduce_grad); the same
+    values are one dot product per (edge, head) of the other operand's row with grad_out[dst], so
+    the [E,H,F] temporary (E*H*F*4 bytes written and read back) never exists. Returns None when
+    the shapes are not of that form."""
+    if kreducer != "sum" or binary_op != "mul" or tgt != EDGE or other_tgt not in (SRC, DST):
+        return None
+    if any(m is not None for pair in maps for m in pair):
+        return None
+    ds, os_ = tuple(data.shape[1:]), tuple(other.shape[1:])
+    if (os_ != tuple(feat_shape) or len(ds) != len(os_) or len(ds) == 0 or ds[:-1] != os_[:-1]
+            or ds[-1] != 1 or os_[-1] == 1):
+        return None
+    out = grad_out.new_empty((data.shape[0],) + ds[:-1])
+    K.binary_op_reduce("none", "dot", graph, other_tgt, DST, other, grad_out, out)
+    return out.unsqueeze(-1)
+
+
 class BinaryReduce(th.autograd.Function):
     @staticmethod
     def forward(ctx, reducer, binary_op, graph, lhs, rhs, lhs_data, rhs_data, out_data,
@@ -79,13 +100,20 @@ class BinaryReduce(th.autograd.Function):
             grad_out = grad_out / degs
         grad_out = grad_out.contiguous()
         grad_lhs = grad_rhs = None
+        maps = (lhs_map, rhs_map, out_map)
         if ctx.needs_input_grad[5]:
+            grad_lhs = _edge_scalar_grad(kreducer, binary_op, graph, lhs, rhs, lhs_data, rhs_data,
+                                         grad_out, maps, feat_shape)
+        if ctx.needs_input_grad[5] and grad_lhs is None:
             grad_lhs = grad_out.new_empty((lhs_data.shape[0],) + feat_shape)
             K.backward_lhs_binary_op_reduce(kreducer, binary_op, graph, lhs, rhs, lhs_data,
                                             rhs_data, out_data, grad_out, grad_lhs, lhs_map[1],
                                             rhs_map[1], out_map[1])
             grad_lhs = _reduce_grad(grad_lhs, lhs_data.shape)
         if ctx.needs_input_grad[6]:
+            grad_rhs = _edge_scalar_grad(kreducer, binary_op, graph, rhs, lhs, rhs_data, lhs_data,
+                                         grad_out, maps, feat_shape)
+        if ctx.needs_input_grad[6] and grad_rhs is None:
             grad_rhs = grad_out.new_empty((rhs_data.shape[0],) + feat_shape)
             K.backward_rhs_binary_op_reduce(kreducer, binary_op, graph, lhs, rhs, lhs_data,
                                             rhs_data, out_data, grad_out, grad_rhs, lhs_map[1],

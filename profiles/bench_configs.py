@@ -144,6 +144,22 @@ def c3(out):
     rec(out, "C3 arxiv", "fused GAT fwd+bwd", ms, 2 * e,
         2 * (gather_bytes(n, e, H * Fw) * 2 + e * 8 + e * H * 8 + n * H * Fw * 4), "3 kernels")
 
+    def gat_builtin_fb():
+        # GATConv as the reference composes it from builtins (gatconv.py:122-170)
+        ev = F.binary_reduce("none", "add", g, 0, 1, elg, erg, e)
+        ev = torch.nn.functional.leaky_relu(ev, 0.2)
+        smax = F.copy_reduce("max", g, 2, ev, n)
+        ev = torch.exp(F.binary_reduce("none", "sub", g, 2, 1, ev, smax, e))
+        ssum = F.copy_reduce("sum", g, 2, ev, n)
+        att = F.binary_reduce("none", "div", g, 2, 1, ev, ssum, e)
+        o = F.binary_reduce("sum", "mul", g, 0, 2, ftg, att, n)
+        o.backward(gout)
+        ftg.grad = elg.grad = erg.grad = None
+    ms = timeit(gat_builtin_fb)
+    rec(out, "C3 arxiv", "GAT attention from builtins fwd+bwd (edge_softmax with max)", ms, 2 * e,
+        2 * (gather_bytes(n, e, H * Fw) * 2 + e * 8 + e * H * 8 + n * H * Fw * 4),
+        "6 forward + 7 backward kernel calls + torch elementwise")
+
 
 def c4(out):
     n, e, R, d = 1885136, 5668682, 133, 16

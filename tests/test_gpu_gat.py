@@ -97,3 +97,27 @@ def test_fused_gat_rejects_unsupported_width():
     with pytest.raises(B.DGLError, match="power of two"):
         K.fused_gat_kernel(g, z(4, 2, 6), z(4, 2, 1), z(4, 2, 1), z(4, 2, 1), z(3, 2, 1),
                            z(4, 2, 6), 0.2)
+
+
+@pytest.mark.parametrize("H,F", [(8, 16), (1, 64), (3, 5)])
+def test_edge_scalar_gradient_is_fused_dot(H, F):
+    """backend.binary_reduce backward w.r.t. a [E,H,1] edge operand of u_mul_e+sum: the fused
+    per-(edge, head) dot equals the reference route (unreduced [E,H,F] gradient, then a sum over F)."""
+    import torch
+    import dgl_hack_b200 as B
+    from dgl_hack_b200 import backend as F_
+    from dgl_hack_b200 import kernel as K
+    n, ne = 1500, 20000
+    src, dst = cases.powerlaw_graph(n, n, ne, 0.5, 9)
+    g = B.GraphIndex.from_coo(n, n, src, dst)
+    torch.manual_seed(1)
+    ft = (torch.rand(n, H, F, device="cuda") * 2 - 1)
+    a = torch.rand(ne, H, 1, device="cuda").requires_grad_(True)
+    gout = torch.rand(n, H, F, device="cuda") * 2 - 1
+    out = F_.binary_reduce("sum", "mul", g, 0, 2, ft, a, n)
+    out.backward(gout)
+    unreduced = torch.empty(ne, H, F, device="cuda")
+    K.backward_rhs_binary_op_reduce("sum", "mul", g, 0, 2, ft, a.detach(), out.detach(), gout,
+                                    unreduced)
+    want = unreduced.sum(dim=-1, keepdim=True)
+    torch.testing.assert_close(a.grad, want, rtol=1e-5, atol=1e-5 * F)
