@@ -83,13 +83,24 @@ class Partition(object):
                 continue
             need = torch.unique(src[mine_src & (part[dst] == q)])  # ascending = peer's halo order
             p.send_idx.append(g2l[need])
+        p.send_counts = [int(t.numel()) for t in p.send_idx]
+        p.send_cat = torch.cat(p.send_idx) if world > 1 else p.send_idx[0]
         return p
+
+    def _a2a(self):
+        """One all-to-all-v instead of 2(k-1) grouped sends/recvs where the backend has it (NCCL)."""
+        return self.world > 1 and dist.get_backend() == "nccl"
 
     # ---- exchanges (grouped isend/irecv: works on gloo and NCCL)
     def start_forward_exchange(self, x_inner):
         """Posts the halo exchange; returns (requests, x_halo, keepalive)."""
         d = x_inner.shape[1:]
         x_halo = x_inner.new_empty((self.n_halo,) + tuple(d))
+        if self._a2a():
+            buf = x_inner.index_select(0, self.send_cat)  # one pack kernel for all peers
+            work = dist.all_to_all_single(x_halo, buf, output_split_sizes=self.halo_counts,
+                                          input_split_sizes=self.send_counts, async_op=True)
+            return [work], x_halo, [buf]
         ops, keep, off = [], [], 0
         for q in range(self.world):
             cnt = self.halo_counts[q]
@@ -107,6 +118,12 @@ class Partition(object):
     def start_backward_exchange(self, g_halo):
         """Sends halo gradients back to their owners; returns (requests, per-peer recv buffers)."""
         d = g_halo.shape[1:]
+        if self._a2a():
+            buf = g_halo.new_empty((int(self.send_cat.numel()),) + tuple(d))
+            work = dist.all_to_all_single(buf, g_halo.contiguous(),
+                                          output_split_sizes=self.send_counts,
+                                          input_split_sizes=self.halo_counts, async_op=True)
+            return [work], buf
         ops, recv, off = [], [], 0
         for q in range(self.world):
             n = self.send_idx[q].numel()
@@ -121,6 +138,17 @@ class Partition(object):
             off += cnt
         reqs = dist.batch_isend_irecv(ops) if ops else []
         return reqs, recv
+
+    def reduce_received(self, g_inner, recv):
+        """Adds the halo gradients received from all peers (rows in send_cat order) into their
+        owners' rows. Overridden by PartitionedGraph with a deterministic segment-sum kernel."""
+        off = 0
+        for q in range(self.world):
+            n = self.send_counts[q]
+            if n:
+                g_inner.index_add_(0, self.send_idx[q], recv[off:off + n])
+            off += n
+        return g_inner
 
     def exchange_bytes(self, row_bytes):
         sent = sum(int(s.numel()) for s in self.send_idx) * row_bytes
@@ -154,9 +182,12 @@ class _HaloCopySum(torch.autograd.Function):
         g_inner = agg_t("inner", grad_out)     # overlaps the exchange
         for r in reqs:
             r.wait()
-        for q in range(part.world):            # fixed peer order; ids unique within a peer
-            if recv[q] is not None:
-                g_inner.index_add_(0, part.send_idx[q], recv[q])
+        if torch.is_tensor(recv):              # all-to-all path: one buffer in send_cat order
+            g_inner = part.reduce_received(g_inner, recv)
+        else:
+            for q in range(part.world):        # fixed peer order; ids unique within a peer
+                if recv[q] is not None:
+                    g_inner.index_add_(0, part.send_idx[q], recv[q])
         return None, None, None, g_inner
 
 
@@ -172,6 +203,14 @@ class PartitionedGraph(object):
         sh, dh = part.edges_halo
         self.g_inner = GraphIndex.from_coo(part.n_inner, part.n_inner, si, di, device)
         self.g_halo = GraphIndex.from_coo(max(part.n_halo, 1), part.n_inner, sh, dh, device)
+        # received halo gradients -> owners: row i of the receive buffer belongs to inner node
+        # send_cat[i]; as a graph (edge i -> node send_cat[i]) the reduction is copy_e + sum, one
+        # deterministic kernel instead of k-1 index_add_ launches with atomics
+        self.g_rev = None
+        if part.world > 1 and part.send_cat.numel() > 0:
+            sc = part.send_cat.to(device)
+            self.g_rev = GraphIndex.from_coo(part.n_inner, part.n_inner, sc, sc, device)
+            part.reduce_received = self._reduce_received
 
     def _agg(self, which, x):
         from . import kernel as K
@@ -188,6 +227,12 @@ class PartitionedGraph(object):
         grad = grad_out.new_empty((rows,) + tuple(grad_out.shape[1:]))
         K.backward_copy_reduce("sum", g, 0, grad, grad_out, grad_out, grad)
         return grad[:n_src]
+
+    def _reduce_received(self, g_inner, recv):
+        from . import kernel as K
+        add = g_inner.new_empty(g_inner.shape)
+        K.copy_reduce("sum", self.g_rev, 2, recv, add)
+        return g_inner.add_(add)
 
     def copy_src_sum(self, x_inner):
         """Halo-exchanging `update_all(copy_src, sum)` for this rank's inner nodes."""

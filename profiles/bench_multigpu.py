@@ -50,6 +50,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--breakdown", action="store_true",
+                    help="also time every phase alone (synchronised; no overlap)")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
@@ -106,6 +108,42 @@ def main():
     torch.cuda.synchronize()
     ms = torch.tensor([a.elapsed_time(b) / args.steps], device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    phases = None
+    if args.breakdown:
+        def t_ms(fn, reps=5):
+            fn()
+            torch.cuda.synchronize()
+            dist.barrier()
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record()
+            for _ in range(reps):
+                fn()
+            b_.record()
+            torch.cuda.synchronize()
+            return a_.elapsed_time(b_) / reps
+        xd = x.detach()
+        g_halo = torch.rand(p.n_halo, d, device=dev)
+
+        def ex_fwd():
+            reqs, xh, keep = p.start_forward_exchange(xd)
+            for r in reqs:
+                r.wait()
+
+        def ex_bwd():
+            reqs, recv = p.start_backward_exchange(g_halo)
+            for r in reqs:
+                r.wait()
+            return recv
+        recv = ex_bwd()
+        xh = torch.rand(max(p.n_halo, 1), d, device=dev)
+        names = ["exchange_fwd", "agg_inner", "agg_halo", "agg_t_halo", "exchange_bwd",
+                 "agg_t_inner", "reduce_received"]
+        fns = [ex_fwd, lambda: pg._agg("inner", xd), lambda: pg._agg("halo", xh[:max(p.n_halo, 1)]),
+               lambda: pg._agg_t("halo", gout), ex_bwd, lambda: pg._agg_t("inner", gout),
+               lambda: p.reduce_received(torch.zeros_like(xd), recv) if torch.is_tensor(recv) else None]
+        vals = torch.tensor([t_ms(f) for f in fns], device=dev)
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        phases = {k: round(v, 4) for k, v in zip(names, vals.tolist())}
     stats = torch.tensor([p.local_edges, p.cut_edges, p.n_inner, p.n_halo], device=dev,
                          dtype=torch.float64)
     allstats = [torch.zeros_like(stats) for _ in range(world)]
@@ -124,7 +162,8 @@ def main():
                 "cut_fraction": round(float(st[:, 1].sum() / st[:, 0].sum()), 4),
                 "max_local_edges": int(st[:, 0].max()), "max_halo_nodes": int(st[:, 3].max()),
                 "halo_bytes_per_step_per_rank_max": int(st[:, 3].max()) * d * 4 * 2,
-                "steps": args.steps, "warmup": args.warmup, "check": check}
+                "steps": args.steps, "warmup": args.warmup, "check": check,
+                "phase_ms_max_over_ranks": phases}
         print(json.dumps(line), flush=True)
         if args.out:
             os.makedirs(os.path.dirname(args.out), exist_ok=True)
