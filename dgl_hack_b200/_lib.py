@@ -95,6 +95,12 @@ SYMBOLS = {
     "DGLB200RgcnLayer1": (_c.c_int, [GraphHandle, TensorP, TensorP, TensorP, TensorP,
                                      _c.c_void_p]),
     "DGLB200RgcnLayer1Backward": (_c.c_int, [GraphHandle] + [TensorP] * 6 + [_c.c_void_p]),
+    "DGLB200PeerAlloc": (_c.c_int, [_c.c_int64, _c.c_int, _c.POINTER(_c.c_void_p), _c.c_void_p]),
+    "DGLB200PeerOpen": (_c.c_int, [_c.c_void_p, _c.c_int, _c.POINTER(_c.c_void_p)]),
+    "DGLB200PeerClose": (_c.c_int, [_c.c_void_p]),
+    "DGLB200PeerFree": (_c.c_int, [_c.c_void_p]),
+    "DGLB200HaloPush": (_c.c_int, [_c.c_void_p, _c.c_int64, _c.c_int, _c.c_void_p, _c.c_void_p,
+                                   _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p]),
     "DGLB200KernelCopyReduceMean": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP,
                                                _c.c_void_p]),
     "DGLB200KernelBackwardCopyReduce": (_c.c_int, [_c.c_char_p, GraphHandle, _c.c_int, TensorP,

@@ -1,0 +1,146 @@
+// Peer-memory halo exchange over NVLink: instead of pack -> NCCL send/recv -> unpack,
+// ONE kernel reads the rows a peer needs from this rank's feature matrix and stores them straight
+// into that peer's halo buffer (CUDA IPC mapping of a cudaMalloc'ed buffer; P2P stores travel over
+// NVLink / NVSwitch at full rate and need no staging copy). The reference has no counterpart (its
+// multi-GPU story is DDP over sampled mini-batches); the partition semantics follow
+// python/dgl/transform.py:551-640 (partition_graph_with_halo).
+//
+// Synchronisation is the caller's (dgl_hack_b200/partition.py): pushes go to alternating buffers
+// and every exchange ends with one stream-ordered NCCL barrier, so a buffer is rewritten only
+// after every rank has passed the barrier that follows its readers.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kMaxPeers = 16;
+
+struct PushArgs {
+  const float* x;          // [*, D] local rows
+  const int32_t* rows;     // [total] local row of every pushed row (NULL = identity)
+  int64_t D;
+  int n_peers;
+  float* peer[kMaxPeers];      // base of each destination buffer (peer-mapped or local)
+  int64_t beg[kMaxPeers + 1];  // rows [beg[q], beg[q+1]) of the push list go to peer q
+  int64_t dst_row[kMaxPeers];  // first destination row inside peer q's buffer
+  int64_t rot;                 // the push list is walked from here (wrapping): ranks start at
+                               // different peers, so no peer's NVLink ingress sees all senders at once
+};
+
+// one warp per pushed row; 128-bit moves when the row pitch allows it
+template <int VEC>
+__global__ void __launch_bounds__(256) halo_push_kernel(const PushArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t total = a.beg[a.n_peers];
+  const int nvec = (int)(a.D / VEC);
+  for (int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < total;
+       j += n_warps) {
+    int64_t i = j + a.rot;
+    if (i >= total) i -= total;
+    int q = 0;
+    while (i >= a.beg[q + 1]) ++q;
+    const int64_t r = a.rows ? (int64_t)__ldg(a.rows + i) : i;
+    const float* src = a.x + r * a.D;
+    float* dst = a.peer[q] + (a.dst_row[q] + (i - a.beg[q])) * a.D;
+    for (int c = lane; c < nvec; c += 32) {
+      if (VEC == 4) {
+        reinterpret_cast<float4*>(dst)[c] = __ldg(reinterpret_cast<const float4*>(src) + c);
+      } else {
+        dst[c] = __ldg(src + c);
+      }
+    }
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+#define API_BEGIN() try {
+#define API_END()                                     \
+  }                                                   \
+  catch (const ::b200::ApiError& e) {                 \
+    ::b200::set_last_error(e.msg);                    \
+    return -1;                                        \
+  }                                                   \
+  catch (const std::exception& e) {                   \
+    ::b200::set_last_error(e.what());                 \
+    return -1;                                        \
+  }                                                   \
+  return 0;
+
+extern "C" {
+
+int DGLB200PeerAlloc(int64_t bytes, int device, void** ptr, unsigned char handle[64]) {
+  API_BEGIN();
+  B200_CHECK(ptr && handle && bytes > 0, "DGLB200PeerAlloc: bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  B200_CUDA(cudaSetDevice(device));
+  B200_CUDA(cudaMalloc(ptr, (size_t)bytes));
+  cudaIpcMemHandle_t h;
+  B200_CUDA(cudaIpcGetMemHandle(&h, *ptr));
+  std::copy(reinterpret_cast<unsigned char*>(&h), reinterpret_cast<unsigned char*>(&h) + 64, handle);
+  API_END();
+}
+
+int DGLB200PeerOpen(const unsigned char handle[64], int device, void** ptr) {
+  API_BEGIN();
+  B200_CHECK(ptr && handle, "DGLB200PeerOpen: bad argument");
+  B200_CUDA(cudaSetDevice(device));
+  cudaIpcMemHandle_t h;
+  std::copy(handle, handle + 64, reinterpret_cast<unsigned char*>(&h));
+  B200_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  API_END();
+}
+
+int DGLB200PeerClose(void* ptr) {
+  API_BEGIN();
+  if (ptr) B200_CUDA(cudaIpcCloseMemHandle(ptr));
+  API_END();
+}
+
+int DGLB200PeerFree(void* ptr) {
+  API_BEGIN();
+  if (ptr) B200_CUDA(cudaFree(ptr));
+  API_END();
+}
+
+// Pushes rows of x into the peers' buffers: row i of the push list (local row rows[i], or i when
+// rows is NULL) with beg[q] <= i < beg[q+1] lands in row dst_row[q] + (i - beg[q]) of peer[q].
+// peer / beg / dst_row are HOST arrays (n_peers <= 16), rows is a device array.
+int DGLB200HaloPush(const float* x, int64_t D, int n_peers, void* const* peer, const int64_t* beg,
+                    const int64_t* dst_row, const int32_t* rows, int first_peer, int device,
+                    void* stream) {
+  API_BEGIN();
+  B200_CHECK(n_peers >= 0 && n_peers <= kMaxPeers, "DGLB200HaloPush: at most 16 peers");
+  B200_CHECK(D > 0 && peer && beg && dst_row, "DGLB200HaloPush: bad argument");
+  PushArgs a{};
+  a.x = x;
+  a.rows = rows;
+  a.D = D;
+  a.n_peers = n_peers;
+  bool al = (reinterpret_cast<uintptr_t>(x) % 16 == 0) && (D % 4 == 0);
+  for (int q = 0; q < n_peers; ++q) {
+    a.peer[q] = static_cast<float*>(peer[q]);
+    a.beg[q] = beg[q];
+    a.dst_row[q] = dst_row[q];
+    al = al && (reinterpret_cast<uintptr_t>(peer[q]) % 16 == 0);
+  }
+  a.beg[n_peers] = beg[n_peers];
+  const int64_t total = beg[n_peers];
+  a.rot = (first_peer >= 0 && first_peer < n_peers) ? beg[first_peer] : 0;
+  if (a.rot >= total) a.rot = 0;
+  if (total == 0) return 0;
+  B200_CUDA(cudaSetDevice(device));
+  const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((total + 7) / 8, 148 * 16));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (al) halo_push_kernel<4><<<blocks, 256, 0, s>>>(a);
+  else halo_push_kernel<1><<<blocks, 256, 0, s>>>(a);
+  B200_CUDA(cudaGetLastError());
+  note_kernel("halo_push", 1);
+  API_END();
+}
+
+}  // extern "C"

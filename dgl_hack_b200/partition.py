@@ -19,6 +19,8 @@ whose sources are local:
 Everything here is torch + torch.distributed and device agnostic, so the exchange logic is tested
 on CPU with gloo (world_size 2); the aggregation itself is the CUDA kernel library.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -89,12 +91,16 @@ class Partition(object):
 
     def _a2a(self):
         """One all-to-all-v instead of 2(k-1) grouped sends/recvs where the backend has it (NCCL)."""
-        return self.world > 1 and dist.get_backend() == "nccl"
+        return self.world > 1 and dist.is_initialized() and dist.get_backend() == "nccl"
 
     # ---- exchanges (grouped isend/irecv: works on gloo and NCCL)
     def start_forward_exchange(self, x_inner):
         """Posts the halo exchange; returns (requests, x_halo, keepalive)."""
         d = x_inner.shape[1:]
+        peer = getattr(self, "peer", None)
+        if peer is not None and peer.usable(x_inner):
+            work, x_halo = peer.forward(x_inner)
+            return [work], x_halo, [x_inner]
         x_halo = x_inner.new_empty((self.n_halo,) + tuple(d))
         if self._a2a():
             buf = x_inner.index_select(0, self.send_cat)  # one pack kernel for all peers
@@ -118,6 +124,10 @@ class Partition(object):
     def start_backward_exchange(self, g_halo):
         """Sends halo gradients back to their owners; returns (requests, per-peer recv buffers)."""
         d = g_halo.shape[1:]
+        peer = getattr(self, "peer", None)
+        if peer is not None and peer.usable(g_halo):
+            work, buf = peer.backward(g_halo)
+            return [work], buf
         if self._a2a():
             buf = g_halo.new_empty((int(self.send_cat.numel()),) + tuple(d))
             work = dist.all_to_all_single(buf, g_halo.contiguous(),
@@ -195,10 +205,27 @@ class PartitionedGraph(object):
     """A Partition bound to the CUDA kernels: two GraphIndex objects (inner-source and
     halo-source edges, destinations = inner nodes) and the halo-exchanging aggregation."""
 
-    def __init__(self, part, device):
+    def __init__(self, part, device, halo="auto", max_feat=256):
+        """halo: "peer" = peer-memory pushes over NVLink (PeerExchange; needs all ranks on one
+        node), "nccl" = all-to-all-v, "auto" = peer when the environment allows it
+        (B200_HALO overrides)."""
         from .graph_index import GraphIndex
         self.part = part
         self.device = torch.device(device)
+        halo = os.environ.get("B200_HALO", halo)
+        part.peer = None
+        if part.world > 1 and halo in ("auto", "peer") and dist.is_initialized() and \
+                dist.get_backend() == "nccl":
+            ok = torch.ones(1, device=self.device)
+            try:
+                px = PeerExchange(part, self.device, max_feat)
+            except Exception:
+                if halo == "peer":
+                    raise
+                px, ok = None, torch.zeros(1, device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            part.peer = px if ok.item() > 0 else None
+        self.halo_path = "peer" if part.peer is not None else ("nccl" if part.world > 1 else "none")
         si, di = part.edges_inner
         sh, dh = part.edges_halo
         self.g_inner = GraphIndex.from_coo(part.n_inner, part.n_inner, si, di, device)
@@ -237,3 +264,111 @@ class PartitionedGraph(object):
     def copy_src_sum(self, x_inner):
         """Halo-exchanging `update_all(copy_src, sum)` for this rank's inner nodes."""
         return _HaloCopySum.apply(self.part, self._agg, self._agg_t, x_inner)
+
+
+class _RawCuda(object):
+    """Exposes a cudaMalloc'ed buffer to torch (torch.as_tensor reads __cuda_array_interface__)."""
+
+    def __init__(self, ptr, n_floats):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4",
+                                         "data": (ptr, False), "version": 3, "strides": None}
+
+
+class PeerExchange(object):
+    """Halo exchange through peer memory (csrc/peer.cu): every rank owns two forward buffers
+    (halo rows it receives) and two backward buffers (halo gradients it receives), mapped into
+    all other ranks of the node with CUDA IPC. An exchange is ONE kernel on the sender (gather
+    the rows a peer needs and store them straight into its buffer over NVLink) followed by one
+    stream-ordered NCCL barrier; buffers alternate, so a buffer is rewritten only after every
+    rank has passed the barrier that follows its last readers."""
+
+    def __init__(self, part, device, max_feat):
+        import ctypes
+        from ._lib import LIB, check_call
+        self.part, self.device, self.max_feat = part, torch.device(device), int(max_feat)
+        self._lib, self._check, self._ct = LIB, check_call, ctypes
+        k, me = part.world, part.rank
+        dev_index = self.device.index or 0
+        self.total_send = int(part.send_cat.numel())
+        sizes = [max(part.n_halo, 1) * max_feat] * 2 + [max(self.total_send, 1) * max_feat] * 2
+        self._own, handles = [], torch.zeros(4, 64, dtype=torch.uint8)
+        for i, n in enumerate(sizes):
+            ptr = ctypes.c_void_p()
+            h = (ctypes.c_ubyte * 64)()
+            check_call(LIB.DGLB200PeerAlloc(int(n) * 4, dev_index, ctypes.byref(ptr), h))
+            self._own.append(ptr.value)
+            handles[i] = torch.tensor(list(h), dtype=torch.uint8)
+        self._views = [torch.as_tensor(_RawCuda(p, n), device=self.device)
+                       for p, n in zip(self._own, sizes)]
+        hd = handles.to(self.device)
+        allh = [torch.empty_like(hd) for _ in range(k)]
+        dist.all_gather(allh, hd)
+        counts = torch.tensor(part.halo_counts, dtype=torch.int64, device=self.device)
+        allc = [torch.empty_like(counts) for _ in range(k)]
+        dist.all_gather(allc, counts)
+        need = torch.stack(allc).cpu()          # need[q][r] = rows rank q receives from rank r
+        self._mapped = []
+        self._peer = [[0] * k for _ in range(4)]  # [buffer][rank] -> device pointer
+        for q in range(k):
+            hq = allh[q].cpu()
+            for i in range(4):
+                if q == me:
+                    self._peer[i][q] = self._own[i]
+                    continue
+                ptr = ctypes.c_void_p()
+                raw = (ctypes.c_ubyte * 64)(*hq[i].tolist())
+                check_call(LIB.DGLB200PeerOpen(raw, dev_index, ctypes.byref(ptr)))
+                self._peer[i][q] = ptr.value
+                self._mapped.append(ptr.value)
+        i64 = ctypes.c_int64
+        # forward: my rows for q land after the blocks of the owners below me in q's halo order
+        self._f_beg = (i64 * (k + 1))(*([0] + torch.cumsum(torch.tensor(part.send_counts), 0).tolist()))
+        self._f_dst = (i64 * k)(*[int(need[q, :me].sum()) for q in range(k)])
+        # backward: my halo block of owner q lands after the blocks of the senders below me in
+        # q's send order (q sends need[r][q] rows to rank r)
+        self._b_beg = (i64 * (k + 1))(*([0] + torch.cumsum(torch.tensor(part.halo_counts), 0).tolist()))
+        self._b_dst = (i64 * k)(*[int(need[:me, q].sum()) for q in range(k)])
+        self._rows = part.send_cat.to(self.device, torch.int32).contiguous()
+        self._flag = torch.zeros(1, device=self.device)
+        self._side = torch.cuda.Stream(device=self.device)
+        self._turn = [0, 0]
+        self._k = k
+
+    def usable(self, x):
+        return x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and \
+            x.shape[1] <= self.max_feat and x.shape[1] % 4 == 0 and x.is_contiguous() and \
+            x.data_ptr() % 16 == 0  # 128-bit peer stores only; other widths go through NCCL
+
+    def _push(self, x, which, beg, dst, rows):
+        ct = self._ct
+        b = 2 * which + self._turn[which]
+        self._turn[which] ^= 1
+        cur = torch.cuda.current_stream(self.device)
+        self._side.wait_stream(cur)
+        with torch.cuda.stream(self._side):
+            peers = (ct.c_void_p * self._k)(*self._peer[b])
+            self._check(self._lib.DGLB200HaloPush(
+                ct.c_void_p(x.data_ptr()), int(x.shape[1]), self._k, peers, beg, dst,
+                ct.c_void_p(rows.data_ptr()) if rows is not None else None,
+                (self.part.rank + 1) % self._k, self.device.index or 0, ct.c_void_p(self._side.cuda_stream)))
+            x.record_stream(self._side)
+            work = dist.all_reduce(self._flag, async_op=True)  # barrier: all pushes have landed
+        return work, self._views[b]
+
+    def forward(self, x_inner):
+        work, buf = self._push(x_inner, 0, self._f_beg, self._f_dst, self._rows)
+        d = x_inner.shape[1]
+        return work, buf[: self.part.n_halo * d].view(self.part.n_halo, d)
+
+    def backward(self, g_halo):
+        work, buf = self._push(g_halo, 1, self._b_beg, self._b_dst, None)
+        d = g_halo.shape[1]
+        return work, buf[: self.total_send * d].view(self.total_send, d)
+
+    def close(self):
+        torch.cuda.synchronize(self.device)
+        for p in self._mapped:
+            self._lib.DGLB200PeerClose(self._ct.c_void_p(p))
+        for p in self._own:
+            self._lib.DGLB200PeerFree(self._ct.c_void_p(p))
+        self._mapped, self._own = [], []

@@ -273,6 +273,25 @@ int DGLB200KernelCopyReduceMean(DGLB200GraphHandle graph, int target,
 const char* DGLB200LastKernel(void);
 int64_t DGLB200LaunchCount(void);
 
+/* ---- multi-GPU halo exchange over peer memory (no reference PackedFunc; the partition semantics
+ *      are partition_graph_with_halo's, python/dgl/transform.py:551-640) ---- */
+
+/* cudaMalloc + cudaIpcGetMemHandle: a buffer other ranks of the same node can map. */
+int DGLB200PeerAlloc(int64_t bytes, int device, void** ptr, unsigned char handle[64]);
+/* cudaIpcOpenMemHandle of another rank's buffer (peer access enabled lazily). */
+int DGLB200PeerOpen(const unsigned char handle[64], int device, void** ptr);
+int DGLB200PeerClose(void* ptr);
+int DGLB200PeerFree(void* ptr);
+/* Fused pack + send: row i of the push list (local row rows[i] of x, or row i when rows is NULL),
+ * beg[q] <= i < beg[q+1], is stored into row dst_row[q] + (i - beg[q]) of peer[q] (row pitch D
+ * floats). peer / beg / dst_row are host arrays, n_peers <= 16; rows is a device int32 array.
+ * The list is walked starting at peer first_peer (wrapping), so that ranks passing rank + 1 do
+ * not all write to the same peer at once.
+ * Ordering against the readers is the caller's (alternating buffers + one barrier per exchange). */
+int DGLB200HaloPush(const float* x, int64_t D, int n_peers, void* const* peer, const int64_t* beg,
+                    const int64_t* dst_row, const int32_t* rows, int first_peer, int device,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif

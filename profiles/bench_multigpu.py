@@ -162,7 +162,7 @@ def main():
                 "cut_fraction": round(float(st[:, 1].sum() / st[:, 0].sum()), 4),
                 "max_local_edges": int(st[:, 0].max()), "max_halo_nodes": int(st[:, 3].max()),
                 "halo_bytes_per_step_per_rank_max": int(st[:, 3].max()) * d * 4 * 2,
-                "steps": args.steps, "warmup": args.warmup, "check": check,
+                "halo_path": pg.halo_path, "steps": args.steps, "warmup": args.warmup, "check": check,
                 "phase_ms_max_over_ranks": phases}
         print(json.dumps(line), flush=True)
         if args.out:
