@@ -101,6 +101,9 @@ SYMBOLS = {
     "DGLB200PeerFree": (_c.c_int, [_c.c_void_p]),
     "DGLB200HaloPush": (_c.c_int, [_c.c_void_p, _c.c_int64, _c.c_int, _c.c_void_p, _c.c_void_p,
                                    _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p]),
+    "DGLB200EdgeSoftmaxForward": (_c.c_int, [GraphHandle, TensorP, TensorP, _c.c_void_p]),
+    "DGLB200EdgeSoftmaxBackward": (_c.c_int, [GraphHandle, TensorP, TensorP, TensorP,
+                                              _c.c_void_p]),
     "DGLB200KernelCopyReduceMean": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP,
                                                _c.c_void_p]),
     "DGLB200KernelBackwardCopyReduce": (_c.c_int, [_c.c_char_p, GraphHandle, _c.c_int, TensorP,

@@ -686,6 +686,46 @@ int DGLB200KernelBackwardFusedGat(DGLB200GraphHandle graph, const DGLB200Tensor*
 }
 
 // ---- RGCN hack layers (src/kernel/binary_reduce.cc:412-450)
+// ---- fused edge_softmax (extension) ----
+static int64_t softmax_width(DGLB200Graph* g, std::initializer_list<const DGLB200Tensor*> ts) {
+  const DGLB200Tensor* first = *ts.begin();
+  for (const DGLB200Tensor* t : ts) {
+    check_float(t, "edge_softmax tensor");
+    check_compact(t, "edge_softmax tensor");
+    B200_CHECK(t->ndim >= 1 && t->shape[0] == g->num_edges,
+               "edge_softmax: tensors must hold one row per edge");
+    B200_CHECK(t->ndim == first->ndim, "edge_softmax: tensors must have identical shapes");
+    for (int i = 0; i < t->ndim; ++i)
+      B200_CHECK(t->shape[i] == first->shape[i], "edge_softmax: tensors must have identical shapes");
+  }
+  return g->num_edges == 0 ? 1 : feat_len(first);
+}
+
+extern "C" int DGLB200EdgeSoftmaxForward(DGLB200GraphHandle graph, const DGLB200Tensor* score,
+                                         DGLB200Tensor* out, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && score && out, "NULL argument");
+  check_ctx(graph, {score, out}, {"score", "out"});
+  const int64_t H = softmax_width(graph, {score, out});
+  B200_CUDA(cudaSetDevice(graph->device));
+  edge_softmax_forward(graph, data_ptr<const float>(score), data_ptr<float>(out), H,
+                       static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+extern "C" int DGLB200EdgeSoftmaxBackward(DGLB200GraphHandle graph, const DGLB200Tensor* out,
+                                          const DGLB200Tensor* grad_out,
+                                          DGLB200Tensor* grad_score, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && out && grad_out && grad_score, "NULL argument");
+  check_ctx(graph, {out, grad_out, grad_score}, {"out", "grad_out", "grad_score"});
+  const int64_t H = softmax_width(graph, {out, grad_out, grad_score});
+  B200_CUDA(cudaSetDevice(graph->device));
+  edge_softmax_backward(graph, data_ptr<const float>(out), data_ptr<const float>(grad_out),
+                        data_ptr<float>(grad_score), H, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
 static int64_t numel(const DGLB200Tensor* t) {
   int64_t n = 1;
   for (int i = 0; i < t->ndim; ++i) n *= t->shape[i];

@@ -269,6 +269,10 @@ void fused_gat_backward(DGLB200Graph* g, const float* ft, const float* el, const
                         const float* sum, const float* exp, const float* ret, const float* gout,
                         float* grad_ft, float* grad_el, float* grad_er, int64_t H, int64_t F,
                         float slope, cudaStream_t s);
+// softmax.cu
+void edge_softmax_forward(DGLB200Graph* g, const float* z, float* out, int64_t H, cudaStream_t s);
+void edge_softmax_backward(DGLB200Graph* g, const float* out, const float* gout, float* gz,
+                           int64_t H, cudaStream_t s);
 // rgcn.cu
 void rgcn_layer0_forward(DGLB200Graph* g, const float* w, const float* norm, float* ret,
                          int64_t n_rows_w, int64_t feat, cudaStream_t s);

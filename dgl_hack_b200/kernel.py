@@ -153,3 +153,18 @@ def copy_reduce_mean(G, target, X, out):
 
 last_kernel = _lib.last_kernel
 launch_count = _lib.launch_count
+
+
+def edge_softmax_forward(G, score, out):
+    """Extension: nn/pytorch/softmax.py EdgeSoftmax.forward as one kernel."""
+    t = [_nd(x) for x in (score, out)]
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200EdgeSoftmaxForward(G.handle, t[0].ptr, t[1].ptr, _stream(G)))
+
+
+def edge_softmax_backward(G, out, grad_out, grad_score):
+    """Extension: nn/pytorch/softmax.py EdgeSoftmax.backward as one kernel."""
+    t = [_nd(x) for x in (out, grad_out, grad_score)]
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200EdgeSoftmaxBackward(G.handle, t[0].ptr, t[1].ptr, t[2].ptr,
+                                                  _stream(G)))

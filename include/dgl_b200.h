@@ -267,6 +267,17 @@ int DGLB200KernelCopyReduceMean(DGLB200GraphHandle graph, int target,
                                 const DGLB200Tensor* in_data, DGLB200Tensor* out_data,
                                 void* stream);
 
+/* edge_softmax over the in-edges of every destination node, forward and backward, ONE kernel
+ * each (python/dgl/nn/pytorch/softmax.py:16-110 EdgeSoftmax runs copy_e+max, e_sub_v, exp,
+ * copy_e+sum, e_div_v forward and copy_e+sum, e_mul_v backward through the builtin kernels).
+ * `score` / `out` / `grad_out` / `grad_score` are [num_edges, ...] float32 in edge-id order with
+ * identical shapes; softmax runs independently per trailing feature column. */
+int DGLB200EdgeSoftmaxForward(DGLB200GraphHandle graph, const DGLB200Tensor* score,
+                              DGLB200Tensor* out, void* stream);
+int DGLB200EdgeSoftmaxBackward(DGLB200GraphHandle graph, const DGLB200Tensor* out,
+                               const DGLB200Tensor* grad_out, DGLB200Tensor* grad_score,
+                               void* stream);
+
 /* Dispatch introspection for tests / bench: name of the kernel family the LAST compute call in
  * this process used ("spmm", "generic_row", "generic_edge", ...), and how many kernel launches
  * the library has issued since load (all threads). */
