@@ -193,6 +193,17 @@ class FusedGat(th.autograd.Function):
         return None, grad_feat_src, grad_el, grad_er, None, None, None, None
 
 
+def fused_gat_supported(num_heads, out_feats):
+    """Shapes the fused attention kernels take (csrc/gat.cu gat_plan): per-head width = VEC (4, 2
+    or 1 floats) x a power of two, at most 1024 floats per row."""
+    v = 4
+    while v > 1 and out_feats % v:
+        v >>= 1
+    lph = out_feats // v
+    return (lph & (lph - 1)) == 0 and (lph <= 32 or lph % 32 == 0) and \
+        (num_heads * out_feats // v + 31) // 32 <= 8 and num_heads <= 1024
+
+
 def fused_gat(graph, feat_src, el, er, slope):
     """tensor.py:415-420 fused_gat; `graph` is a GraphIndex on feat_src's device."""
     feat_src, el, er = feat_src.contiguous(), el.contiguous(), er.contiguous()

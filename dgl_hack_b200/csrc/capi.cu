@@ -686,6 +686,28 @@ int DGLB200KernelBackwardFusedGat(DGLB200GraphHandle graph, const DGLB200Tensor*
 }
 
 // ---- RGCN hack layers (src/kernel/binary_reduce.cc:412-450)
+// ---- node partitioning (host) ----
+int DGLB200MetisPartition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy,
+                          const int64_t* vwgt, int k, uint64_t seed, int64_t* part,
+                          int64_t* objval) {
+  API_BEGIN();
+  B200_CHECK(nvtxs >= 0 && nvtxs < (1ll << 31) - 1, "MetisPartition: number of vertices out of range");
+  B200_CHECK(k >= 1, "MetisPartition: the number of partitions must be positive");
+  B200_CHECK(part != nullptr && (nvtxs == 0 || (xadj && (adjncy || xadj[nvtxs] == 0))),
+             "MetisPartition: NULL argument");
+  if (nvtxs > 0) {
+    B200_CHECK(xadj[0] == 0, "MetisPartition: xadj[0] must be 0");
+    for (int64_t v = 0; v < nvtxs; ++v)
+      B200_CHECK(xadj[v + 1] >= xadj[v], "MetisPartition: xadj must be non-decreasing");
+    for (int64_t j = 0; j < xadj[nvtxs]; ++j)
+      B200_CHECK(adjncy[j] >= 0 && adjncy[j] < nvtxs, "MetisPartition: neighbour id out of range");
+  }
+  int64_t cut = 0;
+  if (nvtxs > 0) cut = kway_partition(nvtxs, xadj, adjncy, vwgt, k, seed, 1.03, part);
+  if (objval) *objval = cut;
+  API_END();
+}
+
 // ---- fused edge_softmax (extension) ----
 static int64_t softmax_width(DGLB200Graph* g, std::initializer_list<const DGLB200Tensor*> ts) {
   const DGLB200Tensor* first = *ts.begin();

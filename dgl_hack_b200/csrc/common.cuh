@@ -269,6 +269,9 @@ void fused_gat_backward(DGLB200Graph* g, const float* ft, const float* el, const
                         const float* sum, const float* exp, const float* ret, const float* gout,
                         float* grad_ft, float* grad_el, float* grad_er, int64_t H, int64_t F,
                         float slope, cudaStream_t s);
+// kway.cu (host): multilevel k-way partitioner; returns the edge cut
+int64_t kway_partition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy,
+                       const int64_t* vwgt, int k, uint64_t seed, double ubfactor, int64_t* part);
 // softmax.cu
 void edge_softmax_forward(DGLB200Graph* g, const float* z, float* out, int64_t H, cudaStream_t s);
 void edge_softmax_backward(DGLB200Graph* g, const float* out, const float* gout, float* gz,

@@ -1,0 +1,474 @@
+// Multilevel k-way node partitioner (host code): the role METIS_PartGraphKway plays for
+// GraphOp::MetisPartition (src/graph/metis_partition.cc:19-66, third_party/METIS is a submodule
+// of the reference and is not rebuilt). Written from the published multilevel scheme, not from
+// METIS sources:
+//   1. coarsening  : heavy-edge matching in random order (+ pairing of still-unmatched low-degree
+//                    vertices that share a neighbour, which keeps power-law graphs shrinking),
+//                    parallel edges merged with summed weights;
+//   2. initial cut : recursive bisection of the coarsest graph -- greedy region growing from
+//                    several seeds, each followed by boundary refinement, best cut kept;
+//   3. uncoarsening: projection + greedy k-way boundary refinement under the balance constraint
+//                    max part weight <= ubfactor * total / k (METIS default 1.03).
+// Input is a symmetric adjacency in CSR form (every edge stored in both directions, no self
+// loops needed; they are ignored). Deterministic for a given seed.
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <numeric>
+#include <queue>
+#include <vector>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+
+#include "common.cuh"
+
+namespace b200 {
+namespace {
+
+struct Rng {
+  uint64_t s;
+  explicit Rng(uint64_t seed) : s(seed * 0x9E3779B97F4A7C15ull + 0x1234567ull) {}
+  uint64_t next() {
+    s ^= s << 13; s ^= s >> 7; s ^= s << 17;
+    return s;
+  }
+  uint32_t below(uint32_t n) { return (uint32_t)((next() >> 11) % n); }
+};
+
+struct LGraph {
+  int32_t n = 0;
+  std::vector<int64_t> xadj;   // [n + 1]
+  std::vector<int32_t> adj;    // neighbours
+  std::vector<int32_t> ew;     // edge weights
+  std::vector<int32_t> vw;     // vertex weights
+  int64_t total_vw = 0;
+};
+
+void shuffle(std::vector<int32_t>& v, Rng& rng) {
+  for (size_t i = v.size(); i > 1; --i) std::swap(v[i - 1], v[rng.below((uint32_t)i)]);
+}
+
+// One coarsening level. cmap[v] = coarse vertex of v.
+void coarsen(const LGraph& g, int32_t max_vw, Rng& rng, LGraph* c, std::vector<int32_t>* cmap) {
+  const int32_t n = g.n;
+  std::vector<int32_t> match(n, -1), order(n);
+  std::iota(order.begin(), order.end(), 0);
+  shuffle(order, rng);
+  for (int32_t v : order) {
+    if (match[v] >= 0) continue;
+    int32_t best = -1, bw = -1;
+    const int64_t beg = g.xadj[v], deg = g.xadj[v + 1] - beg;
+    // ties go to the first candidate met, so the scan starts at a random neighbour: adjacency
+    // lists are sorted by id and "lowest id first" would systematically match across communities
+    const int64_t rot = deg > 1 ? rng.below((uint32_t)std::min<int64_t>(deg, 0x7fffffff)) : 0;
+    for (int64_t i = 0; i < deg; ++i) {
+      const int64_t j = beg + (i + rot < deg ? i + rot : i + rot - deg);
+      const int32_t u = g.adj[j];
+      if (u == v || match[u] >= 0 || g.vw[v] + g.vw[u] > max_vw) continue;
+      if (g.ew[j] > bw) bw = g.ew[j], best = u;
+    }
+    if (best >= 0) match[v] = best, match[best] = v;
+  }
+  // two-hop pairing: unmatched vertices hanging off a common neighbour (leaves of hubs)
+  const int64_t avg_deg = g.xadj[n] / std::max(n, 1) + 1;
+  for (int32_t h = 0; h < n; ++h) {
+    if (g.xadj[h + 1] - g.xadj[h] < 2) continue;
+    int32_t pending = -1;
+    for (int64_t j = g.xadj[h]; j < g.xadj[h + 1]; ++j) {
+      const int32_t u = g.adj[j];
+      if (u == h || match[u] >= 0 || g.xadj[u + 1] - g.xadj[u] > 2 * avg_deg) continue;
+      if (pending < 0 || pending == u) { pending = u; continue; }
+      if (g.vw[pending] + g.vw[u] > max_vw) { pending = u; continue; }
+      match[pending] = u, match[u] = pending, pending = -1;
+    }
+  }
+  cmap->assign(n, -1);
+  int32_t nc = 0;
+  std::vector<int32_t> first, second;
+  first.reserve(n / 2 + 1), second.reserve(n / 2 + 1);
+  for (int32_t v = 0; v < n; ++v) {
+    if ((*cmap)[v] >= 0) continue;
+    const int32_t u = match[v];
+    (*cmap)[v] = nc;
+    first.push_back(v);
+    if (u >= 0 && u != v) (*cmap)[u] = nc, second.push_back(u);
+    else second.push_back(-1);
+    ++nc;
+  }
+  c->n = nc;
+  c->xadj.assign(nc + 1, 0);
+  c->vw.assign(nc, 0);
+  c->adj.clear(), c->ew.clear();
+  c->adj.reserve(g.adj.size() / 2), c->ew.reserve(g.adj.size() / 2);
+  c->total_vw = g.total_vw;
+  std::vector<int64_t> slot(nc, -1);  // position of a coarse neighbour in the row being built
+  for (int32_t cv = 0; cv < nc; ++cv) {
+    const int64_t row_beg = (int64_t)c->adj.size();
+    for (int32_t v : {first[cv], second[cv]}) {
+      if (v < 0) continue;
+      c->vw[cv] += g.vw[v];
+      for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
+        const int32_t cu = (*cmap)[g.adj[j]];
+        if (cu == cv) continue;
+        if (slot[cu] >= row_beg) c->ew[slot[cu]] += g.ew[j];
+        else slot[cu] = (int64_t)c->adj.size(), c->adj.push_back(cu), c->ew.push_back(g.ew[j]);
+      }
+    }
+    c->xadj[cv + 1] = (int64_t)c->adj.size();
+  }
+}
+
+int64_t edge_cut(const LGraph& g, const std::vector<int32_t>& part) {
+  int64_t cut = 0;
+  for (int32_t v = 0; v < g.n; ++v)
+    for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j)
+      if (part[g.adj[j]] != part[v]) cut += g.ew[j];
+  return cut / 2;
+}
+
+// Greedy k-way boundary refinement. target[p] = desired weight of part p; a move may not push a
+// part above ub * target. Overweight parts shed vertices even at a loss.
+void refine(const LGraph& g, int k, const std::vector<double>& target, double ub, int passes,
+            Rng& rng, std::vector<int32_t>* part_io) {
+  std::vector<int32_t>& part = *part_io;
+  std::vector<int64_t> pw(k, 0), maxw(k);
+  for (int32_t v = 0; v < g.n; ++v) pw[part[v]] += g.vw[v];
+  for (int p = 0; p < k; ++p) maxw[p] = (int64_t)(ub * target[p]) + 1;
+  std::vector<int64_t> conn(k, 0);
+  std::vector<int32_t> touched, order(g.n);
+  std::iota(order.begin(), order.end(), 0);
+  for (int pass = 0; pass < passes; ++pass) {
+    shuffle(order, rng);
+    int64_t moved = 0;
+    for (int32_t v : order) {
+      const int own = part[v];
+      touched.clear();
+      bool boundary = false;
+      for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
+        const int32_t u = g.adj[j];
+        if (u == v) continue;
+        const int p = part[u];
+        if (conn[p] == 0) touched.push_back(p);
+        conn[p] += g.ew[j];
+        boundary |= (p != own);
+      }
+      const bool over = pw[own] > maxw[own];
+      if (boundary || over) {
+        const int64_t id = conn[own];
+        int best = -1;
+        int64_t best_gain = 0;
+        for (int p : touched) {
+          if (p == own || pw[p] + g.vw[v] > maxw[p]) continue;
+          const int64_t gain = conn[p] - id;
+          const bool better_balance = pw[own] - g.vw[v] >= pw[p] + g.vw[v] ||
+                                      (double)pw[own] / target[own] > (double)(pw[p] + g.vw[v]) / target[p];
+          if (best < 0) {
+            if (gain > 0 || (gain == 0 && better_balance && pw[own] - pw[p] > g.vw[v]) || over)
+              best = p, best_gain = gain;
+          } else if (gain > best_gain || (gain == best_gain && pw[p] < pw[best])) {
+            best = p, best_gain = gain;
+          }
+        }
+        if (best < 0 && over) {  // no adjacent part has room: take the lightest part overall
+          int light = -1;
+          for (int p = 0; p < k; ++p)
+            if (p != own && pw[p] + g.vw[v] <= maxw[p] &&
+                (light < 0 || pw[p] * target[light] < pw[light] * target[p])) light = p;
+          best = light;
+        }
+        if (best >= 0) {
+          part[v] = best;
+          pw[own] -= g.vw[v], pw[best] += g.vw[v];
+          ++moved;
+        }
+      }
+      for (int p : touched) conn[p] = 0;
+    }
+    if (moved * 2000 < (int64_t)g.n + 2000 && pass >= 1) break;  // converged: < 0.05 % moved
+  }
+}
+
+// Two-way Fiduccia-Mattheyses refinement with hill climbing: vertices move one at a time in
+// order of gain (also at a loss), each at most once per pass; the pass is rolled back to its best
+// balanced prefix. Used on the (small) coarsest graph only.
+void fm_refine(const LGraph& g, const double target[2], double ub, int max_passes,
+               std::vector<int32_t>* part_io) {
+  std::vector<int32_t>& part = *part_io;
+  const int32_t n = g.n;
+  typedef std::pair<int64_t, int32_t> Item;
+  std::vector<int64_t> gain(n);
+  std::vector<char> locked(n);
+  std::vector<int32_t> moves;
+  int64_t pw[2] = {0, 0};
+  for (int32_t v = 0; v < n; ++v) pw[part[v]] += g.vw[v];
+  const int64_t maxw[2] = {(int64_t)(ub * target[0]) + 1, (int64_t)(ub * target[1]) + 1};
+  auto imbalance = [&](const int64_t w[2]) {
+    return std::max(std::max<double>(0, w[0] - maxw[0]), std::max<double>(0, w[1] - maxw[1]));
+  };
+  const int limit = std::max(50, std::min(n / 5, 2000));
+  for (int pass = 0; pass < max_passes; ++pass) {
+    std::priority_queue<Item> q[2];
+    for (int32_t v = 0; v < n; ++v) {
+      int64_t ext = 0, in = 0;
+      for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
+        if (g.adj[j] == v) continue;
+        (part[g.adj[j]] == part[v] ? in : ext) += g.ew[j];
+      }
+      gain[v] = ext - in;
+      locked[v] = 0;
+      q[part[v]].push(Item(gain[v], v));
+    }
+    moves.clear();
+    int64_t cur = 0, best = 0;
+    double best_imb = imbalance(pw);
+    size_t best_len = 0;
+    int since_best = 0;
+    while (since_best < limit) {
+      int32_t cand[2] = {-1, -1};
+      for (int sd = 0; sd < 2; ++sd) {
+        while (!q[sd].empty()) {
+          const Item it = q[sd].top();
+          if (locked[it.second] || part[it.second] != sd || it.first != gain[it.second]) { q[sd].pop(); continue; }
+          cand[sd] = it.second;
+          break;
+        }
+      }
+      int from = -1;
+      const bool ok0 = cand[0] >= 0 && pw[1] + g.vw[cand[0]] <= maxw[1];
+      const bool ok1 = cand[1] >= 0 && pw[0] + g.vw[cand[1]] <= maxw[0];
+      if (pw[0] > maxw[0] && cand[0] >= 0) from = 0;        // restore balance first
+      else if (pw[1] > maxw[1] && cand[1] >= 0) from = 1;
+      else if (ok0 && ok1) from = gain[cand[0]] >= gain[cand[1]] ? 0 : 1;
+      else if (ok0) from = 0;
+      else if (ok1) from = 1;
+      if (from < 0) break;
+      const int32_t v = cand[from];
+      q[from].pop();
+      locked[v] = 1;
+      part[v] = 1 - from;
+      pw[from] -= g.vw[v], pw[1 - from] += g.vw[v];
+      cur -= gain[v];
+      moves.push_back(v);
+      for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
+        const int32_t u = g.adj[j];
+        if (u == v || locked[u]) continue;
+        gain[u] += (part[u] == from ? 2 : -2) * (int64_t)g.ew[j];
+        q[part[u]].push(Item(gain[u], u));
+      }
+      const double imb = imbalance(pw);
+      if (imb < best_imb || (imb == best_imb && cur < best)) {
+        best = cur, best_imb = imb, best_len = moves.size(), since_best = 0;
+      } else {
+        ++since_best;
+      }
+    }
+    for (size_t i = moves.size(); i > best_len; --i) {  // roll back past the best prefix
+      const int32_t v = moves[i - 1];
+      pw[part[v]] -= g.vw[v];
+      part[v] = 1 - part[v];
+      pw[part[v]] += g.vw[v];
+    }
+    if (best_len == 0) break;
+  }
+}
+
+// Bisection of a small graph into weights (frac, 1 - frac): region growing + FM, best of 8.
+void flat_bisect(const LGraph& g, double frac, Rng& rng, std::vector<int32_t>* out) {
+  const int32_t n = g.n;
+  std::vector<int32_t> best_part;
+  int64_t best_cut = -1;
+  double best_dev = 0;
+  const std::vector<double> target = {frac * g.total_vw, (1.0 - frac) * g.total_vw};
+  const int trials = n <= 1 ? 1 : 8;
+  for (int t = 0; t < trials; ++t) {
+    std::vector<int32_t> part(n, 1);
+    std::vector<int64_t> gain(n, 0);
+    std::vector<char> in_q(n, 0);
+    typedef std::pair<int64_t, int32_t> Item;
+    std::priority_queue<Item> q;
+    int64_t w0 = 0;
+    const int64_t want = (int64_t)(frac * g.total_vw);
+    int32_t scan = 0;
+    std::vector<int32_t> order(n);
+    std::iota(order.begin(), order.end(), 0);
+    shuffle(order, rng);
+    while (w0 < want) {
+      int32_t v = -1;
+      while (!q.empty()) {  // lazy deletion: skip stale gains / vertices already taken
+        Item it = q.top();
+        q.pop();
+        if (part[it.second] == 1 && it.first == gain[it.second]) { v = it.second; break; }
+      }
+      if (v < 0) {  // new seed (first one, or the region ran out of frontier)
+        while (scan < n && (part[order[scan]] == 0 || gain[order[scan]] == INT64_MIN)) ++scan;
+        if (scan >= n) break;
+        v = order[scan];
+      }
+      if (w0 + g.vw[v] > want + (want >> 4) + 1 && w0 > 0) {  // too heavy to add: try another
+        gain[v] = INT64_MIN;
+        continue;
+      }
+      part[v] = 0;
+      w0 += g.vw[v];
+      for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
+        const int32_t u = g.adj[j];
+        if (u == v || part[u] == 0 || gain[u] == INT64_MIN) continue;
+        if (!in_q[u]) {  // gain = weight into the region - weight to the rest
+          int64_t ext = 0;
+          for (int64_t jj = g.xadj[u]; jj < g.xadj[u + 1]; ++jj) ext += g.ew[jj];
+          gain[u] = -ext;
+          in_q[u] = 1;
+        }
+        gain[u] += 2 * (int64_t)g.ew[j];
+        q.push(Item(gain[u], u));
+      }
+    }
+    const int64_t cut_grown = edge_cut(g, part);
+    fm_refine(g, target.data(), 1.03, 10, &part);
+    const int64_t cut = edge_cut(g, part);
+    (void)cut_grown;
+    int64_t pw0 = 0;
+    for (int32_t v = 0; v < n; ++v) pw0 += part[v] == 0 ? g.vw[v] : 0;
+    const double dev = std::abs((double)pw0 - target[0]) / std::max(1.0, (double)g.total_vw);
+    const bool ok = dev <= 0.05, best_ok = best_dev <= 0.05;
+    if (best_cut < 0 || (ok && !best_ok) || (ok == best_ok && (ok ? cut < best_cut : dev < best_dev))) {
+      best_cut = cut, best_dev = dev, best_part = part;
+    }
+  }
+  *out = best_part;
+}
+
+// Multilevel bisection: the graph handed to the k-way initial partitioning is itself coarsened to
+// ~150 vertices, bisected there, and FM-refined at every level on the way back, so hill climbing
+// happens at every scale (one flat FM on a few thousand blurred vertices does not find the cut).
+void bisect(const LGraph& g, double frac, Rng& rng, std::vector<int32_t>* out) {
+  std::vector<LGraph> levels;
+  std::vector<std::vector<int32_t>> cmaps;
+  const int32_t coarsen_to = 150;
+  const LGraph* cur_g = &g;
+  levels.reserve(40);
+  while (cur_g->n > coarsen_to && levels.size() < 38) {
+    const int32_t max_vw = (int32_t)std::max<int64_t>(1, (int64_t)(1.5 * g.total_vw / coarsen_to));
+    LGraph c;
+    std::vector<int32_t> cmap;
+    coarsen(*cur_g, max_vw, rng, &c, &cmap);
+    if (c.n > 0.95 * cur_g->n) break;
+    cmaps.push_back(std::move(cmap));
+    levels.push_back(std::move(c));
+    cur_g = &levels.back();
+  }
+  std::vector<int32_t> part;
+  flat_bisect(*cur_g, frac, rng, &part);
+  const double target[2] = {frac * g.total_vw, (1.0 - frac) * g.total_vw};
+  for (int lvl = (int)levels.size() - 1; lvl >= 0; --lvl) {
+    const LGraph& fine = lvl == 0 ? g : levels[lvl - 1];
+    std::vector<int32_t> p(fine.n);
+    for (int32_t v = 0; v < fine.n; ++v) p[v] = part[cmaps[lvl][v]];
+    part.swap(p);
+    fm_refine(fine, target, 1.03, 6, &part);
+  }
+  *out = part;
+}
+
+void induced(const LGraph& g, const std::vector<int32_t>& part, int side, LGraph* s,
+             std::vector<int32_t>* ids) {
+  std::vector<int32_t> local(g.n, -1);
+  ids->clear();
+  for (int32_t v = 0; v < g.n; ++v)
+    if (part[v] == side) local[v] = (int32_t)ids->size(), ids->push_back(v);
+  s->n = (int32_t)ids->size();
+  s->xadj.assign(s->n + 1, 0);
+  s->vw.resize(s->n);
+  s->adj.clear(), s->ew.clear();
+  s->total_vw = 0;
+  for (int32_t i = 0; i < s->n; ++i) {
+    const int32_t v = (*ids)[i];
+    s->vw[i] = g.vw[v];
+    s->total_vw += g.vw[v];
+    for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j)
+      if (local[g.adj[j]] >= 0 && g.adj[j] != v) s->adj.push_back(local[g.adj[j]]), s->ew.push_back(g.ew[j]);
+    s->xadj[i + 1] = (int64_t)s->adj.size();
+  }
+}
+
+void recursive_bisection(const LGraph& g, int k, int base, Rng& rng, const std::vector<int32_t>& ids,
+                         std::vector<int32_t>* labels) {
+  if (k == 1 || g.n == 0) {
+    for (int32_t v : ids) (*labels)[v] = base;
+    return;
+  }
+  const int k0 = k / 2;
+  std::vector<int32_t> part;
+  bisect(g, (double)k0 / k, rng, &part);
+  for (int side = 0; side < 2; ++side) {
+    LGraph s;
+    std::vector<int32_t> sub, sub_global;
+    induced(g, part, side, &s, &sub);
+    sub_global.reserve(sub.size());
+    for (int32_t i : sub) sub_global.push_back(ids[i]);
+    recursive_bisection(s, side == 0 ? k0 : k - k0, side == 0 ? base : base + k0, rng, sub_global,
+                        labels);
+  }
+}
+
+}  // namespace
+
+int64_t kway_partition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy,
+                       const int64_t* vwgt, int k, uint64_t seed, double ubfactor, int64_t* part) {
+  Rng rng(seed);
+  const bool dbg = std::getenv("B200_KWAY_DEBUG") != nullptr;
+  auto t0 = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what, int64_t a, int64_t b) {
+    if (!dbg) return;
+    auto t1 = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[kway] %s n=%lld x=%lld  %.3fs\n", what, (long long)a, (long long)b,
+                 std::chrono::duration<double>(t1 - t0).count());
+    t0 = t1;
+  };
+  std::vector<LGraph> levels(1);
+  levels.reserve(64);  // references into `levels` stay valid while levels are appended
+  LGraph& g0 = levels[0];
+  g0.n = (int32_t)nvtxs;
+  g0.xadj.assign(xadj, xadj + nvtxs + 1);
+  g0.adj.resize(xadj[nvtxs]);
+  for (int64_t j = 0; j < xadj[nvtxs]; ++j) g0.adj[j] = (int32_t)adjncy[j];
+  g0.ew.assign(xadj[nvtxs], 1);
+  g0.vw.resize(nvtxs);
+  for (int64_t v = 0; v < nvtxs; ++v) g0.vw[v] = vwgt ? (int32_t)std::max<int64_t>(vwgt[v], 0) : 1, g0.total_vw += g0.vw[v];
+  std::vector<std::vector<int32_t>> cmaps;
+  int lg = 1;
+  while ((1 << lg) < k) ++lg;
+  const int32_t coarsen_to = (int32_t)std::max<int64_t>(std::max(40 * k, 2000), nvtxs / (20 * lg));
+  while (levels.back().n > coarsen_to && levels.size() < 48) {
+    const LGraph& g = levels.back();
+    const int32_t max_vw = (int32_t)std::max<int64_t>(1, (int64_t)(1.5 * g.total_vw / coarsen_to));
+    LGraph c;
+    std::vector<int32_t> cmap;
+    coarsen(g, max_vw, rng, &c, &cmap);
+    if (c.n > 0.97 * g.n) break;  // matching no longer shrinks the graph
+    cmaps.push_back(std::move(cmap));
+    levels.push_back(std::move(c));
+    lap("coarsen", levels.back().n, (int64_t)levels.back().adj.size());
+  }
+  const LGraph& gc = levels.back();
+  std::vector<int32_t> cur(gc.n, 0), ids(gc.n);
+  std::iota(ids.begin(), ids.end(), 0);
+  recursive_bisection(gc, k, 0, rng, ids, &cur);
+  lap("initial", gc.n, edge_cut(gc, cur));
+  std::vector<double> target(k, (double)g0.total_vw / k);
+  refine(gc, k, target, ubfactor, 10, rng, &cur);
+  for (int lvl = (int)levels.size() - 2; lvl >= 0; --lvl) {
+    const LGraph& g = levels[lvl];
+    std::vector<int32_t> fine(g.n);
+    for (int32_t v = 0; v < g.n; ++v) fine[v] = cur[cmaps[lvl][v]];
+    cur.swap(fine);
+    refine(g, k, target, ubfactor, 30, rng, &cur);
+    lap("refine", g.n, edge_cut(g, cur));
+    levels[lvl + 1] = LGraph();  // release the coarser level
+  }
+  for (int64_t v = 0; v < nvtxs; ++v) part[v] = cur[v];
+  return edge_cut(levels[0], cur);
+}
+
+}  // namespace b200

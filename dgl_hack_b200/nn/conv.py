@@ -164,7 +164,8 @@ class GATConv(nn.Module):
     arithmetic and are left out). Attention = u_add_v -> leaky_relu -> edge_softmax -> u_mul_e+sum.
     With `fused=True` (what the fork's FusedGATConv does, fusedGatConv.py:151) the attention runs
     as the fused GAT kernel; it needs attn_drop == 0 and, like the reference's fused op, applies no
-    max-subtraction."""
+    max-subtraction. Head widths the fused kernel does not take (backend.fused_gat_supported) run
+    the builtin composition on the same kernels library."""
 
     def __init__(self, in_feats, out_feats, num_heads, feat_drop=0., attn_drop=0.,
                  negative_slope=0.2, residual=False, activation=None, fused=False):
@@ -222,7 +223,7 @@ class GATConv(nn.Module):
             feat_src = feat_dst = self.fc(h_src).view(-1, self._num_heads, self._out_feats)
         el = (feat_src * self.attn_l).sum(dim=-1).unsqueeze(-1)
         er = (feat_dst * self.attn_r).sum(dim=-1).unsqueeze(-1)
-        if self._fused:
+        if self._fused and B.fused_gat_supported(self._num_heads, self._out_feats):
             rst = B.fused_gat(graph.gidx, feat_src, el, er, self.negative_slope)
         else:
             graph.srcdata.update({"ft": feat_src, "el": el})

@@ -37,6 +37,78 @@ def range_partition(num_nodes, dst, k):
     return part
 
 
+def symmetric_csr(num_nodes, src, dst):
+    """Host CSR (xadj, adjncy int64) of the symmetrised simple graph -- what the reference feeds
+    METIS: `to_bidirected(g)` then the in-CSR (python/dgl/transform.py:625-626,
+    src/graph/metis_partition.cc:25-31). Self loops and parallel edges are dropped."""
+    src = torch.as_tensor(src, dtype=torch.int64)
+    dst = torch.as_tensor(dst, dtype=torch.int64).to(src.device)
+    keep = src != dst
+    u = torch.cat([src[keep], dst[keep]])
+    v = torch.cat([dst[keep], src[keep]])
+    key = torch.unique(u * num_nodes + v)  # sorted: rows ascending, neighbours ascending
+    rows = torch.div(key, num_nodes, rounding_mode="floor")
+    adjncy = (key - rows * num_nodes).cpu().contiguous()
+    xadj = torch.zeros(num_nodes + 1, dtype=torch.int64)
+    xadj[1:] = torch.cumsum(torch.bincount(rows, minlength=num_nodes), 0).cpu()
+    return xadj, adjncy
+
+
+def metis_partition_assignment(num_nodes, src, dst, k, balance="nodes", seed=0,
+                               return_cut=False):
+    """Node -> part vector (int64, CPU) from the library's multilevel k-way partitioner
+    (DGLB200MetisPartition, csrc/kway.cu), the counterpart of
+    `_CAPI_DGLMetisPartition(to_bidirected(g), k)` (transform.py:623-629). balance="nodes"
+    equalises node counts as the reference does (vwgt = NULL); "in_edges" equalises
+    in-degree + 1, i.e. the aggregation work each GPU gets."""
+    import ctypes
+    from ._lib import LIB, check_call
+    xadj, adjncy = symmetric_csr(num_nodes, src, dst)
+    vw = None
+    if balance == "in_edges":
+        d = torch.as_tensor(dst, dtype=torch.int64)
+        vw = (torch.bincount(d, minlength=num_nodes) + 1).cpu().contiguous()
+    elif balance != "nodes":
+        raise ValueError("balance must be 'nodes' or 'in_edges'")
+    part = torch.empty(num_nodes, dtype=torch.int64)
+    cut = ctypes.c_int64()
+    check_call(LIB.DGLB200MetisPartition(
+        int(num_nodes), ctypes.c_void_p(xadj.data_ptr()), ctypes.c_void_p(adjncy.data_ptr()),
+        ctypes.c_void_p(vw.data_ptr() if vw is not None else None), int(k), int(seed),
+        ctypes.c_void_p(part.data_ptr()), ctypes.byref(cut)))
+    return (part, int(cut.value)) if return_cut else part
+
+
+def partition_graph_with_halo(num_nodes, src, dst, node_part, num_parts=None):
+    """1-hop form of `dgl.transform.partition_graph_with_halo(g, node_part, 1)`
+    (transform.py:551-586 -> GraphOp::GetSubgraphWithHalo, src/graph/graph_op.cc:403-509) on COO
+    arrays. For every part: `induced_nodes` (parent ids, ascending), `induced_edges` (parent ids of
+    the in-edges of the owned nodes, ordered by (destination, edge id) as `InEdges(nodes)` returns
+    them), `inner_node` (1 = owned, 0 = halo), `inner_edge` (1 = the source is owned too, 0 = cut
+    edge, graph_op.cc:427-433) and the local COO in `induced_edges` order."""
+    src = torch.as_tensor(src, dtype=torch.int64)
+    dst = torch.as_tensor(dst, dtype=torch.int64)
+    node_part = torch.as_tensor(node_part, dtype=torch.int64)
+    assert node_part.numel() == num_nodes
+    k = int(num_parts if num_parts is not None else node_part.max().item() + 1)
+    out = {}
+    for p in range(k):
+        eids = torch.nonzero(node_part[dst] == p).flatten()
+        eids = eids[torch.sort(dst[eids], stable=True).indices]
+        es, ed = src[eids], dst[eids]
+        owned = node_part == p
+        mark = owned.clone()
+        mark[es] = True
+        nodes = torch.nonzero(mark).flatten()
+        g2l = torch.full((num_nodes,), -1, dtype=torch.int64)
+        g2l[nodes] = torch.arange(nodes.numel())
+        out[p] = {"induced_nodes": nodes, "induced_edges": eids,
+                  "inner_node": owned[nodes].to(torch.int32),
+                  "inner_edge": owned[es].to(torch.int32),
+                  "src": g2l[es], "dst": g2l[ed], "part_id": node_part[nodes]}
+    return out
+
+
 class Partition(object):
     """One rank's share of a graph: inner nodes, halo nodes, local COO split by source locality."""
 

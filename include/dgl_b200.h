@@ -284,6 +284,20 @@ int DGLB200EdgeSoftmaxBackward(DGLB200GraphHandle graph, const DGLB200Tensor* ou
 const char* DGLB200LastKernel(void);
 int64_t DGLB200LaunchCount(void);
 
+/* ---- node partitioning (host code; GraphOp::MetisPartition, src/graph/metis_partition.cc:19-66,
+ *      = METIS_PartGraphKway(nvtxs, ncon=1, xadj, adjncy, nparts=k) on the symmetrised graph) ---- */
+
+/* Multilevel k-way partition of a symmetric graph in CSR form (host int64 arrays, as the
+ * reference hands METIS its in-CSR): part[v] in [0, k) minimising the edge cut with every part's
+ * weight <= 1.03 * total / k (METIS' default imbalance). vwgt = NULL means unit vertex weights
+ * (what the reference passes); otherwise one non-negative weight per vertex. *objval receives the
+ * edge cut. Deterministic for a given seed. METIS itself is a submodule the reference links; this
+ * is an independent implementation of the same published scheme, so assignments differ while the
+ * invariants the reference tests (tests/compute/test_transform.py:223-272) hold. */
+int DGLB200MetisPartition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy,
+                          const int64_t* vwgt, int k, uint64_t seed, int64_t* part,
+                          int64_t* objval);
+
 /* ---- multi-GPU halo exchange over peer memory (no reference PackedFunc; the partition semantics
  *      are partition_graph_with_halo's, python/dgl/transform.py:551-640) ---- */
 

@@ -224,6 +224,94 @@ def c4(out):
         "torch gather+bmm then our copy_e kernel")
 
 
+def models(out):
+    """The configs' models through dgl_hack_b200.nn (module forward + backward, CUDA events):
+    C1 2-layer GCN (Cora-shaped), C3 GATConv builtin-composed (fused edge_softmax) vs FusedGATConv,
+    edge_softmax fused vs 4-call, C4 RelGraphConv (basis, typed-adjacency kernel)."""
+    import dgl_hack_b200.nn as nnb
+    from dgl_hack_b200.graph import Graph
+    # C1
+    n, e = 2708, 10556
+    gen = torch.Generator(device=DEV)
+    gen.manual_seed(1)
+    src = torch.cat([torch.randint(0, n, (e - n,), generator=gen, device=DEV),
+                     torch.arange(n, device=DEV)])
+    dst = torch.cat([torch.randint(0, n, (e - n,), generator=gen, device=DEV),
+                     torch.arange(n, device=DEV)])
+    g = Graph(src, dst, num_nodes=n, device=DEV)
+    l1 = nnb.GraphConv(1433, 16, activation=torch.relu).to(DEV)
+    l2 = nnb.GraphConv(16, 7).to(DEV)
+    x = rand(n, 1433)
+    y = torch.randint(0, 7, (n,), device=DEV)
+    params = list(l1.parameters()) + list(l2.parameters())
+
+    def gcn_step():
+        loss = torch.nn.functional.cross_entropy(l2(g, l1(g, x)), y)
+        loss.backward()
+        for p_ in params:
+            p_.grad = None
+    ms = timeit(gcn_step)
+    rec(out, "C1 cora", "2-layer GCN fwd+loss+bwd (nn.GraphConv via update_all)", ms, 4 * e, 0,
+        "host/launch bound")
+    # C3
+    n, e, H, Fw = 169343, 1166243, 8, 16
+    src, dst = bench.make_graph_coo(n, e, 0.4, 3, DEV)
+    g = Graph(src, dst, num_nodes=n, device=DEV)
+    z = rand(e, H, 1).requires_grad_(True)
+    go = rand(e, H, 1)
+    for form in ("fused", "builtin"):
+        os.environ["B200_EDGE_SOFTMAX"] = form
+        with torch.no_grad():
+            ms = timeit(lambda: nnb.edge_softmax(g, z))
+        rec(out, "C3 arxiv", "edge_softmax forward (%s)" % form, ms, e,
+            2 * e * H * 4 + e * 8 + n * 4, "1 kernel" if form == "fused" else "4 kernels + exp")
+
+        def sm_fb():
+            nnb.edge_softmax(g, z).backward(go)
+            z.grad = None
+        ms = timeit(sm_fb)
+        rec(out, "C3 arxiv", "edge_softmax fwd+bwd (%s)" % form, ms, 2 * e,
+            5 * e * H * 4 + 2 * (e * 8 + n * 4))
+    x = rand(n, 128)
+    gout = rand(n, H, Fw)
+    for form, cls in (("builtin composition, fused edge_softmax", nnb.GATConv),
+                      ("fused GAT kernel", nnb.FusedGATConv)):
+        os.environ["B200_EDGE_SOFTMAX"] = "fused"
+        conv = cls(128, Fw, H).to(DEV)
+
+        def gat_step():
+            conv(g, x).backward(gout)
+            for p_ in conv.parameters():
+                p_.grad = None
+        ms = timeit(gat_step)
+        rec(out, "C3 arxiv", "GATConv 128->8x16 fwd+bwd (%s)" % form, ms, 2 * e, 0)
+    os.environ["B200_EDGE_SOFTMAX"] = "builtin"
+    conv = nnb.GATConv(128, Fw, H).to(DEV)
+    ms = timeit(gat_step)
+    rec(out, "C3 arxiv", "GATConv 128->8x16 fwd+bwd (builtin composition, 4-call edge_softmax)",
+        ms, 2 * e, 0)
+    os.environ.pop("B200_EDGE_SOFTMAX")
+    # C4
+    n, e, R, d = 1885136, 5668682, 133, 16
+    gen.manual_seed(4)
+    src = torch.randint(0, n, (e,), generator=gen, device=DEV)
+    dst = torch.randint(0, n, (e,), generator=gen, device=DEV)
+    w = (torch.arange(1, R + 1, device=DEV, dtype=torch.float64)) ** -1.1
+    et = torch.multinomial(w, e, replacement=True, generator=gen)
+    g = Graph(src, dst, num_nodes=n, device=DEV)
+    conv = nnb.RelGraphConv(d, d, R, "basis", num_bases=R, self_loop=True).to(DEV)
+    x = rand(n, d)
+    norm = torch.rand(e, 1, device=DEV)
+    gout = rand(n, d)
+
+    def rgcn_step():
+        conv(g, x, et, norm).backward(gout)
+        for p_ in conv.parameters():
+            p_.grad = None
+    ms = timeit(rgcn_step)
+    rec(out, "C4 AM", "RelGraphConv 16->16 R=133 fwd+bwd (typed-adjacency kernel)", ms, 2 * e, 0)
+
+
 def sbm_graph(n, e, blocks, p_in, alpha, seed):
     gen = torch.Generator(device=DEV)
     gen.manual_seed(seed)
@@ -338,7 +426,7 @@ def main():
     L2 = torch.cuda.get_device_properties(DEV).L2_cache_size
     out = []
     for name in args.only.split(","):
-        {"ref": ref_cpu, "c1": c1, "c2": c2, "c3": c3, "c4": c4, "c5": c5}[name](out)
+        {"ref": ref_cpu, "c1": c1, "c2": c2, "c3": c3, "c4": c4, "c5": c5, "models": models}[name](out)
         torch.cuda.empty_cache()
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(out, open(args.out, "w"), indent=1)
