@@ -179,7 +179,7 @@ bool try_spmm(const KernelCall& c) {
   a.red = c.red;
   a.op = c.op;
   int bmode = kBNone;
-  bool use_out_csr;
+  bool use_out_csr, walk_in_plain = false;
   // (tensor, target, user map) of the two gathered operands in "row/col of the walked CSR" terms
   const float *A = nullptr, *B = nullptr;
   int a_tgt = kNone, b_tgt = kNone;
@@ -215,9 +215,22 @@ bool try_spmm(const KernelCall& c) {
       a.b_head_div = hd;
     }
   } else {
+    const int t_tgt = c.mode == kGradLhs ? c.lhs_tgt : c.rhs_tgt;
+    if (c.red == kRNone) {
+      // edge outputs (apply_edges u_add_v, e_sub_v, copies to edges ...): the gradient of a NODE
+      // operand with a +-1 derivative is copy_e + sum of grad_out over the node's out-edges
+      // (source operand) or in-edges (destination operand, in-CSR order as the reference walks it)
+      if (t_tgt == kEdge || !(c.op == kUseLhs || c.op == kAdd || c.op == kSub)) return false;
+      if (c.op == kUseLhs && c.mode == kGradRhs) return false;
+      use_out_csr = (t_tgt == kSrc);
+      walk_in_plain = !use_out_csr;
+      o_map = c.mode == kGradLhs ? c.lhs_map : c.rhs_map;
+      A = c.gout; a_tgt = kEdge; a_map = c.out_map;
+      a.red = kSum;
+      a.op = (c.op == kSub && c.mode == kGradRhs) ? kOpNegA : kUseLhs;
+    } else {
     // gradient of a SOURCE-target operand under a sum reduction: a transposed SpMM of grad_out
     if (c.red != kSum) return false;
-    const int t_tgt = c.mode == kGradLhs ? c.lhs_tgt : c.rhs_tgt;
     if (t_tgt != kSrc) return false;
     use_out_csr = true;
     o_map = c.mode == kGradLhs ? c.lhs_map : c.rhs_map;
@@ -252,9 +265,11 @@ bool try_spmm(const KernelCall& c) {
     } else {
       return false;
     }
+    }
   }
 
-  const int walk = use_out_csr ? kWalkOut : kWalkInSorted;  // forward: reference sum order
+  // forward: reference sum order
+  const int walk = use_out_csr ? kWalkOut : (walk_in_plain ? kWalkIn : kWalkInSorted);
   const Csr& csr = walk_csr(g, walk);
   const int row_tgt = use_out_csr ? kSrc : kDst;
   const int col_tgt = use_out_csr ? kDst : kSrc;
@@ -353,7 +368,7 @@ bool try_spmm(const KernelCall& c) {
     if (plan.n_seg == 0) return;
     combine_partials_kernel<<<plan.n_heavy, 128, 0, s>>>(
         plan.heavy_row, plan.heavy_ptr, partial.as<float>(), csr.indptr, c.dst, o_map, (int)D,
-        c.red, a.mean);
+        a.red, a.mean);
     note_kernel(nullptr, 1);
   };
 
@@ -403,7 +418,7 @@ bool try_spmm(const KernelCall& c) {
       while (twarps > 1 && (size_t)twarps * t.stages * (t.slot_bytes + 8) > 200 * 1024) twarps >>= 1;
       const size_t smem = (size_t)twarps * t.stages * (t.slot_bytes + 8);
       const int tblocks = (int)((n_items + twarps - 1) / twarps);
-      const bool tsum = (c.red == kSum);
+      const bool tsum = (a.red == kSum);
       if (vec == 4) launch_tma_vec<4>(t, tch, tsum, scalar_w, tblocks, twarps, smem, s);
       else if (vec == 2) launch_tma_vec<2>(t, tch, tsum, scalar_w, tblocks, twarps, smem, s);
       else launch_tma_vec<1>(t, tch, tsum, scalar_w, tblocks, twarps, smem, s);
@@ -421,7 +436,7 @@ bool try_spmm(const KernelCall& c) {
       (lpr == 32) ? n_items * slabs
                   : a.n_wide + (n_items - a.n_wide + (32 / lpr) - 1) / (32 / lpr);
   const int blocks = (int)((n_warps + 7) / 8);
-  const bool sum = (c.red == kSum);
+  const bool sum = (a.red == kSum);
   if (vec == 4) launch_vec<4>(a, ch, bmode, sum, blocks, s);
   else if (vec == 2) launch_vec<2>(a, ch, bmode, sum, blocks, s);
   else launch_vec<1>(a, ch, bmode, sum, blocks, s);

@@ -224,6 +224,27 @@ def c4(out):
         "torch gather+bmm then our copy_e kernel")
 
 
+def graphed(out, cfg, op, step, e):
+    """Same step captured once into a CUDA graph and replayed: the kernels' own time without the
+    per-call Python / FFI / autograd host cost (the library allocates scratch stream-ordered and
+    builds its plans on first use, so a warmed-up step is capturable)."""
+    try:
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                step()
+        torch.cuda.current_stream().wait_stream(s)
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            step()
+        ms = timeit(gr.replay)
+        rec(out, cfg, op, ms, e, 0, "torch.cuda.CUDAGraph replay")
+    except Exception as ex:  # capture is an optimisation; report instead of failing the sweep
+        torch.cuda.synchronize()
+        print(json.dumps({"config": cfg, "op": op, "error": str(ex)[:300]}), flush=True)
+
+
 def models(out):
     """The configs' models through dgl_hack_b200.nn (module forward + backward, CUDA events):
     C1 2-layer GCN (Cora-shaped), C3 GATConv builtin-composed (fused edge_softmax) vs FusedGATConv,
@@ -253,6 +274,7 @@ def models(out):
     ms = timeit(gcn_step)
     rec(out, "C1 cora", "2-layer GCN fwd+loss+bwd (nn.GraphConv via update_all)", ms, 4 * e, 0,
         "host/launch bound")
+    graphed(out, "C1 cora", "2-layer GCN fwd+loss+bwd, CUDA-graph replay", gcn_step, 4 * e)
     # C3
     n, e, H, Fw = 169343, 1166243, 8, 16
     src, dst = bench.make_graph_coo(n, e, 0.4, 3, DEV)
@@ -285,6 +307,8 @@ def models(out):
                 p_.grad = None
         ms = timeit(gat_step)
         rec(out, "C3 arxiv", "GATConv 128->8x16 fwd+bwd (%s)" % form, ms, 2 * e, 0)
+        graphed(out, "C3 arxiv", "GATConv 128->8x16 fwd+bwd (%s), CUDA-graph replay" % form,
+                gat_step, 2 * e)
     os.environ["B200_EDGE_SOFTMAX"] = "builtin"
     conv = nnb.GATConv(128, Fw, H).to(DEV)
     ms = timeit(gat_step)
@@ -310,6 +334,7 @@ def models(out):
             p_.grad = None
     ms = timeit(rgcn_step)
     rec(out, "C4 AM", "RelGraphConv 16->16 R=133 fwd+bwd (typed-adjacency kernel)", ms, 2 * e, 0)
+    graphed(out, "C4 AM", "RelGraphConv 16->16 R=133 fwd+bwd, CUDA-graph replay", rgcn_step, 2 * e)
 
 
 def sbm_graph(n, e, blocks, p_in, alpha, seed):
