@@ -193,6 +193,38 @@ class FusedGat(th.autograd.Function):
         return None, grad_feat_src, grad_el, grad_er, None, None, None, None
 
 
+class GatAttnProj(th.autograd.Function):
+    """el / er of gatconv.py:143-144 as one streaming kernel each way (csrc/attn.cu)."""
+
+    @staticmethod
+    def forward(ctx, feat, attn_l, attn_r):
+        n, h = feat.shape[0], feat.shape[1]
+        el = feat.new_empty((n, h, 1)) if attn_l is not None else None
+        er = feat.new_empty((n, h, 1)) if attn_r is not None else None
+        K.gat_attn_proj(feat, attn_l, attn_r, el, er)
+        ctx.save_for_backward(feat, attn_l, attn_r)
+        return el, er
+
+    @staticmethod
+    def backward(ctx, grad_el, grad_er):
+        feat, attn_l, attn_r = ctx.saved_tensors
+        grad_feat = th.empty_like(feat)
+        gl = grad_el.contiguous() if attn_l is not None else None
+        gr = grad_er.contiguous() if attn_r is not None else None
+        gal = th.empty_like(attn_l) if attn_l is not None else None
+        gar = th.empty_like(attn_r) if attn_r is not None else None
+        K.gat_attn_proj_backward(feat, attn_l, attn_r, gl, gr, grad_feat, gal, gar)
+        return grad_feat, gal, gar
+
+
+def gat_attn_proj(feat, attn_l=None, attn_r=None):
+    """(el, er) = ((feat * attn_l).sum(-1, keepdim), (feat * attn_r).sum(-1, keepdim)) for
+    feat [N, H, F] and attention vectors [1, H, F]; either vector may be None."""
+    al = attn_l.contiguous() if attn_l is not None else None
+    ar = attn_r.contiguous() if attn_r is not None else None
+    return GatAttnProj.apply(feat.contiguous(), al, ar)
+
+
 def fused_gat_supported(num_heads, out_feats):
     """Shapes the fused attention kernels take (csrc/gat.cu gat_plan): per-head width = VEC (4, 2
     or 1 floats) x a power of two, at most 1024 floats per row."""

@@ -708,6 +708,81 @@ int DGLB200MetisPartition(int64_t nvtxs, const int64_t* xadj, const int64_t* adj
   API_END();
 }
 
+// ---- GAT attention projections (extension) ----
+static void attn_shapes(const DGLB200Tensor* feat, std::initializer_list<const DGLB200Tensor*> attn,
+                        std::initializer_list<const DGLB200Tensor*> per_node, int64_t* n, int64_t* H,
+                        int64_t* F) {
+  check_float(feat, "feat");
+  check_compact(feat, "feat");
+  B200_CHECK(feat->ndim == 3, "attn_proj: feat must be [N, H, F]");
+  *n = feat->shape[0], *H = feat->shape[1], *F = feat->shape[2];
+  B200_CHECK(feat->ctx.device_type == 2, "attn_proj: feat must be a CUDA tensor");
+  for (const DGLB200Tensor* t : attn) {
+    if (!t) continue;
+    check_float(t, "attn");
+    check_compact(t, "attn");
+    B200_CHECK(num_elements(t) == *H * *F && t->ndim >= 2 && t->shape[t->ndim - 1] == *F,
+               "attn_proj: attention vectors must be [1, H, F]");
+    B200_CHECK(t->ctx.device_type == feat->ctx.device_type && t->ctx.device_id == feat->ctx.device_id,
+               "attn_proj: tensors must be on one device");
+  }
+  for (const DGLB200Tensor* t : per_node) {
+    if (!t) continue;
+    check_float(t, "el/er");
+    check_compact(t, "el/er");
+    B200_CHECK(num_elements(t) == *n * *H && t->shape[0] == *n,
+               "attn_proj: el / er must be [N, H, 1]");
+    B200_CHECK(t->ctx.device_type == feat->ctx.device_type && t->ctx.device_id == feat->ctx.device_id,
+               "attn_proj: tensors must be on one device");
+  }
+}
+
+int DGLB200GatAttnProj(const DGLB200Tensor* feat, const DGLB200Tensor* attn_l,
+                       const DGLB200Tensor* attn_r, DGLB200Tensor* el, DGLB200Tensor* er,
+                       void* stream) {
+  API_BEGIN();
+  B200_CHECK(feat && ((attn_l && el) || (attn_r && er)), "NULL argument");
+  B200_CHECK((attn_l != nullptr) == (el != nullptr) && (attn_r != nullptr) == (er != nullptr),
+             "attn_proj: every attention vector needs its output and vice versa");
+  int64_t n, H, F;
+  attn_shapes(feat, {attn_l, attn_r}, {el, er}, &n, &H, &F);
+  B200_CUDA(cudaSetDevice(feat->ctx.device_id));
+  attn_proj_forward(data_ptr<const float>(feat), attn_l ? data_ptr<const float>(attn_l) : nullptr,
+                    attn_r ? data_ptr<const float>(attn_r) : nullptr,
+                    el ? data_ptr<float>(el) : nullptr, er ? data_ptr<float>(er) : nullptr, n, H, F,
+                    static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* attn_l,
+                               const DGLB200Tensor* attn_r, const DGLB200Tensor* grad_el,
+                               const DGLB200Tensor* grad_er, DGLB200Tensor* grad_feat,
+                               DGLB200Tensor* grad_attn_l, DGLB200Tensor* grad_attn_r,
+                               void* stream) {
+  API_BEGIN();
+  B200_CHECK(feat && grad_feat && ((attn_l && grad_el) || (attn_r && grad_er)), "NULL argument");
+  B200_CHECK((attn_l != nullptr) == (grad_el != nullptr) && (attn_r != nullptr) == (grad_er != nullptr),
+             "attn_proj backward: every attention vector needs its output gradient");
+  B200_CHECK((!grad_attn_l || attn_l) && (!grad_attn_r || attn_r),
+             "attn_proj backward: gradient requested for an absent attention vector");
+  int64_t n, H, F;
+  attn_shapes(feat, {attn_l, attn_r, (const DGLB200Tensor*)grad_attn_l,
+                     (const DGLB200Tensor*)grad_attn_r},
+              {grad_el, grad_er}, &n, &H, &F);
+  check_float(grad_feat, "grad_feat");
+  check_compact(grad_feat, "grad_feat");
+  B200_CHECK(num_elements(grad_feat) == n * H * F, "attn_proj backward: grad_feat must be [N, H, F]");
+  B200_CUDA(cudaSetDevice(feat->ctx.device_id));
+  attn_proj_backward(data_ptr<const float>(feat), attn_l ? data_ptr<const float>(attn_l) : nullptr,
+                     attn_r ? data_ptr<const float>(attn_r) : nullptr,
+                     grad_el ? data_ptr<const float>(grad_el) : nullptr,
+                     grad_er ? data_ptr<const float>(grad_er) : nullptr, data_ptr<float>(grad_feat),
+                     grad_attn_l ? data_ptr<float>(grad_attn_l) : nullptr,
+                     grad_attn_r ? data_ptr<float>(grad_attn_r) : nullptr, n, H, F,
+                     static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
 // ---- fused edge_softmax (extension) ----
 static int64_t softmax_width(DGLB200Graph* g, std::initializer_list<const DGLB200Tensor*> ts) {
   const DGLB200Tensor* first = *ts.begin();

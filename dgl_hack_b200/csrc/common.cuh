@@ -272,6 +272,12 @@ void fused_gat_backward(DGLB200Graph* g, const float* ft, const float* el, const
 // kway.cu (host): multilevel k-way partitioner; returns the edge cut
 int64_t kway_partition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy,
                        const int64_t* vwgt, int k, uint64_t seed, double ubfactor, int64_t* part);
+// attn.cu
+void attn_proj_forward(const float* feat, const float* al, const float* ar, float* el, float* er,
+                       int64_t n, int64_t H, int64_t F, cudaStream_t s);
+void attn_proj_backward(const float* feat, const float* al, const float* ar, const float* gl,
+                        const float* gr, float* gfeat, float* gal, float* gar, int64_t n,
+                        int64_t H, int64_t F, cudaStream_t s);
 // softmax.cu
 void edge_softmax_forward(DGLB200Graph* g, const float* z, float* out, int64_t H, cudaStream_t s);
 void edge_softmax_backward(DGLB200Graph* g, const float* out, const float* gout, float* gz,

@@ -168,3 +168,29 @@ def edge_softmax_backward(G, out, grad_out, grad_score):
     with torch.cuda.device(G.device):
         check_call(LIB.DGLB200EdgeSoftmaxBackward(G.handle, t[0].ptr, t[1].ptr, t[2].ptr,
                                                   _stream(G)))
+
+
+def _keep(*xs):
+    """NDArray views (kept alive by the caller for the duration of the call) and their pointers;
+    None stays NULL."""
+    nds = [None if x is None else _nd(x) for x in xs]
+    return nds, [None if t is None else t.ptr for t in nds]
+
+
+def gat_attn_proj(feat, attn_l, attn_r, el, er):
+    """Extension: el = (feat * attn_l).sum(-1), er = (feat * attn_r).sum(-1) (gatconv.py:143-144)
+    in one pass; a None attention vector / output skips that projection."""
+    keep, ptrs = _keep(feat, attn_l, attn_r, el, er)
+    with torch.cuda.device(feat.device):
+        s = ctypes.c_void_p(torch.cuda.current_stream(feat.device).cuda_stream)
+        check_call(LIB.DGLB200GatAttnProj(*ptrs, s))
+    del keep
+
+
+def gat_attn_proj_backward(feat, attn_l, attn_r, grad_el, grad_er, grad_feat, grad_attn_l,
+                           grad_attn_r):
+    keep, ptrs = _keep(feat, attn_l, attn_r, grad_el, grad_er, grad_feat, grad_attn_l, grad_attn_r)
+    with torch.cuda.device(feat.device):
+        s = ctypes.c_void_p(torch.cuda.current_stream(feat.device).cuda_stream)
+        check_call(LIB.DGLB200GatAttnProjBackward(*ptrs, s))
+    del keep

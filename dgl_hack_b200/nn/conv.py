@@ -221,8 +221,16 @@ class GATConv(nn.Module):
         else:
             h_src = h_dst = self.feat_drop(feat)
             feat_src = feat_dst = self.fc(h_src).view(-1, self._num_heads, self._out_feats)
-        el = (feat_src * self.attn_l).sum(dim=-1).unsqueeze(-1)
-        er = (feat_dst * self.attn_r).sum(dim=-1).unsqueeze(-1)
+        # el = (feat_src * attn_l).sum(-1), er = (feat_dst * attn_r).sum(-1), gatconv.py:143-144:
+        # one streaming kernel each way instead of torch's mul + reduce passes
+        if feat_src is feat_dst and self._num_heads * self._out_feats <= 1024:
+            el, er = B.gat_attn_proj(feat_src, self.attn_l, self.attn_r)
+        elif self._num_heads * self._out_feats <= 1024:
+            el, _ = B.gat_attn_proj(feat_src, self.attn_l, None)
+            _, er = B.gat_attn_proj(feat_dst, None, self.attn_r)
+        else:
+            el = (feat_src * self.attn_l).sum(dim=-1).unsqueeze(-1)
+            er = (feat_dst * self.attn_r).sum(dim=-1).unsqueeze(-1)
         if self._fused and B.fused_gat_supported(self._num_heads, self._out_feats):
             rst = B.fused_gat(graph.gidx, feat_src, el, er, self.negative_slope)
         else:

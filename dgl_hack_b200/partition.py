@@ -79,6 +79,23 @@ def metis_partition_assignment(num_nodes, src, dst, k, balance="nodes", seed=0,
     return (part, int(cut.value)) if return_cut else part
 
 
+def kway_partition_on_rank0(num_nodes, src, dst, world, rank, device, balance="in_edges"):
+    """Rank 0 runs the k-way partitioner (host code) and broadcasts the node -> part vector, the
+    way tools/partition.py partitions once and every trainer loads its part. Returns
+    (part on `device`, seconds rank 0 spent partitioning)."""
+    import time
+    part = torch.empty(num_nodes, dtype=torch.int64, device=device)
+    secs = torch.zeros(1, dtype=torch.float64, device=device)
+    if rank == 0:
+        t0 = time.time()
+        part.copy_(metis_partition_assignment(num_nodes, src, dst, world, balance=balance))
+        secs[0] = time.time() - t0
+    if world > 1:
+        dist.broadcast(part, 0)
+        dist.broadcast(secs, 0)
+    return part, float(secs.item())
+
+
 def partition_graph_with_halo(num_nodes, src, dst, node_part, num_parts=None):
     """1-hop form of `dgl.transform.partition_graph_with_halo(g, node_part, 1)`
     (transform.py:551-586 -> GraphOp::GetSubgraphWithHalo, src/graph/graph_op.cc:403-509) on COO

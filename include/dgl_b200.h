@@ -278,6 +278,22 @@ int DGLB200EdgeSoftmaxBackward(DGLB200GraphHandle graph, const DGLB200Tensor* ou
                                const DGLB200Tensor* grad_out, DGLB200Tensor* grad_score,
                                void* stream);
 
+/* GAT attention projections (python/dgl/nn/pytorch/conv/gatconv.py:143-144):
+ *   el[n,h] = sum_f feat[n,h,f] * attn_l[h,f],  er[n,h] = sum_f feat[n,h,f] * attn_r[h,f]
+ * in one pass over feat [N, H, F]; attn_* are [1, H, F] (or [H, F]); el / er are [N, H, 1].
+ * attn_r / er (or attn_l / el) may be NULL to compute one projection only (bipartite blocks
+ * project source and destination features separately). Backward: grad_feat [N, H, F] =
+ * grad_el * attn_l + grad_er * attn_r and grad_attn_k [H, F] = sum_n grad_k[n,h] * feat[n,h,f]
+ * (two-stage, fixed fold order). H * F <= 1024 for the backward. */
+int DGLB200GatAttnProj(const DGLB200Tensor* feat, const DGLB200Tensor* attn_l,
+                       const DGLB200Tensor* attn_r, DGLB200Tensor* el, DGLB200Tensor* er,
+                       void* stream);
+int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* attn_l,
+                               const DGLB200Tensor* attn_r, const DGLB200Tensor* grad_el,
+                               const DGLB200Tensor* grad_er, DGLB200Tensor* grad_feat,
+                               DGLB200Tensor* grad_attn_l, DGLB200Tensor* grad_attn_r,
+                               void* stream);
+
 /* Dispatch introspection for tests / bench: name of the kernel family the LAST compute call in
  * this process used ("spmm", "generic_row", "generic_edge", ...), and how many kernel launches
  * the library has issued since load (all threads). */

@@ -22,7 +22,8 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "profiles"))
 import dgl_hack_b200 as B  # noqa: E402
 from dgl_hack_b200 import backend as F  # noqa: E402
-from dgl_hack_b200.partition import Partition, PartitionedGraph, range_partition  # noqa: E402
+from dgl_hack_b200.partition import (Partition, PartitionedGraph, range_partition,  # noqa: E402
+                                      kway_partition_on_rank0)
 
 
 def sbm_graph(n, e, blocks, p_in, alpha, seed, dev):
@@ -53,6 +54,9 @@ def main():
     ap.add_argument("--breakdown", action="store_true",
                     help="also time every phase alone (synchronised; no overlap)")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--partition", default="range", choices=["range", "kway"],
+                    help="range: contiguous ranges balanced by in-edges; kway: the library's "
+                         "multilevel k-way partitioner (the reference's metis_partition role)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -64,7 +68,11 @@ def main():
     e = int(61859140 * args.scale)
     d = args.feat
     src, dst = sbm_graph(n, e, 64, 0.85, 0.5, 5, dev)
-    part = range_partition(n, dst, world)
+    part_s = 0.0
+    if args.partition == "kway" and world > 1:
+        part, part_s = kway_partition_on_rank0(n, src, dst, world, rank, dev)
+    else:
+        part = range_partition(n, dst, world)
     p = Partition.build(n, src, dst, part, rank, world)
     pg = PartitionedGraph(p, dev)
     gen = torch.Generator(device=dev)
@@ -157,8 +165,9 @@ def main():
         line = {"metric": "partitioned copy_src+sum fwd+bwd", "n_gpus": world, "scaling": "strong",
                 "ms_per_step": round(ms.item(), 4),
                 "gedges_per_s": round(2 * e / ms.item() / 1e6, 3),
-                "config": {"workload": "products-shaped SBM N=%d E=%d D=%d, range partition" %
-                           (n, e, d)},
+                "config": {"workload": "products-shaped SBM N=%d E=%d D=%d, %s partition" %
+                           (n, e, d, args.partition)},
+                "partition_seconds_rank0": round(part_s, 2),
                 "cut_fraction": round(float(st[:, 1].sum() / st[:, 0].sum()), 4),
                 "max_local_edges": int(st[:, 0].max()), "max_halo_nodes": int(st[:, 3].max()),
                 "halo_bytes_per_step_per_rank_max": int(st[:, 3].max()) * d * 4 * 2,
