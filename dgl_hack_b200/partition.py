@@ -178,6 +178,55 @@ class Partition(object):
         p.send_cat = torch.cat(p.send_idx) if world > 1 else p.send_idx[0]
         return p
 
+    @classmethod
+    def from_files(cls, directory, rank, world, device="cpu"):
+        """The same plan as `build`, from the per-part files partition_tool.py writes (the way the
+        reference's trainers load `<part_id>.dgl`): this rank's file gives its nodes and edges, the
+        other parts' `induced_nodes` / `inner_node` / `part_id` give what they need from here."""
+        import numpy as np
+        files = [np.load(os.path.join(directory, "%d.npz" % q)) for q in range(world)]
+        me = files[rank]
+        assert int(me["num_parts"]) == world, "files were written for another number of parts"
+        p = cls()
+        p.rank, p.world = rank, world
+        dev = torch.device(device)
+        t = lambda a: torch.from_numpy(np.asarray(a)).to(dev)  # noqa: E731
+        nodes, inner, owner = t(me["induced_nodes"]), t(me["inner_node"]).bool(), t(me["part_id"])
+        p.inner_global = nodes[inner]
+        p.n_inner = int(p.inner_global.numel())
+        halo, halo_owner = nodes[~inner], owner[~inner]
+        order = torch.argsort(halo_owner * int(me["num_nodes"]) + halo)
+        p.halo_global = halo[order]
+        p.n_halo = int(halo.numel())
+        p.halo_counts = torch.bincount(halo_owner, minlength=world).tolist()
+        # local ids of the file (parent order) -> plan ids (inner first, halo grouped by owner)
+        remap = torch.empty(nodes.numel(), dtype=torch.int64, device=dev)
+        remap[torch.nonzero(inner).flatten()] = torch.arange(p.n_inner, device=dev)
+        remap[torch.nonzero(~inner).flatten()[order]] = p.n_inner + torch.arange(p.n_halo, device=dev)
+        # edges back in parent edge-id order (= the order `build` keeps)
+        eorder = torch.argsort(t(me["induced_edges"]))
+        ls, ld = remap[t(me["src"])[eorder]], remap[t(me["dst"])[eorder]]
+        remote = ~t(me["inner_edge"]).bool()[eorder]
+        p.edges_inner = (ls[~remote], ld[~remote])
+        p.edges_halo = (ls[remote] - p.n_inner, ld[remote])
+        p.local_edges = int(ls.numel())
+        p.cut_edges = int(remote.sum())
+        g2l = {int(g): i for i, g in enumerate(p.inner_global.tolist())} if world > 1 else {}
+        p.send_idx = []
+        for q in range(world):
+            if q == rank:
+                p.send_idx.append(torch.empty(0, dtype=torch.int64, device=dev))
+                continue
+            fq = files[q]
+            need = np.sort(fq["induced_nodes"][(fq["inner_node"] == 0) & (fq["part_id"] == rank)])
+            p.send_idx.append(torch.tensor([g2l[int(g)] for g in need], dtype=torch.int64,
+                                           device=dev))
+        p.send_counts = [int(x.numel()) for x in p.send_idx]
+        p.send_cat = torch.cat(p.send_idx) if world > 1 else p.send_idx[0]
+        p.node_feats = {k[5:]: t(me[k])[torch.nonzero(inner).flatten()] for k in me.files
+                        if k.startswith("feat/")}
+        return p
+
     def _a2a(self):
         """One all-to-all-v instead of 2(k-1) grouped sends/recvs where the backend has it (NCCL)."""
         return self.world > 1 and dist.is_initialized() and dist.get_backend() == "nccl"

@@ -12,7 +12,8 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from dgl_hack_b200.partition import Partition, range_partition, _HaloCopySum
+from dgl_hack_b200.partition import (Partition, range_partition, kway_partition_on_rank0,
+                                     _HaloCopySum)
 
 
 def _free_port():
@@ -42,6 +43,9 @@ def _worker(rank, world, port, n, e, d, method, q):
         w = torch.rand(n, d, generator=g, dtype=torch.float64)
         if method == "range":
             part = range_partition(n, dst, world)
+        elif method == "kway":  # rank 0 runs the library's k-way partitioner and broadcasts
+            part, _ = kway_partition_on_rank0(n, src, dst, world, rank, torch.device("cpu"))
+            assert int(part.min()) >= 0 and int(part.max()) < world
         else:
             part = torch.randint(0, world, (n,), generator=torch.Generator().manual_seed(9))
         p = Partition.build(n, src, dst, part, rank, world)
@@ -79,7 +83,7 @@ def _worker(rank, world, port, n, e, d, method, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,method", [(2, "range"), (2, "random"), (3, "random")])
+@pytest.mark.parametrize("world,method", [(2, "range"), (2, "random"), (3, "random"), (2, "kway")])
 def test_halo_exchange_matches_single_graph(world, method):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
