@@ -783,6 +783,22 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
   API_END();
 }
 
+// ---- neighbour sampling (extension) ----
+int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,
+                           int fanout, int replace, uint64_t rng_seed, const int64_t* offsets,
+                           int64_t* out_src, int64_t* out_dst, int64_t* out_eid, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph != nullptr, "NULL graph");
+  B200_CHECK(n_seeds >= 0, "SampleNeighbors: negative number of seeds");
+  B200_CHECK(n_seeds == 0 || (seeds && offsets && out_src && out_dst && out_eid),
+             "SampleNeighbors: NULL argument");
+  B200_CHECK(fanout != 0, "SampleNeighbors: fanout must be positive, or negative for all in-edges");
+  B200_CUDA(cudaSetDevice(graph->device));
+  sample_neighbors(graph, seeds, n_seeds, fanout, replace != 0, rng_seed, offsets, out_src, out_dst,
+                   out_eid, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
 // ---- fused edge_softmax (extension) ----
 static int64_t softmax_width(DGLB200Graph* g, std::initializer_list<const DGLB200Tensor*> ts) {
   const DGLB200Tensor* first = *ts.begin();

@@ -278,6 +278,10 @@ void attn_proj_forward(const float* feat, const float* al, const float* ar, floa
 void attn_proj_backward(const float* feat, const float* al, const float* ar, const float* gl,
                         const float* gr, float* gfeat, float* gal, float* gar, int64_t n,
                         int64_t H, int64_t F, cudaStream_t s);
+// sample.cu
+void sample_neighbors(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, int fanout,
+                      bool replace, uint64_t rng_seed, const int64_t* offsets, int64_t* out_src,
+                      int64_t* out_dst, int64_t* out_eid, cudaStream_t s);
 // softmax.cu
 void edge_softmax_forward(DGLB200Graph* g, const float* z, float* out, int64_t H, cudaStream_t s);
 void edge_softmax_backward(DGLB200Graph* g, const float* out, const float* gout, float* gz,

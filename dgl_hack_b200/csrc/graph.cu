@@ -15,6 +15,32 @@
 
 namespace b200 {
 
+// Graph arrays live in the device's stream-ordered memory pool (cudaMallocAsync) with the release
+// threshold raised, so building and dropping a graph -- which the mini-batch path does for every
+// sampled block -- costs no cudaMalloc / cudaFree round trips (each one a device-wide
+// synchronisation plus ~100 us of driver work; 15 arrays per graph). An array is allocated on the
+// stream that first writes it and freed in stream order (or after a device synchronise when the
+// whole graph goes away).
+static void pool_init(int device) {
+  static bool done[64] = {};
+  if (device < 0 || device >= 64 || done[device]) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    uint64_t keep = UINT64_MAX;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  }
+  done[device] = true;
+}
+
+template <typename T>
+static cudaError_t pool_alloc(T** p, size_t bytes, cudaStream_t s) {
+  return cudaMallocAsync(reinterpret_cast<void**>(p), bytes ? bytes : 4, s);
+}
+
+static void pool_free(void* p, cudaStream_t s) {
+  if (p) cudaFreeAsync(p, s);
+}
+
 // ---------------------------------------------------------------- small utilities
 __global__ void fill_f32_kernel(float* __restrict__ p, int64_t n, float v) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -351,12 +377,15 @@ static void coo_to_csr_device(int64_t n_rows, int64_t nnz, const int32_t* rows,
 }
 
 // ---------------------------------------------------------------- lazily built per-CSR arrays
-static void ensure_device(int device) { B200_CUDA(cudaSetDevice(device)); }
+static void ensure_device(int device) {
+  B200_CUDA(cudaSetDevice(device));
+  pool_init(device);
+}
 
 const int32_t* csr_rows(DGLB200Graph* g, int walk, cudaStream_t s) {
   Csr& c = (walk == kWalkOut) ? g->out : g->in;  // in_sorted shares the in-CSR's indptr
   if (!c.row) {
-    B200_CUDA(cudaMalloc(&c.row, std::max<int64_t>(g->num_edges, 1) * 4));
+    B200_CUDA(pool_alloc(&c.row, std::max<int64_t>(g->num_edges, 1) * 4, s));
     expand_rows(c.indptr, c.n_rows, c.row, s);
   }
   return c.row;
@@ -369,7 +398,7 @@ const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s) {
   Csr& o = out_csr ? g->in : g->out;
   if (!c.to_other) {
     const int64_t e = g->num_edges;
-    B200_CUDA(cudaMalloc(&c.to_other, std::max<int64_t>(e, 1) * 4));
+    B200_CUDA(pool_alloc(&c.to_other, std::max<int64_t>(e, 1) * 4, s));
     if (e > 0) {
       // pos_of_eid_in_other[o.eids[q]] = q ; to_other[p] = pos_of_eid_in_other[c.eids[p]]
       Scratch inv((size_t)e * 4, s);
@@ -439,13 +468,13 @@ __global__ void seg_fill_kernel(const int32_t* __restrict__ indptr, int64_t n_ro
     heavy_ptr[heavy_idx[n_rows]] = seg_off[n_rows];  // sentinel: totals after the scans
 }
 
-static void free_plan(Csr::Plan& p) {
-  cudaFree(p.seg_row);
-  cudaFree(p.seg_beg);
-  cudaFree(p.seg_end);
-  cudaFree(p.heavy_row);
-  cudaFree(p.heavy_ptr);
-  cudaFree(p.sched);
+static void free_plan(Csr::Plan& p, cudaStream_t s) {
+  pool_free(p.seg_row, s);
+  pool_free(p.seg_beg, s);
+  pool_free(p.seg_end, s);
+  pool_free(p.heavy_row, s);
+  pool_free(p.heavy_ptr, s);
+  pool_free(p.sched, s);
   p = Csr::Plan();
 }
 
@@ -463,7 +492,7 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
       csr.plan_next = (csr.plan_next + 1) % Csr::kPlanSlots;
       // a kernel enqueued earlier may still read the evicted plan
       B200_CUDA(cudaStreamSynchronize(s));
-      free_plan(csr.plan[slot]);
+      free_plan(csr.plan[slot], s);
     }
   }
   struct View {  // the CSR's shape + the chosen slot's fields under the names used below
@@ -505,15 +534,15 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
         int32_t *sk, *sv;
         radix_sort_pairs(key.as<int32_t>(), kb.as<int32_t>(), nullptr, va.as<int32_t>(),
                          vb.as<int32_t>(), c.n_rows, 256, &sk, &sv, s);
-        B200_CUDA(cudaMalloc(&c.sched, (size_t)c.n_rows * 4));
+        B200_CUDA(pool_alloc(&c.sched, (size_t)c.n_rows * 4, s));
         B200_CUDA(cudaMemcpyAsync(c.sched, sv, (size_t)c.n_rows * 4, cudaMemcpyDeviceToDevice, s));
       }
       if (c.n_seg > 0) {
-        B200_CUDA(cudaMalloc(&c.seg_row, (size_t)c.n_seg * 4));
-        B200_CUDA(cudaMalloc(&c.seg_beg, (size_t)c.n_seg * 4));
-        B200_CUDA(cudaMalloc(&c.seg_end, (size_t)c.n_seg * 4));
-        B200_CUDA(cudaMalloc(&c.heavy_row, (size_t)c.n_heavy * 4));
-        B200_CUDA(cudaMalloc(&c.heavy_ptr, (size_t)(c.n_heavy + 1) * 4));
+        B200_CUDA(pool_alloc(&c.seg_row, (size_t)c.n_seg * 4, s));
+        B200_CUDA(pool_alloc(&c.seg_beg, (size_t)c.n_seg * 4, s));
+        B200_CUDA(pool_alloc(&c.seg_end, (size_t)c.n_seg * 4, s));
+        B200_CUDA(pool_alloc(&c.heavy_row, (size_t)c.n_heavy * 4, s));
+        B200_CUDA(pool_alloc(&c.heavy_ptr, (size_t)(c.n_heavy + 1) * 4, s));
         seg_fill_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, seg_len, nseg.as<int32_t>(),
                                                heavy.as<int32_t>(), c.seg_row, c.seg_beg,
                                                c.seg_end, c.heavy_row, c.heavy_ptr);
@@ -536,22 +565,22 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
   return p;
 }
 
-static void free_csr(Csr& c) {
-  cudaFree(c.indptr);
-  cudaFree(c.indices);
-  cudaFree(c.eids);
-  cudaFree(c.row);
-  cudaFree(c.to_other);
-  for (int k = 0; k < Csr::kPlanSlots; ++k) free_plan(c.plan[k]);
+static void free_csr(Csr& c, cudaStream_t s = nullptr) {
+  pool_free(c.indptr, s);
+  pool_free(c.indices, s);
+  pool_free(c.eids, s);
+  pool_free(c.row, s);
+  pool_free(c.to_other, s);
+  for (int k = 0; k < Csr::kPlanSlots; ++k) free_plan(c.plan[k], s);
   c = Csr();
 }
 
-static void alloc_csr(Csr& c, int64_t n_rows, int64_t n_cols, int64_t nnz) {
+static void alloc_csr(Csr& c, int64_t n_rows, int64_t n_cols, int64_t nnz, cudaStream_t s) {
   c.n_rows = n_rows;
   c.n_cols = n_cols;
-  B200_CUDA(cudaMalloc(&c.indptr, (size_t)(n_rows + 1) * 4));
-  B200_CUDA(cudaMalloc(&c.indices, (size_t)std::max<int64_t>(nnz, 1) * 4));
-  B200_CUDA(cudaMalloc(&c.eids, (size_t)std::max<int64_t>(nnz, 1) * 4));
+  B200_CUDA(pool_alloc(&c.indptr, (size_t)(n_rows + 1) * 4, s));
+  B200_CUDA(pool_alloc(&c.indices, (size_t)std::max<int64_t>(nnz, 1) * 4, s));
+  B200_CUDA(pool_alloc(&c.eids, (size_t)std::max<int64_t>(nnz, 1) * 4, s));
 }
 
 // in_s = Transpose(out-CSR): stable sort of the out-CSR positions by destination.
@@ -561,9 +590,9 @@ static void build_in_sorted(DGLB200Graph* g, cudaStream_t s) {
   c.n_rows = g->num_dst;
   c.n_cols = g->num_src;
   c.indptr = g->in.indptr;  // alias (never freed through in_s)
-  B200_CUDA(cudaMalloc(&c.indices, (size_t)std::max<int64_t>(e, 1) * 4));
-  B200_CUDA(cudaMalloc(&c.eids, (size_t)std::max<int64_t>(e, 1) * 4));
-  B200_CUDA(cudaMalloc(&c.to_other, (size_t)std::max<int64_t>(e, 1) * 4));
+  B200_CUDA(pool_alloc(&c.indices, (size_t)std::max<int64_t>(e, 1) * 4, s));
+  B200_CUDA(pool_alloc(&c.eids, (size_t)std::max<int64_t>(e, 1) * 4, s));
+  B200_CUDA(pool_alloc(&c.to_other, (size_t)std::max<int64_t>(e, 1) * 4, s));
   if (e == 0) return;
   const int32_t* out_row = csr_rows(g, kWalkOut, s);
   Scratch ip((size_t)(g->num_dst + 1) * 4, s);
@@ -595,8 +624,8 @@ const int32_t* graph_coo(DGLB200Graph* g, int which, cudaStream_t s) {
     const int64_t e = g->num_edges;
     const size_t eb = (size_t)std::max<int64_t>(e, 1) * 4;
     int32_t *cs = nullptr, *cd = nullptr;
-    B200_CUDA(cudaMalloc(&cs, eb));
-    B200_CUDA(cudaMalloc(&cd, eb));
+    B200_CUDA(pool_alloc(&cs, eb, s));
+    B200_CUDA(pool_alloc(&cd, eb, s));
     if (e > 0) {
       const int32_t* in_row = csr_rows(g, kWalkIn, s);
       const int blocks = (int)std::min<int64_t>((e + 255) / 256, 148 * 16);
@@ -609,17 +638,17 @@ const int32_t* graph_coo(DGLB200Graph* g, int which, cudaStream_t s) {
   return which ? g->coo_dst : g->coo_src;
 }
 
-static void free_typed(TypeIndex& t) {
-  cudaFree(t.in.ids);
-  cudaFree(t.in.eids);
-  cudaFree(t.in.types);
-  cudaFree(t.out.ids);
-  cudaFree(t.out.eids);
-  cudaFree(t.out.types);
-  cudaFree(t.bt_src);
-  cudaFree(t.bt_dst);
-  cudaFree(t.bt_eid);
-  cudaFree(t.type_ptr);
+static void free_typed(TypeIndex& t, cudaStream_t s = nullptr) {
+  pool_free(t.in.ids, s);
+  pool_free(t.in.eids, s);
+  pool_free(t.in.types, s);
+  pool_free(t.out.ids, s);
+  pool_free(t.out.eids, s);
+  pool_free(t.out.types, s);
+  pool_free(t.bt_src, s);
+  pool_free(t.bt_dst, s);
+  pool_free(t.bt_eid, s);
+  pool_free(t.type_ptr, s);
   t = TypeIndex();
 }
 
@@ -630,11 +659,11 @@ static void build_typed(DGLB200Graph* g, const int32_t* et, int64_t num_types, c
   const int64_t e = g->num_edges;
   const size_t eb = (size_t)std::max<int64_t>(e, 1) * 4;
   TypeIndex& t = g->ty;
-  free_typed(t);
+  free_typed(t, s);  // a previous typing: released in stream order
   int32_t** arrays[] = {&t.in.ids, &t.in.eids, &t.in.types, &t.out.ids, &t.out.eids,
                         &t.out.types, &t.bt_src, &t.bt_dst, &t.bt_eid};
-  for (auto a : arrays) B200_CUDA(cudaMalloc(a, eb));
-  B200_CUDA(cudaMalloc(&t.type_ptr, (size_t)(num_types + 1) * 4));
+  for (auto a : arrays) B200_CUDA(pool_alloc(a, eb, s));
+  B200_CUDA(pool_alloc(&t.type_ptr, (size_t)(num_types + 1) * 4, s));
   t.num_types = num_types;
   fill_i32(t.type_ptr, num_types + 1, 0, s);
   if (e == 0) return;
@@ -743,29 +772,29 @@ int DGLB200GraphCreateFromCOO(int64_t num_src, int64_t num_dst, int64_t num_edge
   g->num_edges = num_edges;
   g->device = device;
   try {
-    alloc_csr(g->in, num_dst, num_src, num_edges);
-    alloc_csr(g->out, num_src, num_dst, num_edges);
+    alloc_csr(g->in, num_dst, num_src, num_edges, s);
+    alloc_csr(g->out, num_src, num_dst, num_edges, s);
     const int64_t e = num_edges;
     Scratch s32((size_t)std::max<int64_t>(e, 1) * 4, s), d32((size_t)std::max<int64_t>(e, 1) * 4, s);
     upload_idx(src, 64, e, s32.as<int32_t>(), s);
     upload_idx(dst, 64, e, d32.as<int32_t>(), s);
     // in-CSR = COOToCSR keyed by dst (immutable_graph.cc:407-421); keep the row expansion,
     // the transpose needs it.
-    B200_CUDA(cudaMalloc(&g->in.row, (size_t)std::max<int64_t>(e, 1) * 4));
+    B200_CUDA(pool_alloc(&g->in.row, (size_t)std::max<int64_t>(e, 1) * 4, s));
     coo_to_csr_device(num_dst, e, d32.as<int32_t>(), s32.as<int32_t>(), nullptr, g->in.indptr,
                       g->in.indices, g->in.eids, g->in.row, nullptr, s);
     // out-CSR = in_csr.Transpose() (immutable_graph.cc:424-437): stable sort of in-CSR positions
     // by src; column = dst row of the position, data = its edge id. The sorted position
     // permutation is out->in ("to_other" of the out-CSR), kept because it is free here.
-    B200_CUDA(cudaMalloc(&g->out.to_other, (size_t)std::max<int64_t>(e, 1) * 4));
+    B200_CUDA(pool_alloc(&g->out.to_other, (size_t)std::max<int64_t>(e, 1) * 4, s));
     coo_to_csr_device(num_src, e, g->in.indices, g->in.row, g->in.eids, g->out.indptr,
                       g->out.indices, g->out.eids, nullptr, g->out.to_other, s);
     build_in_sorted(g, s);
   } catch (...) {
     g->in_s.indptr = nullptr;
-    free_csr(g->in_s);
-    free_csr(g->in);
-    free_csr(g->out);
+    free_csr(g->in_s, s);
+    free_csr(g->in, s);
+    free_csr(g->out, s);
     delete g;
     throw;
   }
@@ -791,8 +820,8 @@ int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edge
   g->num_edges = num_edges;
   g->device = device;
   try {
-    alloc_csr(g->in, num_dst, num_src, num_edges);
-    alloc_csr(g->out, num_src, num_dst, num_edges);
+    alloc_csr(g->in, num_dst, num_src, num_edges, s);
+    alloc_csr(g->out, num_src, num_dst, num_edges, s);
     upload_idx(in_indptr, idx_bits, num_dst + 1, g->in.indptr, s);
     upload_idx(in_indices, idx_bits, num_edges, g->in.indices, s);
     upload_idx(in_eids, idx_bits, num_edges, g->in.eids, s);
@@ -803,9 +832,9 @@ int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edge
     B200_CUDA(cudaStreamSynchronize(s));  // host buffers may be released by the caller now
   } catch (...) {
     g->in_s.indptr = nullptr;
-    free_csr(g->in_s);
-    free_csr(g->in);
-    free_csr(g->out);
+    free_csr(g->in_s, s);
+    free_csr(g->in, s);
+    free_csr(g->out, s);
     delete g;
     throw;
   }
@@ -817,10 +846,11 @@ int DGLB200GraphFree(DGLB200GraphHandle g) {
   API_BEGIN();
   if (g) {
     cudaSetDevice(g->device);
-    cudaDeviceSynchronize();
+    cudaDeviceSynchronize();  // nothing on any stream still reads the arrays
+    cudaStream_t s = nullptr;
     free_typed(g->ty);
-    cudaFree(g->coo_src);
-    cudaFree(g->coo_dst);
+    pool_free(g->coo_src, s);
+    pool_free(g->coo_dst, s);
     g->in_s.indptr = nullptr;
     free_csr(g->in_s);
     free_csr(g->in);
@@ -890,7 +920,7 @@ int DGLB200GraphSetEdgeTypes(DGLB200GraphHandle g, const void* etypes, int idx_b
   try {
     build_typed(g, et.as<int32_t>(), num_types, s);
   } catch (...) {
-    free_typed(g->ty);
+    free_typed(g->ty, s);
     throw;
   }
   B200_CUDA(cudaStreamSynchronize(s));

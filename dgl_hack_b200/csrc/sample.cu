@@ -1,0 +1,123 @@
+// Uniform neighbour sampling over the in-CSR: the device form of
+// dgl.sampling.sample_neighbors(g, seeds, fanout, replace) and dgl.in_subgraph(g, seeds) that the
+// fork's mini-batch trainers call on the host (examples/pytorch/graphsage/
+// train_sampling_multi_gpu.py:22-38, python/dgl/sampling/neighbor.py, src/graph/sampling/).
+//
+// The caller sizes the output from the in-degrees (offsets[i] = first output slot of seed i):
+//   fanout < 0           : every in-edge of the seed, in in-CSR (edge id) order   -> in_subgraph
+//   replace              : `fanout` independent uniform picks (none for in-degree 0)
+//   !replace, deg<=fanout: every in-edge once
+//   !replace, deg> fanout: `fanout` distinct in-edges (Floyd's algorithm; selection sampling for
+//                          fanouts above the per-thread table)
+// Randomness is a counter-based hash of (rng_seed, seed index, draw), so a call is reproducible
+// and independent of the launch shape. Outputs are global ids (int64): src, dst = seed, edge id.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace b200 {
+namespace {
+
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {  // splitmix64 finaliser
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+__device__ __forceinline__ uint32_t draw(uint64_t key, uint64_t i, uint64_t k, uint32_t n) {
+  const uint64_t r = mix64(mix64(key ^ (i * 0xD1B54A32D192ED03ull)) + k);
+  return (uint32_t)(((r >> 32) * (uint64_t)n) >> 32);  // unbiased enough for n << 2^32
+}
+
+struct SampleArgs {
+  const int32_t *indptr, *indices, *eids;
+  const int64_t *seeds, *offsets;
+  int64_t *out_src, *out_dst, *out_eid;
+  int64_t n_seeds;
+  int fanout, replace;
+  uint64_t key;
+};
+
+constexpr int kTable = 64;  // distinct picks kept per thread (Floyd)
+
+// with replacement / copy-all: one thread per output slot of a seed, a warp per seed
+__global__ void __launch_bounds__(256) sample_simple_kernel(SampleArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < a.n_seeds; i += warps) {
+    const int64_t v = a.seeds[i];
+    const int beg = __ldg(a.indptr + v), deg = __ldg(a.indptr + v + 1) - beg;
+    const int64_t o = a.offsets[i];
+    const int cnt = (int)(a.offsets[i + 1] - o);
+    const bool all = cnt == deg && !(a.replace && a.fanout >= 0);
+    for (int k = lane; k < cnt; k += 32) {
+      const int p = beg + (all ? k : (int)draw(a.key, (uint64_t)i, (uint64_t)k, (uint32_t)deg));
+      a.out_src[o + k] = __ldg(a.indices + p);
+      a.out_dst[o + k] = v;
+      a.out_eid[o + k] = __ldg(a.eids + p);
+    }
+  }
+}
+
+// without replacement, in-degree above the fanout: one thread per seed
+__global__ void __launch_bounds__(128) sample_distinct_kernel(SampleArgs a) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_seeds; i += stride) {
+    const int64_t v = a.seeds[i];
+    const int beg = __ldg(a.indptr + v), deg = __ldg(a.indptr + v + 1) - beg;
+    if (deg <= a.fanout) continue;  // copied by sample_simple_kernel
+    const int64_t o = a.offsets[i];
+    const int f = a.fanout;
+    if (f <= kTable) {
+      int pick[kTable];
+      for (int k = 0; k < f; ++k) {  // Floyd: j runs over deg - f .. deg - 1
+        const int j = deg - f + k;
+        int t = (int)draw(a.key, (uint64_t)i, (uint64_t)k, (uint32_t)(j + 1));
+        for (int q = 0; q < k; ++q)
+          if (pick[q] == t) { t = j; break; }
+        pick[k] = t;
+      }
+      for (int k = 0; k < f; ++k) {
+        const int p = beg + pick[k];
+        a.out_src[o + k] = __ldg(a.indices + p);
+        a.out_dst[o + k] = v;
+        a.out_eid[o + k] = __ldg(a.eids + p);
+      }
+    } else {  // selection sampling: position q is taken with probability needed / remaining
+      int need = f, k = 0;
+      for (int q = 0; q < deg && need > 0; ++q) {
+        if (draw(a.key, (uint64_t)i, (uint64_t)q, (uint32_t)(deg - q)) < (uint32_t)need) {
+          const int p = beg + q;
+          a.out_src[o + k] = __ldg(a.indices + p);
+          a.out_dst[o + k] = v;
+          a.out_eid[o + k] = __ldg(a.eids + p);
+          ++k, --need;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace
+
+void sample_neighbors(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, int fanout,
+                      bool replace, uint64_t rng_seed, const int64_t* offsets, int64_t* out_src,
+                      int64_t* out_dst, int64_t* out_eid, cudaStream_t s) {
+  if (n_seeds == 0) return;
+  SampleArgs a{g->in.indptr, g->in.indices, g->in.eids, seeds, offsets, out_src, out_dst, out_eid,
+               n_seeds, fanout, replace ? 1 : 0, mix64(rng_seed)};
+  const int blocks = (int)std::min<int64_t>((n_seeds + 7) / 8, 148 * 16);
+  if (replace || fanout < 0) {
+    sample_simple_kernel<<<blocks, 256, 0, s>>>(a);
+    note_kernel("sample_neighbors", 1);
+  } else {
+    // rows with deg <= fanout are copied whole; the others are overwritten by distinct picks
+    sample_simple_kernel<<<blocks, 256, 0, s>>>(a);
+    sample_distinct_kernel<<<(int)std::min<int64_t>((n_seeds + 127) / 128, 148 * 16), 128, 0, s>>>(a);
+    note_kernel("sample_neighbors", 2);
+  }
+  B200_CUDA(cudaGetLastError());
+}
+
+}  // namespace b200

@@ -1,0 +1,136 @@
+"""Mini-batch blocks on the device: `sample_neighbors`, `in_subgraph`,
+`to_block` with the reference's meaning (python/dgl/sampling/neighbor.py, python/dgl/transform.py
+in_subgraph / to_block; used by examples/pytorch/graphsage/train_sampling_multi_gpu.py:22-38),
+so the sampled trainers run entirely on the GPU: sampling is one kernel over the in-CSR
+(csrc/sample.cu), compaction is a few torch ops, and the block is a bipartite
+`dgl_hack_b200.graph.Graph` consumed by the same kernels as the full graph.
+
+    frontier = sample_neighbors(g, seeds, fanout, replace=True)
+    block = to_block(frontier, seeds)            # block.srcdata[NID], dstdata[NID], edata[EID]
+    h = layer(block, (x[block.srcdata[NID]], x[block.dstdata[NID]]))
+
+Differences from the reference are confined to the random stream (a counter-based hash instead of
+the host RNG): which neighbours are drawn differs, the distribution and every structural rule do
+not (fanout picks per seed with replacement, min(deg, fanout) distinct ones without, nothing for
+zero in-degree; block sources = destinations first, then new sources by first appearance).
+"""
+import ctypes
+
+import torch
+
+from ._lib import LIB, DGLError, check_call
+from .graph import Graph
+
+NID = "_ID"
+EID = "_ID"
+
+__all__ = ["NID", "EID", "Frontier", "sample_neighbors", "in_subgraph", "to_block",
+           "compact_block"]
+
+
+class Frontier(object):
+    """Sampled edges in parent ids, grouped by seed: src, dst, eid (int64 device tensors)."""
+
+    def __init__(self, src, dst, eid, num_nodes):
+        self.src, self.dst, self.eid, self.num_nodes = src, dst, eid, num_nodes
+
+    def number_of_edges(self):
+        return int(self.src.numel())
+
+    def all_edges(self):
+        return self.src, self.dst
+
+
+_counter = [0]
+
+
+def _gidx(g):
+    return g.gidx if hasattr(g, "gidx") else g
+
+
+def sample_neighbors(g, seeds, fanout, replace=False, rng_seed=None):
+    """`fanout` in-neighbours of every seed, uniformly (dgl.sampling.sample_neighbors with
+    edge_dir='in', prob=None). fanout = -1 selects every in-edge. `rng_seed` makes a call
+    reproducible; by default a per-process counter seeded from torch's generator is used."""
+    gidx = _gidx(g)
+    dev = gidx.device
+    seeds = torch.as_tensor(seeds, dtype=torch.int64, device=dev).contiguous()
+    if seeds.dim() != 1:
+        raise DGLError("seeds must be a 1-D tensor of node ids")
+    if fanout == 0:
+        raise DGLError("fanout must be positive (or -1 for all in-edges)")
+    if seeds.numel() and (int(seeds.min()) < 0 or int(seeds.max()) >= gidx.num_dst):
+        raise DGLError("seed id out of range")
+    deg = gidx.in_degrees()[seeds]
+    if fanout < 0:
+        cnt = deg
+    elif replace:
+        cnt = torch.where(deg > 0, torch.full_like(deg, fanout), torch.zeros_like(deg))
+    else:
+        cnt = deg.clamp(max=fanout)
+    offsets = torch.zeros(seeds.numel() + 1, dtype=torch.int64, device=dev)
+    torch.cumsum(cnt, 0, out=offsets[1:])
+    total = int(offsets[-1].item())
+    out = torch.empty((3, max(total, 1)), dtype=torch.int64, device=dev)
+    if rng_seed is None:
+        if _counter[0] == 0:
+            _counter[0] = int(torch.randint(1, 2 ** 62, (1,)).item())
+        _counter[0] += 1
+        rng_seed = _counter[0]
+    with torch.cuda.device(dev):
+        check_call(LIB.DGLB200SampleNeighbors(
+            gidx.handle, ctypes.c_void_p(seeds.data_ptr()), int(seeds.numel()), int(fanout),
+            int(bool(replace)), int(rng_seed) & (2 ** 64 - 1), ctypes.c_void_p(offsets.data_ptr()),
+            ctypes.c_void_p(out[0].data_ptr()), ctypes.c_void_p(out[1].data_ptr()),
+            ctypes.c_void_p(out[2].data_ptr()),
+            ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
+    out = out[:, :total]
+    return Frontier(out[0], out[1], out[2], gidx.num_dst)
+
+
+def in_subgraph(g, nodes):
+    """All in-edges of `nodes` (dgl.in_subgraph): grouped by node, edge-id order inside a node."""
+    return sample_neighbors(g, nodes, -1)
+
+
+def compact_block(src, dst, dst_nodes):
+    """Relabelling of dgl.to_block on plain tensors (any device): returns (src_nid, src_local,
+    dst_local) -- block source nodes are `dst_nodes` first, then the other sources by first
+    appearance in `src`; edges keep their order."""
+    dev = src.device
+    dst_nodes = torch.as_tensor(dst_nodes, dtype=torch.int64, device=dev)
+    n_dst = int(dst_nodes.numel())
+    allv = torch.cat([dst_nodes, src])
+    uniq, inv = torch.unique(allv, return_inverse=True)
+    if n_dst and int(torch.unique(dst_nodes).numel()) != n_dst:
+        raise DGLError("to_block: destination nodes must be unique")
+    first = torch.full((uniq.numel(),), allv.numel(), dtype=torch.int64, device=dev)
+    first.scatter_reduce_(0, inv, torch.arange(allv.numel(), device=dev), "amin")
+    order = torch.argsort(first)                      # unique values by first appearance
+    rank = torch.empty_like(order)
+    rank[order] = torch.arange(order.numel(), device=dev)
+    src_nid = uniq[order]
+    src_local = rank[inv[n_dst:]]
+    pos = torch.searchsorted(uniq, dst).clamp(max=max(int(uniq.numel()) - 1, 0))
+    if dst.numel() and not torch.equal(uniq[pos], dst):
+        raise DGLError("to_block: an edge ends in a node that is not a destination node")
+    dst_local = rank[pos] if dst.numel() else dst
+    if dst_local.numel() and int(dst_local.max()) >= n_dst:
+        raise DGLError("to_block: an edge ends in a node that is not a destination node")
+    return src_nid, src_local, dst_local
+
+
+def to_block(frontier, dst_nodes, device=None):
+    """Bipartite block of a frontier (dgl.to_block): destination nodes = `dst_nodes` (unique), source
+    nodes = the destinations first, then every other source in order of first appearance; edges
+    keep the frontier's order. Parent ids are stored as block.srcdata[NID], dstdata[NID],
+    edata[EID]."""
+    dev = frontier.src.device if device is None else torch.device(device)
+    dst_nodes = torch.as_tensor(dst_nodes, dtype=torch.int64, device=dev)
+    src_nid, src_local, dst_local = compact_block(frontier.src, frontier.dst, dst_nodes)
+    block = Graph(src_local, dst_local, num_src=int(src_nid.numel()),
+                  num_dst=int(dst_nodes.numel()), device=dev)
+    block.srcdata[NID] = src_nid
+    block.dstdata[NID] = dst_nodes
+    block.edata[EID] = frontier.eid
+    return block

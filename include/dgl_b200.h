@@ -294,6 +294,18 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
                                DGLB200Tensor* grad_attn_l, DGLB200Tensor* grad_attn_r,
                                void* stream);
 
+/* Uniform neighbour sampling on the device: dgl.sampling.sample_neighbors(g, seeds, fanout,
+ * replace) / dgl.in_subgraph(g, seeds) (python/dgl/sampling/neighbor.py, used by
+ * examples/pytorch/graphsage/train_sampling_multi_gpu.py:27-38). seeds[n_seeds] and
+ * offsets[n_seeds + 1] are DEVICE int64 arrays; offsets is the exclusive prefix sum of the
+ * per-seed output counts the caller derives from the in-degrees: deg for fanout < 0 (all
+ * in-edges, in-CSR order), (deg > 0 ? fanout : 0) with replacement, min(deg, fanout) without.
+ * Outputs (device int64, offsets[n_seeds] entries): source node, destination (= the seed) and
+ * edge id of every sampled edge, grouped by seed. Reproducible for a given rng_seed. */
+int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,
+                           int fanout, int replace, uint64_t rng_seed, const int64_t* offsets,
+                           int64_t* out_src, int64_t* out_dst, int64_t* out_eid, void* stream);
+
 /* Dispatch introspection for tests / bench: name of the kernel family the LAST compute call in
  * this process used ("spmm", "generic_row", "generic_edge", ...), and how many kernel launches
  * the library has issued since load (all threads). */
