@@ -158,18 +158,34 @@ __global__ void __launch_bounds__(kBwdVThreads) attn_proj_bwd_vec_kernel(
   }
 }
 
-// grad_attn_k[col] = sum over blocks, in block order (deterministic).
-__global__ void attn_proj_fold_kernel(const float* __restrict__ part, float* __restrict__ gal,
-                                      float* __restrict__ gar, int n_blocks, int D) {
-  const int col = blockIdx.x * blockDim.x + threadIdx.x;
-  if (col >= D) return;
+// grad_attn_k[col] = sum of the block partials in a FIXED order: 32 row groups x 32 columns per
+// CTA, row group q folds blocks q, q + 32, ... sequentially (independent loads), then the 32 group
+// sums are folded in group order through shared memory. (The first version walked all partials
+// with one thread per column: 295 us for 2,368 partials -- more than the streaming kernel itself.)
+__global__ void __launch_bounds__(1024) attn_proj_fold_kernel(const float* __restrict__ part,
+                                                              float* __restrict__ gal,
+                                                              float* __restrict__ gar, int n_blocks,
+                                                              int D) {
+  __shared__ float sh[2][32][33];
+  const int c = threadIdx.x & 31, q = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + c;
   float sl = 0.f, sr = 0.f;
-  for (int b = 0; b < n_blocks; ++b) {
-    sl = __fadd_rn(sl, part[((int64_t)b * 2 + 0) * D + col]);
-    sr = __fadd_rn(sr, part[((int64_t)b * 2 + 1) * D + col]);
+  if (col < D) {
+#pragma unroll 4
+    for (int b = q; b < n_blocks; b += 32) {
+      sl = __fadd_rn(sl, __ldg(part + ((int64_t)b * 2 + 0) * D + col));
+      sr = __fadd_rn(sr, __ldg(part + ((int64_t)b * 2 + 1) * D + col));
+    }
   }
-  if (gal) gal[col] = sl;
-  if (gar) gar[col] = sr;
+  sh[0][q][c] = sl;
+  sh[1][q][c] = sr;
+  __syncthreads();
+  if (q < 2 && col < D) {
+    float acc = 0.f;
+    for (int k = 0; k < 32; ++k) acc = __fadd_rn(acc, sh[q][k][c]);
+    float* dst = q == 0 ? gal : gar;
+    if (dst) dst[col] = acc;
+  }
 }
 
 int sm_count() {
@@ -200,7 +216,7 @@ void attn_proj_backward(const float* feat, const float* al, const float* ar, con
                         int64_t H, int64_t F, cudaStream_t s) {
   const int64_t D = H * F;
   B200_CHECK(D <= kBwdThreads * kBwdCols, "attn_proj: H * F above 1024 is not supported");
-  int n_blocks = (int)std::min<int64_t>(std::max<int64_t>(n, 1), (int64_t)sm_count() * 16);
+  int n_blocks = (int)std::min<int64_t>(std::max<int64_t>(n, 1), (int64_t)sm_count() * 5);
   const int rows = (int)((n + n_blocks - 1) / std::max(n_blocks, 1));
   n_blocks = rows > 0 ? (int)((n + rows - 1) / rows) : 0;
   Scratch part((size_t)std::max(n_blocks, 1) * 2 * D * sizeof(float), s);
@@ -218,8 +234,8 @@ void attn_proj_backward(const float* feat, const float* al, const float* ar, con
                                                           part.as<float>(), n, rows, (int)H, (int)F);
     B200_CUDA(cudaGetLastError());
   }
-  attn_proj_fold_kernel<<<(int)((D + 127) / 128), 128, 0, s>>>(part.as<float>(), gal, gar, n_blocks,
-                                                               (int)D);
+  attn_proj_fold_kernel<<<(int)((D + 31) / 32), 1024, 0, s>>>(part.as<float>(), gal, gar, n_blocks,
+                                                              (int)D);
   B200_CUDA(cudaGetLastError());
   note_kernel("attn_proj_bwd", 2);
 }
