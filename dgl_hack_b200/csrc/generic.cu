@@ -73,6 +73,9 @@ __global__ void __launch_bounds__(256) generic_row_kernel(const GArgs a, int lan
   for (int64_t r = (int64_t)blockIdx.x * rows_per_block + threadIdx.x / lanes_per_row;
        r < a.n_rows; r += (int64_t)gridDim.x * rows_per_block) {
     const int beg = __ldg(a.indptr + r), end = __ldg(a.indptr + r + 1);
+    // with a destination id map only rows that have edges own a slot (reference maps hold -1 or
+    // end early for the others); such rows keep the value written by the fill
+    if (dmap && beg == end) continue;
     const int64_t drow = dmap ? __ldg(dmap + r) : r;
     for (int j = lane; j < a.n_elem; j += lanes_per_row) {
       int tx = j, k = 0;

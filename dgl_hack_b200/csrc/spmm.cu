@@ -379,7 +379,7 @@ bool try_spmm(const KernelCall& c) {
     const int tch = round_tma_ch((nvec + 31) / 32);
     const int64_t row_bytes = D * 4;
     bool ok = (lpr == 32) && (bmode == kBNone || scalar_w) && tch > 0 && row_bytes <= 8192 &&
-              aligned(A, 16);
+              aligned(A, 16) && o_map == nullptr;  // id-mapped outputs stay on the LDG path
     const int64_t mean_deg = E / std::max<int64_t>(csr.n_rows, 1);
     // Measured on B200 (profiles/r1_spmm_paths.md): the LDG path beats the bulk-copy path on
     // this gather (TMA 1-D copies of 2.4 KB rows top out near 20-30 B/clk/SM), so it is opt-in.

@@ -149,6 +149,11 @@ spmm_kernel(const SpmmArgs a) {
       if (a.n_seg > 0 && deg > a.seg_len) {  // heavy row: served by its segments
         row_ok = false;
         deg = 0;
+      } else if (a.out_map && deg == 0) {
+        // with an output id map only rows that receive edges have a slot (the reference's
+        // _build_idx_map holds -1 / ends early for the others, runtime/scheduler.py): the row
+        // keeps the identity written by the fill and the map is never read for it
+        row_ok = false;
       }
     }
   }

@@ -276,6 +276,92 @@ class Graph(object):
             reduced.update(apply_node_func(NodeBatch(self, data)))
         self._dst_frame.update(reduced)
 
+    # ---- partial message passing (id-mapped kernels) --------------------------------------
+    def edge_subindex(self, eids):
+        """Unit graph over the selected edges with the parent's node ids, plus the (forward,
+        backward) edge-id maps the kernels take: what runtime/spmv.py:146-180
+        build_gidx_and_mapping_uv builds for send_and_recv / pull (forward map in out-CSR order,
+        backward map in in-CSR order), constructed on the device."""
+        eids = th.as_tensor(eids, dtype=th.int64, device=self.device)
+        gidx = GraphIndex.from_coo(self._ns, self._nd, self._src[eids], self._dst[eids],
+                                   self.device)
+        e32 = eids.to(th.int32)
+        fwd = e32[gidx.get_adj_csr(True)[2].long()]
+        bwd = e32[gidx.get_adj_csr(False)[2].long()]
+        return gidx, (fwd, bwd)
+
+    def _reduce_on(self, eids, recv, message_func, reduce_func, apply_node_func):
+        mfuncs = message_func if isinstance(message_func, (list, tuple)) else [message_func]
+        rfuncs = reduce_func if isinstance(reduce_func, (list, tuple)) else [reduce_func]
+        if not (all(isinstance(m, fn.MessageFunction) for m in mfuncs)
+                and all(isinstance(r, fn.ReduceFunction) for r in rfuncs)):
+            raise DGLError("partial message passing takes builtin message and reduce functions")
+        gidx, emap = self.edge_subindex(eids)
+        o2n = th.full((self._nd,), -1, dtype=th.int32, device=self.device)
+        o2n[recv] = th.arange(recv.numel(), dtype=th.int32, device=self.device)
+        omap, none, n_out = (o2n, o2n), (None, None), int(recv.numel())
+        by_field = {m.out_field: m for m in mfuncs}
+        reduced = {}
+        for r in rfuncs:
+            if r.msg_field not in by_field:
+                raise DGLError('Reduce function requires message field "%s", but no message '
+                               'function generates it.' % r.msg_field)
+            m = by_field[r.msg_field]
+            if isinstance(m, fn.CopyMessageFunction):
+                reduced[r.out_field] = F.copy_reduce(
+                    r.name, gidx, m.target, self._col(m.target, m.in_field), n_out,
+                    emap if m.target == fn.TargetCode.EDGE else none, omap)
+            else:
+                reduced[r.out_field] = F.binary_reduce(
+                    r.name, m.binary_op, gidx, m.lhs, m.rhs, self._col(m.lhs, m.lhs_field),
+                    self._col(m.rhs, m.rhs_field), n_out,
+                    emap if m.lhs == fn.TargetCode.EDGE else none,
+                    emap if m.rhs == fn.TargetCode.EDGE else none, omap)
+        if apply_node_func is not None:
+            data = {k: v.index_select(0, recv) for k, v in self._dst_frame.items()}
+            data.update(reduced)
+            reduced.update(apply_node_func(NodeBatch(self, data)))
+        for k, v in reduced.items():  # WRITE_ROW_: only the receiving rows change
+            if k in self._dst_frame and self._dst_frame[k].shape[1:] == v.shape[1:]:
+                base = self._dst_frame[k]
+            else:
+                base = v.new_zeros((self._nd,) + tuple(v.shape[1:]))
+            self._dst_frame[k] = base.index_copy(0, recv, v)
+
+    def send_and_recv(self, edges, message_func, reduce_func, apply_node_func=None):
+        """Messages along the edges with ids `edges`, reduced at their destinations; only those
+        destination rows are written (scheduler.py schedule_snr)."""
+        eids = th.as_tensor(edges, dtype=th.int64, device=self.device)
+        if eids.numel() == 0:
+            return
+        recv = th.unique(self._dst[eids])
+        self._reduce_on(eids, recv, message_func, reduce_func, apply_node_func)
+
+    def pull(self, v, message_func, reduce_func, apply_node_func=None):
+        """All in-edges of the nodes `v` send, `v` receive (scheduler.py schedule_pull): nodes of
+        `v` without in-edges get the reducer's identity."""
+        from . import sampling
+        v = th.unique(th.as_tensor(v, dtype=th.int64, device=self.device))
+        if v.numel() == 0:
+            return
+        eids = sampling.in_subgraph(self, v).eid
+        if eids.numel() == 0:
+            if apply_node_func is not None:
+                data = {k: x.index_select(0, v) for k, x in self._dst_frame.items()}
+                for k, x in apply_node_func(NodeBatch(self, data)).items():
+                    self._dst_frame[k] = self._dst_frame[k].index_copy(0, v, x)
+            return
+        self._reduce_on(eids, v, message_func, reduce_func, apply_node_func)
+
+    def push(self, u, message_func, reduce_func, apply_node_func=None):
+        """All out-edges of the nodes `u` send, their destinations receive (scheduler.py
+        schedule_push = send_and_recv over the out-edges)."""
+        u = th.as_tensor(u, dtype=th.int64, device=self.device)
+        mark = th.zeros(self._ns, dtype=th.bool, device=self.device)
+        mark[u] = True
+        self.send_and_recv(th.nonzero(mark[self._src]).flatten(), message_func, reduce_func,
+                           apply_node_func)
+
     def apply_nodes(self, func):
         self._dst_frame.update(func(NodeBatch(self, dict(self._dst_frame))))
 

@@ -72,10 +72,13 @@ class EdgeSoftmaxFused(th.autograd.Function):
 
 def edge_softmax(graph, logits, eids=None):
     """graph: dgl_hack_b200.Graph or GraphIndex; logits [E, *, 1] (any trailing shape) in edge-id
-    order. `eids` (softmax over an edge subgraph, softmax.py:58-59) is not on this path."""
+    order; with `eids` the softmax runs over that edge subgraph (softmax.py:58-59) and logits holds one
+    row per selected edge."""
     if eids is not None:
-        raise NotImplementedError("edge_softmax over an edge subset is outside this path")
-    gidx = _gidx(graph)
+        # softmax.py:58-59: `g.edge_subgraph(eids)`; row i of logits belongs to edge eids[i]
+        gidx, _ = graph.edge_subindex(eids)
+    else:
+        gidx = _gidx(graph)
     if logits.shape[0] != gidx.number_of_edges():
         raise ValueError("logits must hold one row per edge")
     if os.environ.get("B200_EDGE_SOFTMAX", "fused") == "builtin":
