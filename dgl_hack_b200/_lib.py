@@ -109,6 +109,8 @@ SYMBOLS = {
     "DGLB200SampleNeighbors": (_c.c_int, [GraphHandle, _c.c_void_p, _c.c_int64, _c.c_int, _c.c_int,
                                           _c.c_uint64, _c.c_void_p, _c.c_void_p, _c.c_void_p,
                                           _c.c_void_p, _c.c_void_p]),
+    "DGLB200KernelScaledCopySum": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP, TensorP,
+                                              TensorP, _c.c_void_p]),
     "DGLB200EdgeSoftmaxForward": (_c.c_int, [GraphHandle, TensorP, TensorP, _c.c_void_p]),
     "DGLB200EdgeSoftmaxBackward": (_c.c_int, [GraphHandle, TensorP, TensorP, TensorP,
                                               _c.c_void_p]),

@@ -193,6 +193,36 @@ class FusedGat(th.autograd.Function):
         return None, grad_feat_src, grad_el, grad_er, None, None, None, None
 
 
+class ScaledCopySum(th.autograd.Function):
+    """out[v] = row_scale[v] * sum_{u->v} col_scale[u] * x[u]; the scales are constants of the
+    graph (degree norms), only x is differentiated: grad_x[u] = col_scale[u] * sum_{u->v}
+    row_scale[v] * grad_out[v] -- the same kernel on the transposed walk with the scales swapped."""
+
+    @staticmethod
+    def forward(ctx, graph, x, col_scale, row_scale):
+        out = x.new_empty((graph.num_dst,) + tuple(x.shape[1:]))
+        K.scaled_copy_sum(graph, False, x, col_scale, row_scale, out)
+        ctx.backward_cache = graph, col_scale, row_scale
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        graph, col_scale, row_scale = ctx.backward_cache
+        grad_out = grad_out.contiguous()
+        grad_x = grad_out.new_empty((graph.num_src,) + tuple(grad_out.shape[1:]))
+        K.scaled_copy_sum(graph, True, grad_out, row_scale, col_scale, grad_x)
+        return None, grad_x, None, None
+
+
+def scaled_copy_sum(graph, x, col_scale=None, row_scale=None):
+    """update_all(copy_src, sum) with per-source and per-destination scalars applied inside the
+    kernel (GraphConv's norm='both' / 'right'); scales are float vectors of length num_src /
+    num_dst that need no gradient."""
+    cs = col_scale.detach().contiguous().reshape(-1) if col_scale is not None else None
+    rs = row_scale.detach().contiguous().reshape(-1) if row_scale is not None else None
+    return ScaledCopySum.apply(graph, x.contiguous(), cs, rs)
+
+
 class GatAttnProj(th.autograd.Function):
     """el / er of gatconv.py:143-144 as one streaming kernel each way (csrc/attn.cu)."""
 

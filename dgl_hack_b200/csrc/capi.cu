@@ -799,6 +799,75 @@ int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64
   API_END();
 }
 
+// ---- scaled aggregation (extension): GraphConv's degree normalisation inside the SpMM ----
+int DGLB200KernelScaledCopySum(DGLB200GraphHandle graph, int transpose, const DGLB200Tensor* in_data,
+                               const DGLB200Tensor* col_scale, const DGLB200Tensor* row_scale,
+                               DGLB200Tensor* out_data, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && in_data && out_data, "NULL argument");
+  check_ctx(graph, {in_data, col_scale, row_scale, out_data},
+            {"in_data", "col_scale", "row_scale", "out_data"});
+  check_float(in_data, "in_data");
+  check_float(out_data, "out_data");
+  check_compact(in_data, "in_data");
+  check_compact(out_data, "out_data");
+  const int64_t n_cols = transpose ? graph->num_dst : graph->num_src;  // gathered side
+  const int64_t n_rows = transpose ? graph->num_src : graph->num_dst;  // written side
+  B200_CHECK(in_data->ndim >= 1 && in_data->shape[0] == n_cols,
+             "ScaledCopySum: in_data must have one row per gathered node");
+  B200_CHECK(out_data->ndim >= 1 && out_data->shape[0] == n_rows &&
+                 feat_len(out_data) == feat_len(in_data),
+             "ScaledCopySum: out_data must have one row per reducing node and in_data's width");
+  if (col_scale) {
+    check_float(col_scale, "col_scale");
+    check_compact(col_scale, "col_scale");
+    B200_CHECK(num_elements(col_scale) == n_cols, "ScaledCopySum: col_scale needs one value per gathered node");
+  }
+  if (row_scale) {
+    check_float(row_scale, "row_scale");
+    check_compact(row_scale, "row_scale");
+    B200_CHECK(num_elements(row_scale) == n_rows, "ScaledCopySum: row_scale needs one value per reducing node");
+  }
+  int64_t sshape[2] = {n_cols, 1};
+  DGLB200Tensor sview = *in_data;  // [n_cols, 1] view of col_scale for the broadcast description
+  sview.ndim = 2;
+  sview.shape = sshape;
+  sview.strides = nullptr;
+  KernelCall c;
+  c.g = graph;
+  c.red = kSum;
+  c.op = col_scale ? kMul : kUseLhs;
+  c.bc = col_scale ? make_bcast("mul", in_data, &sview) : make_bcast("use_lhs", in_data, nullptr);
+  c.lhs_tgt = kSrc;
+  c.out = nullptr;
+  c.dst = data_ptr<float>(out_data);
+  c.dst_rows = n_rows;
+  c.lhs_map = c.rhs_map = c.out_map = nullptr;
+  c.mean = false;
+  c.row_scale = row_scale ? data_ptr<const float>(row_scale) : nullptr;
+  c.stream = static_cast<cudaStream_t>(stream);
+  c.rhs = col_scale ? data_ptr<const float>(col_scale) : nullptr;
+  c.rhs_rows = col_scale ? n_cols : 0;
+  if (!transpose) {   // out[v] = rs[v] * sum_{u -> v} cs[u] * in[u]
+    c.mode = kFwd;
+    c.rhs_tgt = col_scale ? kSrc : kNone;
+    c.lhs = data_ptr<const float>(in_data);
+    c.gout = nullptr;
+    c.lhs_rows = n_cols;
+    c.out_rows = n_rows;
+  } else {            // out[u] = rs[u] * sum_{u -> v} cs[v] * in[v]: the gradient's transposed walk
+    c.mode = kGradLhs;
+    c.rhs_tgt = col_scale ? kDst : kNone;
+    c.lhs = data_ptr<const float>(out_data);  // never read: only the other operand and grad_out are
+    c.gout = data_ptr<const float>(in_data);
+    c.lhs_rows = n_rows;
+    c.out_rows = n_cols;
+  }
+  B200_CUDA(cudaSetDevice(graph->device));
+  B200_CHECK(try_spmm(c), "ScaledCopySum: shape not supported by the SpMM kernel");
+  API_END();
+}
+
 // ---- fused edge_softmax (extension) ----
 static int64_t softmax_width(DGLB200Graph* g, std::initializer_list<const DGLB200Tensor*> ts) {
   const DGLB200Tensor* first = *ts.begin();

@@ -255,6 +255,7 @@ struct KernelCall {
   const int32_t *lhs_map, *rhs_map, *out_map;  // user mappings (NULL = none)
   Bcast bc;
   bool mean;  // extension: divide the row sum by max(deg, 1)
+  const float* row_scale = nullptr;  // extension (SpMM only): multiply finished row r by row_scale[r]
   cudaStream_t stream;
 };
 

@@ -91,17 +91,20 @@ __global__ void __launch_bounds__(128)
 combine_partials_kernel(const int32_t* __restrict__ heavy_row,
                         const int32_t* __restrict__ heavy_ptr, const float* __restrict__ partial,
                         const int32_t* __restrict__ indptr, float* __restrict__ out,
-                        const int32_t* __restrict__ out_map, int D, int red, int mean) {
+                        const int32_t* __restrict__ out_map, int D, int red, int mean,
+                        const float* __restrict__ row_scale) {
   const int h = blockIdx.x;
   const int r = heavy_row[h];
   const int p0 = heavy_ptr[h], p1 = heavy_ptr[h + 1];
   const int64_t orow = out_map ? out_map[r] : r;
   const int deg = indptr[r + 1] - indptr[r];
   const float dn = (float)(deg > 1 ? deg : 1);
+  const float rs = row_scale ? row_scale[r] : 1.f;
   for (int col = threadIdx.x; col < D; col += blockDim.x) {
     float acc = partial[(int64_t)p0 * D + col];
     for (int k = p0 + 1; k < p1; ++k) acc = red_call(red, acc, partial[(int64_t)k * D + col]);
     if (mean) acc = __fdiv_rn(acc, dn);
+    if (row_scale) acc = __fmul_rn(acc, rs);
     out[orow * D + col] = acc;
   }
 }
@@ -176,6 +179,7 @@ bool try_spmm(const KernelCall& c) {
   a.a_pos_ids = nullptr;
   a.a_node_map = nullptr;
   a.mean = c.mean ? 1 : 0;
+  a.row_scale = c.row_scale;
   a.red = c.red;
   a.op = c.op;
   int bmode = kBNone;
@@ -368,7 +372,7 @@ bool try_spmm(const KernelCall& c) {
     if (plan.n_seg == 0) return;
     combine_partials_kernel<<<plan.n_heavy, 128, 0, s>>>(
         plan.heavy_row, plan.heavy_ptr, partial.as<float>(), csr.indptr, c.dst, o_map, (int)D,
-        a.red, a.mean);
+        a.red, a.mean, a.row_scale);
     note_kernel(nullptr, 1);
   };
 
@@ -379,7 +383,7 @@ bool try_spmm(const KernelCall& c) {
     const int tch = round_tma_ch((nvec + 31) / 32);
     const int64_t row_bytes = D * 4;
     bool ok = (lpr == 32) && (bmode == kBNone || scalar_w) && tch > 0 && row_bytes <= 8192 &&
-              aligned(A, 16) && o_map == nullptr;  // id-mapped outputs stay on the LDG path
+              aligned(A, 16) && o_map == nullptr && c.row_scale == nullptr;  // mapped / scaled: LDG path
     const int64_t mean_deg = E / std::max<int64_t>(csr.n_rows, 1);
     // Measured on B200 (profiles/r1_spmm_paths.md): the LDG path beats the bulk-copy path on
     // this gather (TMA 1-D copies of 2.4 KB rows top out near 20-30 B/clk/SM), so it is opt-in.

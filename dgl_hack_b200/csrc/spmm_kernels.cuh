@@ -37,6 +37,7 @@ struct SpmmArgs {
   int b_head_div;  // kBHead: B column = A column / b_head_div
   int b_is_lhs;
   int op, red, mean;
+  const float* row_scale;  // optional: every finished output row is multiplied by row_scale[row]
   float* out;
   const int32_t* out_map;
   int need_col;
@@ -286,6 +287,11 @@ spmm_kernel(const SpmmArgs a) {
         if (a.mean && !is_seg) {
 #pragma unroll
           for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fdiv_rn(acc[c].v[e], dn);
+        }
+        if (a.row_scale && !is_seg) {
+          const float rs = __ldg(a.row_scale + r);
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fmul_rn(acc[c].v[e], rs);
         }
         st_vec<VEC>(op + c * lpr * VEC, acc[c]);
       }

@@ -194,3 +194,13 @@ def gat_attn_proj_backward(feat, attn_l, attn_r, grad_el, grad_er, grad_feat, gr
         s = ctypes.c_void_p(torch.cuda.current_stream(feat.device).cuda_stream)
         check_call(LIB.DGLB200GatAttnProjBackward(*ptrs, s))
     del keep
+
+
+def scaled_copy_sum(G, transpose, X, col_scale, row_scale, out):
+    """Extension: out[r] = row_scale[r] * sum over r's edges of col_scale[c] * X[c] on the in-CSR
+    (transpose False) or the out-CSR (True); GraphConv's normalisation inside the SpMM."""
+    keep, ptrs = _keep(X, col_scale, row_scale, out)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelScaledCopySum(G.handle, int(bool(transpose)), *ptrs,
+                                                  _stream(G)))
+    del keep

@@ -6,6 +6,8 @@ reference modules, so results match the reference CPU path on identical inputs a
 are torch (cuBLAS) matmuls exactly as in the reference; everything that touches the graph goes
 through the B200 kernels.
 """
+import os
+
 import torch as th
 from torch import nn
 from torch.nn import functional as tF
@@ -56,11 +58,20 @@ class GraphConv(nn.Module):
         if self.bias is not None:
             init.zeros_(self.bias)
 
+    def _norms(self, graph):
+        """(source scale, destination scale) of graphconv.py:128-133, 165-172 as float vectors,
+        cached on the graph index (they depend on the structure only)."""
+        cache = graph.gidx.__dict__.setdefault("_graphconv_norm", {})
+        if self._norm not in cache:
+            ind = graph.in_degrees().float().clamp(min=1)
+            if self._norm == "both":
+                outd = graph.out_degrees().float().clamp(min=1)
+                cache[self._norm] = (th.pow(outd, -0.5), th.pow(ind, -0.5))
+            else:
+                cache[self._norm] = (None, 1.0 / ind)
+        return cache[self._norm]
+
     def forward(self, graph, feat, weight=None):
-        graph = graph.local_var()
-        if self._norm == "both":
-            degs = graph.out_degrees().to(feat.device).float().clamp(min=1)
-            feat = feat * _bcast_rows(th.pow(degs, -0.5), feat)
         if weight is not None:
             if self.weight is not None:
                 raise DGLError("External weight is provided while at the same time the module has"
@@ -69,6 +80,38 @@ class GraphConv(nn.Module):
         else:
             weight = self.weight
         mult_first = self._in_feats > self._out_feats
+        if os.environ.get("B200_GRAPHCONV_FUSED", "1") == "0":
+            return self._forward_unfused(graph, feat, weight, mult_first)
+        # Same arithmetic as the reference, with `feat * norm_src` and `rst * norm_dst` applied
+        # inside the aggregation kernel (one pass over the features instead of three).
+        cs, rs = self._norms(graph) if self._norm != "none" else (None, None)
+        pad = 0
+        if mult_first and weight is not None:
+            # aggregate at a width that is a multiple of 4 floats: 16-byte aligned rows take the
+            # vector path of the kernel (47 classes: 4.7 -> 2.6 ms at products scale); the zero
+            # columns are dropped again after the aggregation
+            pad = (-self._out_feats) % 4 if feat.dim() == 2 else 0
+            w = tF.pad(weight, (0, pad)) if pad else weight
+            # the reference scales the rows before the product (graphconv.py:133, 148); scaling
+            # inside the aggregation is the same product per element, one rounding later
+            feat = th.matmul(feat, w)
+        rst = B.scaled_copy_sum(graph.gidx, feat, cs, rs)
+        if pad:
+            rst = rst[..., :self._out_feats]
+        if not mult_first and weight is not None:
+            rst = th.matmul(rst, weight)
+        if self.bias is not None:
+            rst = rst + self.bias
+        if self._activation is not None:
+            rst = self._activation(rst)
+        return rst
+
+    def _forward_unfused(self, graph, feat, weight, mult_first):
+        """graphconv.py:128-176 step by step (B200_GRAPHCONV_FUSED=0)."""
+        graph = graph.local_var()
+        if self._norm == "both":
+            degs = graph.out_degrees().to(feat.device).float().clamp(min=1)
+            feat = feat * _bcast_rows(th.pow(degs, -0.5), feat)
         if mult_first and weight is not None:
             feat = th.matmul(feat, weight)
         graph.srcdata["h"] = feat

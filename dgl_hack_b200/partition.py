@@ -399,9 +399,49 @@ class PartitionedGraph(object):
         K.copy_reduce("sum", self.g_rev, 2, recv, add)
         return g_inner.add_(add)
 
-    def copy_src_sum(self, x_inner):
-        """Halo-exchanging `update_all(copy_src, sum)` for this rank's inner nodes."""
-        return _HaloCopySum.apply(self.part, self._agg, self._agg_t, x_inner)
+    def copy_src_sum(self, x_inner, src_scale=None, dst_scale=None):
+        """Halo-exchanging `update_all(copy_src, sum)` for this rank's inner nodes. With scales
+        (float vectors over the inner nodes, constants of the graph such as GraphConv's degree
+        norms): out[v] = dst_scale[v] * sum_{u->v} src_scale[u] * x[u], the scaling done inside the
+        aggregation kernels (backend.scaled_copy_sum); the halo nodes' src_scale values are
+        fetched from their owners once and cached."""
+        if src_scale is None and dst_scale is None:
+            return _HaloCopySum.apply(self.part, self._agg, self._agg_t, x_inner)
+        from . import kernel as K
+        part = self.part
+        cs_in = src_scale.detach().reshape(-1).contiguous() if src_scale is not None else None
+        rs = dst_scale.detach().reshape(-1).contiguous() if dst_scale is not None else None
+        cs_halo = None
+        if cs_in is not None:
+            cache = self.__dict__.setdefault("_halo_scale", {})
+            key = (cs_in.data_ptr(), cs_in._version)
+            if key not in cache:
+                cache.clear()
+                h = cs_in.new_ones((max(part.n_halo, 1),))
+                if part.world > 1:
+                    peer, part.peer = part.peer, None      # width 1: not a peer-push shape
+                    reqs, got, keep = part.start_forward_exchange(cs_in.reshape(-1, 1))
+                    for r in reqs:
+                        r.wait()
+                    part.peer = peer
+                    h[:part.n_halo] = got.reshape(-1)
+                cache[key] = h
+            cs_halo = cache[key]
+
+        def agg(which, x):
+            g, cs = (self.g_inner, cs_in) if which == "inner" else (self.g_halo, cs_halo)
+            out = x.new_empty((part.n_inner,) + tuple(x.shape[1:]))
+            K.scaled_copy_sum(g, False, x.contiguous(), cs, rs, out)
+            return out
+
+        def agg_t(which, grad_out):
+            g, cs = (self.g_inner, cs_in) if which == "inner" else (self.g_halo, cs_halo)
+            n_src = part.n_inner if which == "inner" else part.n_halo
+            rows = max(n_src, 1) if which == "halo" else n_src
+            grad = grad_out.new_empty((rows,) + tuple(grad_out.shape[1:]))
+            K.scaled_copy_sum(g, True, grad_out, rs, cs, grad)
+            return grad[:n_src]
+        return _HaloCopySum.apply(part, agg, agg_t, x_inner)
 
 
 class _RawCuda(object):

@@ -306,6 +306,16 @@ int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64
                            int fanout, int replace, uint64_t rng_seed, const int64_t* offsets,
                            int64_t* out_src, int64_t* out_dst, int64_t* out_eid, void* stream);
 
+/* Aggregation with GraphConv's degree scaling inside the kernel (python/dgl/nn/pytorch/conv/
+ * graphconv.py:128-176 does `feat * norm`, update_all(copy_src, sum), `rst * norm` as three
+ * passes): transpose = 0: out[v] = row_scale[v] * sum_{u -> v} col_scale[u] * in[u];
+ * transpose = 1 (its gradient): out[u] = row_scale[u] * sum_{u -> v} col_scale[v] * in[v].
+ * Either scale may be NULL. Same summation orders as CopyReduce / BackwardCopyReduce. */
+int DGLB200KernelScaledCopySum(DGLB200GraphHandle graph, int transpose,
+                               const DGLB200Tensor* in_data, const DGLB200Tensor* col_scale,
+                               const DGLB200Tensor* row_scale, DGLB200Tensor* out_data,
+                               void* stream);
+
 /* Dispatch introspection for tests / bench: name of the kernel family the LAST compute call in
  * this process used ("spmm", "generic_row", "generic_edge", ...), and how many kernel launches
  * the library has issued since load (all threads). */

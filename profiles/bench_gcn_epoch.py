@@ -26,6 +26,9 @@ from dgl_hack_b200.partition import (Partition, PartitionedGraph, range_partitio
                                       kway_partition_on_rank0)
 
 
+FUSED = os.environ.get("B200_GRAPHCONV_FUSED", "1") != "0"
+
+
 class GCN(torch.nn.Module):
     def __init__(self, dims):
         super().__init__()
@@ -40,12 +43,23 @@ class GCN(torch.nn.Module):
     def forward(self, pg, h, norm_src, norm_dst):
         n = len(self.w)
         for k, (w, b) in enumerate(zip(self.w, self.b)):
-            if w.shape[0] > w.shape[1]:      # graphconv.py:138-147: shrink first
-                h = (h @ w) * norm_src
-                h = pg.copy_src_sum(h)
+            if FUSED:
+                # degree scaling inside the aggregation kernels; a width that is not a multiple of
+                # 4 floats is aggregated zero-padded (what nn.GraphConv does)
+                if w.shape[0] > w.shape[1]:
+                    pad = (-w.shape[1]) % 4
+                    h = h @ (torch.nn.functional.pad(w, (0, pad)) if pad else w)
+                    h = pg.copy_src_sum(h, norm_src, norm_dst)[:, :w.shape[1]]
+                else:
+                    h = pg.copy_src_sum(h, norm_src, norm_dst) @ w
+                h = h + b      # (torch.addmm materialises the broadcast bias first: slower here)
             else:
-                h = pg.copy_src_sum(h * norm_src) @ w
-            h = h * norm_dst + b
+                if w.shape[0] > w.shape[1]:      # graphconv.py:138-147: shrink first
+                    h = (h @ w) * norm_src
+                    h = pg.copy_src_sum(h)
+                else:
+                    h = pg.copy_src_sum(h * norm_src) @ w
+                h = h * norm_dst + b
             if k + 1 < n:
                 h = torch.relu(h)
         return h
@@ -115,11 +129,16 @@ def main():
     dist.barrier()
     torch.cuda.synchronize()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    prof = os.environ.get("B200_PROFILE") == "1"   # ncu --profile-from-start off: timed epochs only
+    if prof:
+        torch.cuda.cudart().cudaProfilerStart()
     a.record()
     for _ in range(args.epochs):
         loss = epoch()
     b.record()
     torch.cuda.synchronize()
+    if prof:
+        torch.cuda.cudart().cudaProfilerStop()
     ms = torch.tensor([a.elapsed_time(b) / args.epochs], device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     lsum = loss.detach().clone()
@@ -135,7 +154,7 @@ def main():
                 "partition_seconds_rank0": round(part_s, 2),
                 "loss": round(lsum.item(), 5), "halo_nodes_total": int(halo[0].item()),
                 "cut_fraction": round(halo[1].item() / max(halo[2].item(), 1), 4),
-                "epochs": args.epochs, "warmup": args.warmup}
+                "epochs": args.epochs, "warmup": args.warmup, "fused_norm": FUSED}
         print(json.dumps(line), flush=True)
         if args.out:
             os.makedirs(os.path.dirname(args.out), exist_ok=True)

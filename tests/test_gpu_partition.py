@@ -112,3 +112,31 @@ def test_partitioned_two_gpus_nccl():
         pr.join(timeout=120)
         assert pr.exitcode == 0
     assert all(r[1] and r[2] for r in res), res
+
+
+@pytest.mark.gpu
+def test_partitioned_scaled_copy_sum_world1():
+    """PartitionedGraph.copy_src_sum with degree scales == backend.scaled_copy_sum on the graph."""
+    import numpy as np
+    import torch
+    import dgl_hack_b200 as B
+    from dgl_hack_b200 import backend as F
+    from dgl_hack_b200.partition import Partition, PartitionedGraph
+    dev = torch.device("cuda:0")
+    n, e = 500, 6000
+    gen = torch.Generator().manual_seed(2)
+    src = torch.randint(0, n, (e,), generator=gen)
+    dst = torch.randint(0, n, (e,), generator=gen)
+    part = torch.zeros(n, dtype=torch.int64)
+    p = Partition.build(n, src.to(dev), dst.to(dev), part.to(dev), 0, 1)
+    pg = PartitionedGraph(p, dev)
+    g = B.GraphIndex.from_coo(n, n, src, dst, dev)
+    x = torch.rand(n, 12, generator=gen).to(dev).requires_grad_(True)
+    cs, rs = torch.rand(n, generator=gen).to(dev) + 0.1, torch.rand(n, generator=gen).to(dev) + 0.1
+    go = torch.rand(n, 12, generator=gen).to(dev)
+    a = pg.copy_src_sum(x, cs, rs)
+    a.backward(go)
+    ga, x.grad = x.grad.clone(), None
+    b = F.scaled_copy_sum(g, x, cs, rs)
+    b.backward(go)
+    assert torch.equal(a, b) and torch.equal(ga, x.grad)
