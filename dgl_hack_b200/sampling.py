@@ -31,8 +31,11 @@ __all__ = ["NID", "EID", "Frontier", "sample_neighbors", "in_subgraph", "to_bloc
 class Frontier(object):
     """Sampled edges in parent ids, grouped by seed: src, dst, eid (int64 device tensors)."""
 
-    def __init__(self, src, dst, eid, num_nodes):
+    def __init__(self, src, dst, eid, num_nodes, seeds=None, dst_local=None):
         self.src, self.dst, self.eid, self.num_nodes = src, dst, eid, num_nodes
+        # set by sample_neighbors: the seeds and, per edge, the index of its seed -- lets to_block
+        # skip the destination lookup when it is asked for a block over the same seeds
+        self.seeds, self.dst_local = seeds, dst_local
 
     def number_of_edges(self):
         return int(self.src.numel())
@@ -59,9 +62,8 @@ def sample_neighbors(g, seeds, fanout, replace=False, rng_seed=None):
         raise DGLError("seeds must be a 1-D tensor of node ids")
     if fanout == 0:
         raise DGLError("fanout must be positive (or -1 for all in-edges)")
-    if seeds.numel() and (int(seeds.min()) < 0 or int(seeds.max()) >= gidx.num_dst):
-        raise DGLError("seed id out of range")
-    deg = gidx.in_degrees()[seeds]
+    bad = ((seeds < 0) | (seeds >= gidx.num_dst)).any()
+    deg = gidx.in_degrees()[seeds.clamp(0, max(gidx.num_dst - 1, 0))]
     if fanout < 0:
         cnt = deg
     elif replace:
@@ -70,7 +72,9 @@ def sample_neighbors(g, seeds, fanout, replace=False, rng_seed=None):
         cnt = deg.clamp(max=fanout)
     offsets = torch.zeros(seeds.numel() + 1, dtype=torch.int64, device=dev)
     torch.cumsum(cnt, 0, out=offsets[1:])
-    total = int(offsets[-1].item())
+    total, bad = torch.stack([offsets[-1], bad.to(torch.int64)]).tolist()   # the one host sync
+    if bad:
+        raise DGLError("seed id out of range")
     out = torch.empty((3, max(total, 1)), dtype=torch.int64, device=dev)
     if rng_seed is None:
         if _counter[0] == 0:
@@ -85,7 +89,9 @@ def sample_neighbors(g, seeds, fanout, replace=False, rng_seed=None):
             ctypes.c_void_p(out[2].data_ptr()),
             ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
     out = out[:, :total]
-    return Frontier(out[0], out[1], out[2], gidx.num_dst)
+    dst_local = torch.repeat_interleave(torch.arange(seeds.numel(), device=dev), cnt,
+                                        output_size=total)
+    return Frontier(out[0], out[1], out[2], gidx.num_dst, seeds, dst_local)
 
 
 def in_subgraph(g, nodes):
@@ -93,16 +99,17 @@ def in_subgraph(g, nodes):
     return sample_neighbors(g, nodes, -1)
 
 
-def compact_block(src, dst, dst_nodes):
+def compact_block(src, dst, dst_nodes, dst_local=None):
     """Relabelling of dgl.to_block on plain tensors (any device): returns (src_nid, src_local,
     dst_local) -- block source nodes are `dst_nodes` first, then the other sources by first
-    appearance in `src`; edges keep their order."""
+    appearance in `src`; edges keep their order. `dst_local` (index into dst_nodes per edge), when
+    already known, skips the destination lookup and its checks."""
     dev = src.device
     dst_nodes = torch.as_tensor(dst_nodes, dtype=torch.int64, device=dev)
     n_dst = int(dst_nodes.numel())
     allv = torch.cat([dst_nodes, src])
     uniq, inv = torch.unique(allv, return_inverse=True)
-    if n_dst and int(torch.unique(dst_nodes).numel()) != n_dst:
+    if dst_local is None and n_dst and int(torch.unique(dst_nodes).numel()) != n_dst:
         raise DGLError("to_block: destination nodes must be unique")
     first = torch.full((uniq.numel(),), allv.numel(), dtype=torch.int64, device=dev)
     first.scatter_reduce_(0, inv, torch.arange(allv.numel(), device=dev), "amin")
@@ -111,6 +118,8 @@ def compact_block(src, dst, dst_nodes):
     rank[order] = torch.arange(order.numel(), device=dev)
     src_nid = uniq[order]
     src_local = rank[inv[n_dst:]]
+    if dst_local is not None:
+        return src_nid, src_local, dst_local
     pos = torch.searchsorted(uniq, dst).clamp(max=max(int(uniq.numel()) - 1, 0))
     if dst.numel() and not torch.equal(uniq[pos], dst):
         raise DGLError("to_block: an edge ends in a node that is not a destination node")
@@ -127,7 +136,12 @@ def to_block(frontier, dst_nodes, device=None):
     edata[EID]."""
     dev = frontier.src.device if device is None else torch.device(device)
     dst_nodes = torch.as_tensor(dst_nodes, dtype=torch.int64, device=dev)
-    src_nid, src_local, dst_local = compact_block(frontier.src, frontier.dst, dst_nodes)
+    known = None
+    if frontier.dst_local is not None and frontier.seeds is not None and (
+            frontier.seeds is dst_nodes or (frontier.seeds.shape == dst_nodes.shape
+                                            and frontier.seeds.data_ptr() == dst_nodes.data_ptr())):
+        known = frontier.dst_local      # same seeds: the sampler already knows every edge's slot
+    src_nid, src_local, dst_local = compact_block(frontier.src, frontier.dst, dst_nodes, known)
     block = Graph(src_local, dst_local, num_src=int(src_nid.numel()),
                   num_dst=int(dst_nodes.numel()), device=dev)
     block.srcdata[NID] = src_nid
