@@ -106,9 +106,14 @@ SYMBOLS = {
                                          _c.POINTER(_c.c_int64)]),
     "DGLB200GatAttnProj": (_c.c_int, [TensorP] * 5 + [_c.c_void_p]),
     "DGLB200GatAttnProjBackward": (_c.c_int, [TensorP] * 8 + [_c.c_void_p]),
+    "DGLB200SampleCounts": (_c.c_int, [GraphHandle, _c.c_void_p, _c.c_int64, _c.c_int, _c.c_int,
+                                       _c.c_void_p, _c.c_void_p]),
     "DGLB200SampleNeighbors": (_c.c_int, [GraphHandle, _c.c_void_p, _c.c_int64, _c.c_int, _c.c_int,
                                           _c.c_uint64, _c.c_void_p, _c.c_void_p, _c.c_void_p,
-                                          _c.c_void_p, _c.c_void_p]),
+                                          _c.c_void_p, _c.c_void_p, _c.c_void_p]),
+    "DGLB200CompactBlock": (_c.c_int, [_c.c_void_p, _c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_int64,
+                                       _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p,
+                                       _c.c_void_p]),
     "DGLB200KernelScaledCopySum": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP, TensorP,
                                               TensorP, _c.c_void_p]),
     "DGLB200EdgeSoftmaxForward": (_c.c_int, [GraphHandle, TensorP, TensorP, _c.c_void_p]),

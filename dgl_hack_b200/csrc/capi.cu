@@ -786,7 +786,8 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
 // ---- neighbour sampling (extension) ----
 int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,
                            int fanout, int replace, uint64_t rng_seed, const int64_t* offsets,
-                           int64_t* out_src, int64_t* out_dst, int64_t* out_eid, void* stream) {
+                           int64_t* out_src, int64_t* out_dst, int64_t* out_eid,
+                           int64_t* out_slot, void* stream) {
   API_BEGIN();
   B200_CHECK(graph != nullptr, "NULL graph");
   B200_CHECK(n_seeds >= 0, "SampleNeighbors: negative number of seeds");
@@ -795,7 +796,37 @@ int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64
   B200_CHECK(fanout != 0, "SampleNeighbors: fanout must be positive, or negative for all in-edges");
   B200_CUDA(cudaSetDevice(graph->device));
   sample_neighbors(graph, seeds, n_seeds, fanout, replace != 0, rng_seed, offsets, out_src, out_dst,
-                   out_eid, static_cast<cudaStream_t>(stream));
+                   out_eid, out_slot, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200SampleCounts(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,
+                        int fanout, int replace, int64_t* offsets, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph != nullptr, "NULL graph");
+  B200_CHECK(n_seeds >= 0, "SampleCounts: negative number of seeds");
+  B200_CHECK(offsets && (n_seeds == 0 || seeds), "SampleCounts: NULL argument");
+  B200_CHECK(fanout != 0, "SampleCounts: fanout must be positive, or negative for all in-edges");
+  B200_CHECK(fanout < 0 || (double)fanout * (double)n_seeds < 2147483647.0,
+             "SampleCounts: more than 2^31 sampled edges");
+  B200_CUDA(cudaSetDevice(graph->device));
+  sample_counts(graph, seeds, n_seeds, fanout, replace != 0, offsets,
+                static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200CompactBlock(const int64_t* dst_nodes, int64_t n_dst, const int64_t* src,
+                        const int64_t* dst, int64_t n_edges, int64_t* src_nid, int64_t* src_local,
+                        int64_t* dst_local, int64_t* counts, void* stream) {
+  API_BEGIN();
+  B200_CHECK(n_dst >= 0 && n_edges >= 0, "CompactBlock: negative size");
+  B200_CHECK(counts != nullptr, "CompactBlock: NULL counts");
+  B200_CHECK(n_dst == 0 || dst_nodes, "CompactBlock: NULL dst_nodes");
+  B200_CHECK(n_edges == 0 || (src && src_local), "CompactBlock: NULL src / src_local");
+  B200_CHECK(n_dst + n_edges == 0 || src_nid, "CompactBlock: NULL src_nid");
+  B200_CHECK(dst == nullptr || n_edges == 0 || dst_local, "CompactBlock: NULL dst_local");
+  compact_block(dst_nodes, n_dst, src, dst, n_edges, src_nid, src_local, dst_local, counts,
+                static_cast<cudaStream_t>(stream));
   API_END();
 }
 

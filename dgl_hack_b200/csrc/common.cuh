@@ -282,7 +282,13 @@ void attn_proj_backward(const float* feat, const float* al, const float* ar, con
 // sample.cu
 void sample_neighbors(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, int fanout,
                       bool replace, uint64_t rng_seed, const int64_t* offsets, int64_t* out_src,
-                      int64_t* out_dst, int64_t* out_eid, cudaStream_t s);
+                      int64_t* out_dst, int64_t* out_eid, int64_t* out_slot, cudaStream_t s);
+void sample_counts(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, int fanout, bool replace,
+                   int64_t* offsets, cudaStream_t s);
+// block.cu
+void compact_block(const int64_t* dst_nodes, int64_t n_dst, const int64_t* src, const int64_t* dst,
+                   int64_t n_edges, int64_t* src_nid, int64_t* src_local, int64_t* dst_local,
+                   int64_t* counts, cudaStream_t s);
 // softmax.cu
 void edge_softmax_forward(DGLB200Graph* g, const float* z, float* out, int64_t H, cudaStream_t s);
 void edge_softmax_backward(DGLB200Graph* g, const float* out, const float* gout, float* gz,

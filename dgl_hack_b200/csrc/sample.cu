@@ -33,7 +33,7 @@ __device__ __forceinline__ uint32_t draw(uint64_t key, uint64_t i, uint64_t k, u
 struct SampleArgs {
   const int32_t *indptr, *indices, *eids;
   const int64_t *seeds, *offsets;
-  int64_t *out_src, *out_dst, *out_eid;
+  int64_t *out_src, *out_dst, *out_eid, *out_slot;  // out_slot (optional): index of the seed
   int64_t n_seeds;
   int fanout, replace;
   uint64_t key;
@@ -56,8 +56,41 @@ __global__ void __launch_bounds__(256) sample_simple_kernel(SampleArgs a) {
       a.out_src[o + k] = __ldg(a.indices + p);
       a.out_dst[o + k] = v;
       a.out_eid[o + k] = __ldg(a.eids + p);
+      if (a.out_slot) a.out_slot[o + k] = i;
     }
   }
+}
+
+// per-seed output counts (int32, scanned in place afterwards) + range check of the seeds
+__global__ void __launch_bounds__(256) sample_count_kernel(const int32_t* __restrict__ indptr,
+                                                           const int64_t* __restrict__ seeds,
+                                                           int64_t n_seeds, int64_t n_rows,
+                                                           int fanout, int replace,
+                                                           int32_t* __restrict__ cnt,
+                                                           int32_t* __restrict__ bad) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= n_seeds; i += stride) {
+    int c = 0;
+    if (i < n_seeds) {
+      const int64_t v = seeds[i];
+      if (v < 0 || v >= n_rows) {
+        atomicOr(bad, 1);
+      } else {
+        const int deg = __ldg(indptr + v + 1) - __ldg(indptr + v);
+        c = fanout < 0 ? deg : (replace ? (deg > 0 ? fanout : 0) : min(deg, fanout));
+      }
+    }
+    cnt[i] = c;
+  }
+}
+
+__global__ void __launch_bounds__(256) sample_offsets_kernel(const int32_t* __restrict__ scanned,
+                                                             const int32_t* __restrict__ bad,
+                                                             int64_t n_seeds,
+                                                             int64_t* __restrict__ offsets) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= n_seeds + 1; i += stride)
+    offsets[i] = i <= n_seeds ? (int64_t)scanned[i] : (int64_t)*bad;
 }
 
 // without replacement, in-degree above the fanout: one thread per seed
@@ -101,12 +134,28 @@ __global__ void __launch_bounds__(128) sample_distinct_kernel(SampleArgs a) {
 
 }  // namespace
 
+// offsets[0 .. n_seeds] = exclusive prefix sum of the per-seed output counts (so offsets[n_seeds]
+// is the number of sampled edges), offsets[n_seeds + 1] = 1 if a seed is out of range.
+void sample_counts(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, int fanout, bool replace,
+                   int64_t* offsets, cudaStream_t s) {
+  Scratch cnt((size_t)(n_seeds + 1) * 4, s), bad(4, s);
+  B200_CUDA(cudaMemsetAsync(bad.ptr, 0, 4, s));
+  const int blocks = (int)std::min<int64_t>((n_seeds + 2 + 255) / 256, 148 * 8);
+  sample_count_kernel<<<blocks, 256, 0, s>>>(g->in.indptr, seeds, n_seeds, g->num_dst, fanout,
+                                             replace ? 1 : 0, cnt.as<int32_t>(), bad.as<int32_t>());
+  exclusive_scan_i32(cnt.as<int32_t>(), n_seeds + 1, s);
+  sample_offsets_kernel<<<blocks, 256, 0, s>>>(cnt.as<int32_t>(), bad.as<int32_t>(), n_seeds,
+                                               offsets);
+  note_kernel("sample_neighbors", 2);
+  B200_CUDA(cudaGetLastError());
+}
+
 void sample_neighbors(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, int fanout,
                       bool replace, uint64_t rng_seed, const int64_t* offsets, int64_t* out_src,
-                      int64_t* out_dst, int64_t* out_eid, cudaStream_t s) {
+                      int64_t* out_dst, int64_t* out_eid, int64_t* out_slot, cudaStream_t s) {
   if (n_seeds == 0) return;
   SampleArgs a{g->in.indptr, g->in.indices, g->in.eids, seeds, offsets, out_src, out_dst, out_eid,
-               n_seeds, fanout, replace ? 1 : 0, mix64(rng_seed)};
+               out_slot, n_seeds, fanout, replace ? 1 : 0, mix64(rng_seed)};
   const int blocks = (int)std::min<int64_t>((n_seeds + 7) / 8, 148 * 16);
   if (replace || fanout < 0) {
     sample_simple_kernel<<<blocks, 256, 0, s>>>(a);

@@ -42,6 +42,9 @@ class GraphIndex(object):
         dst = torch.as_tensor(dst, dtype=torch.int64).contiguous()
         if src.shape != dst.shape or src.dim() != 1:
             raise _lib.DGLError("src and dst must be 1-D arrays of equal length")
+        # device tensors are read in stream order (torch's allocator keeps a freed block out of
+        # reach of later work on other streams only); host buffers must outlive the copy
+        on_device = src.is_cuda and dst.is_cuda
         handle = _lib.GraphHandle()
         dev_index = device.index or 0
         with torch.cuda.device(dev_index):
@@ -49,7 +52,8 @@ class GraphIndex(object):
                 int(num_src), int(num_dst), int(src.shape[0]), ctypes.c_void_p(src.data_ptr()),
                 ctypes.c_void_p(dst.data_ptr()), dev_index, _stream(device),
                 ctypes.byref(handle)))
-            torch.cuda.current_stream(device).synchronize()  # src/dst may be freed by the caller
+            if not on_device:
+                torch.cuda.current_stream(device).synchronize()  # src/dst may be freed by the caller
         return cls(handle, device)
 
     @classmethod

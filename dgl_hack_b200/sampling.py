@@ -2,7 +2,7 @@
 `to_block` with the reference's meaning (python/dgl/sampling/neighbor.py, python/dgl/transform.py
 in_subgraph / to_block; used by examples/pytorch/graphsage/train_sampling_multi_gpu.py:22-38),
 so the sampled trainers run entirely on the GPU: sampling is one kernel over the in-CSR
-(csrc/sample.cu), compaction is a few torch ops, and the block is a bipartite
+(csrc/sample.cu), compaction is one hash-table pass (csrc/block.cu), and the block is a bipartite
 `dgl_hack_b200.graph.Graph` consumed by the same kernels as the full graph.
 
     frontier = sample_neighbors(g, seeds, fanout, replace=True)
@@ -62,20 +62,17 @@ def sample_neighbors(g, seeds, fanout, replace=False, rng_seed=None):
         raise DGLError("seeds must be a 1-D tensor of node ids")
     if fanout == 0:
         raise DGLError("fanout must be positive (or -1 for all in-edges)")
-    bad = ((seeds < 0) | (seeds >= gidx.num_dst)).any()
-    deg = gidx.in_degrees()[seeds.clamp(0, max(gidx.num_dst - 1, 0))]
-    if fanout < 0:
-        cnt = deg
-    elif replace:
-        cnt = torch.where(deg > 0, torch.full_like(deg, fanout), torch.zeros_like(deg))
-    else:
-        cnt = deg.clamp(max=fanout)
-    offsets = torch.zeros(seeds.numel() + 1, dtype=torch.int64, device=dev)
-    torch.cumsum(cnt, 0, out=offsets[1:])
-    total, bad = torch.stack([offsets[-1], bad.to(torch.int64)]).tolist()   # the one host sync
+    n = int(seeds.numel())
+    stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    offsets = torch.empty(n + 2, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        check_call(LIB.DGLB200SampleCounts(
+            gidx.handle, ctypes.c_void_p(seeds.data_ptr()), n, int(fanout), int(bool(replace)),
+            ctypes.c_void_p(offsets.data_ptr()), stream))
+    total, bad = offsets[n:].tolist()                                       # the one host sync
     if bad:
         raise DGLError("seed id out of range")
-    out = torch.empty((3, max(total, 1)), dtype=torch.int64, device=dev)
+    out = torch.empty((4, max(total, 1)), dtype=torch.int64, device=dev)
     if rng_seed is None:
         if _counter[0] == 0:
             _counter[0] = int(torch.randint(1, 2 ** 62, (1,)).item())
@@ -83,15 +80,12 @@ def sample_neighbors(g, seeds, fanout, replace=False, rng_seed=None):
         rng_seed = _counter[0]
     with torch.cuda.device(dev):
         check_call(LIB.DGLB200SampleNeighbors(
-            gidx.handle, ctypes.c_void_p(seeds.data_ptr()), int(seeds.numel()), int(fanout),
+            gidx.handle, ctypes.c_void_p(seeds.data_ptr()), n, int(fanout),
             int(bool(replace)), int(rng_seed) & (2 ** 64 - 1), ctypes.c_void_p(offsets.data_ptr()),
             ctypes.c_void_p(out[0].data_ptr()), ctypes.c_void_p(out[1].data_ptr()),
-            ctypes.c_void_p(out[2].data_ptr()),
-            ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
+            ctypes.c_void_p(out[2].data_ptr()), ctypes.c_void_p(out[3].data_ptr()), stream))
     out = out[:, :total]
-    dst_local = torch.repeat_interleave(torch.arange(seeds.numel(), device=dev), cnt,
-                                        output_size=total)
-    return Frontier(out[0], out[1], out[2], gidx.num_dst, seeds, dst_local)
+    return Frontier(out[0], out[1], out[2], gidx.num_dst, seeds, out[3])
 
 
 def in_subgraph(g, nodes):
@@ -107,6 +101,9 @@ def compact_block(src, dst, dst_nodes, dst_local=None):
     dev = src.device
     dst_nodes = torch.as_tensor(dst_nodes, dtype=torch.int64, device=dev)
     n_dst = int(dst_nodes.numel())
+    if dev.type == "cuda":
+        return _compact_block_device(src, dst, dst_nodes, dst_local)
+    # host tensors (partition tooling, CPU tests): the same relabelling with torch ops
     allv = torch.cat([dst_nodes, src])
     uniq, inv = torch.unique(allv, return_inverse=True)
     if dst_local is None and n_dst and int(torch.unique(dst_nodes).numel()) != n_dst:
@@ -127,6 +124,40 @@ def compact_block(src, dst, dst_nodes, dst_local=None):
     if dst_local.numel() and int(dst_local.max()) >= n_dst:
         raise DGLError("to_block: an edge ends in a node that is not a destination node")
     return src_nid, src_local, dst_local
+
+
+def _compact_block_device(src, dst, dst_nodes, dst_local):
+    """compact_block on device tensors: one hash-table pass (csrc/block.cu), one host sync for the
+    number of source nodes and the status bits."""
+    dev = src.device
+    src = src.to(torch.int64).contiguous()
+    dst_nodes = dst_nodes.contiguous()
+    n_dst, n_e = int(dst_nodes.numel()), int(src.numel())
+    look_up = dst_local is None
+    if look_up:
+        dst = torch.as_tensor(dst, dtype=torch.int64, device=dev).contiguous()
+        if dst.numel() != n_e:
+            raise DGLError("to_block: src and dst differ in length")
+    buf = torch.empty(max(n_dst + 3 * n_e, 1) + 2, dtype=torch.int64, device=dev)
+    counts = buf[:2]
+    src_nid = buf[2:2 + n_dst + n_e]
+    src_local = buf[2 + n_dst + n_e:2 + n_dst + 2 * n_e]
+    out_dst = buf[2 + n_dst + 2 * n_e:2 + n_dst + 3 * n_e]
+    ptr = lambda t: ctypes.c_void_p(t.data_ptr() if t.numel() else 0)  # noqa: E731
+    with torch.cuda.device(dev):
+        check_call(LIB.DGLB200CompactBlock(
+            ptr(dst_nodes), n_dst, ptr(src), ptr(dst) if look_up else ctypes.c_void_p(0), n_e,
+            ptr(src_nid), ptr(src_local), ptr(out_dst) if look_up else ctypes.c_void_p(0),
+            ctypes.c_void_p(counts.data_ptr()),
+            ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
+    n_src, status = counts.tolist()                     # the one host sync
+    if status & 4:
+        raise DGLError("to_block: negative node id")
+    if status & 1:
+        raise DGLError("to_block: destination nodes must be unique")
+    if status & 2:
+        raise DGLError("to_block: an edge ends in a node that is not a destination node")
+    return src_nid[:n_src], src_local, (out_dst if look_up else dst_local)
 
 
 def to_block(frontier, dst_nodes, device=None):

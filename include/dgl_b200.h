@@ -301,10 +301,31 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
  * per-seed output counts the caller derives from the in-degrees: deg for fanout < 0 (all
  * in-edges, in-CSR order), (deg > 0 ? fanout : 0) with replacement, min(deg, fanout) without.
  * Outputs (device int64, offsets[n_seeds] entries): source node, destination (= the seed) and
- * edge id of every sampled edge, grouped by seed. Reproducible for a given rng_seed. */
+ * edge id of every sampled edge, grouped by seed; out_slot (may be NULL) receives the index of
+ * the seed in seeds[] -- the destination id inside a block over the same seeds. Reproducible for
+ * a given rng_seed.
+ * DGLB200SampleCounts computes those offsets on the device: offsets is a device int64
+ * [n_seeds + 2]; [0 .. n_seeds] = the exclusive prefix sum (so offsets[n_seeds] = number of
+ * sampled edges, which the caller reads back to size the outputs), [n_seeds + 1] = 1 if a seed
+ * is outside [0, num_dst). */
+int DGLB200SampleCounts(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,
+                        int fanout, int replace, int64_t* offsets, void* stream);
 int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,
                            int fanout, int replace, uint64_t rng_seed, const int64_t* offsets,
-                           int64_t* out_src, int64_t* out_dst, int64_t* out_eid, void* stream);
+                           int64_t* out_src, int64_t* out_dst, int64_t* out_eid,
+                           int64_t* out_slot, void* stream);
+
+/* Id compaction of dgl.to_block (python/dgl/transform.py to_block, used by
+ * examples/pytorch/graphsage/train_sampling_multi_gpu.py:31-36) on DEVICE int64 arrays: block
+ * source nodes are dst_nodes[n_dst] first, then every other value of src[n_edges] in order of
+ * first appearance. Writes src_nid (capacity n_dst + n_edges; counts[0] entries are valid),
+ * src_local[n_edges], and -- when dst is not NULL -- dst_local[n_edges], the index of dst[e] in
+ * dst_nodes (dst == NULL: dst_local is not touched). counts is a device int64[2]: [0] number of
+ * block source nodes, [1] status bits the caller must check after the stream has run: 1 = a
+ * destination node appears twice, 2 = an edge ends outside dst_nodes, 4 = negative id. */
+int DGLB200CompactBlock(const int64_t* dst_nodes, int64_t n_dst, const int64_t* src,
+                        const int64_t* dst, int64_t n_edges, int64_t* src_nid, int64_t* src_local,
+                        int64_t* dst_local, int64_t* counts, void* stream);
 
 /* Aggregation with GraphConv's degree scaling inside the kernel (python/dgl/nn/pytorch/conv/
  * graphconv.py:128-176 does `feat * norm`, update_all(copy_src, sum), `rst * norm` as three

@@ -143,3 +143,39 @@ def test_full_neighbourhood_blocks_equal_full_graph_layer():
     gw_full = torch.autograd.grad(full[seeds].sum(), l1.fc_neigh.weight, retain_graph=True)[0]
     gw_blk = torch.autograd.grad(h.sum(), l1.fc_neigh.weight)[0]
     torch.testing.assert_close(gw_blk, gw_full, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_dst,n_e,span,seed", [(40, 300, 500, 0), (1, 1, 3, 1), (0, 0, 5, 2),
+                                                 (5, 0, 9, 3), (3000, 200000, 50000, 4),
+                                                 (1000, 5000, 2 ** 40, 5)])
+def test_device_compact_block_equals_host_relabelling(n_dst, n_e, span, seed):
+    """csrc/block.cu (hash table) against the torch relabelling on host tensors, bit for bit, with
+    the destination lookup and with the sampler's known slots."""
+    from dgl_hack_b200.sampling import compact_block
+    rng = np.random.default_rng(seed)
+    dst_nodes = torch.from_numpy(rng.choice(min(span, 10 ** 7), n_dst, replace=False).astype(np.int64)
+                                 * max(span // 10 ** 7, 1))
+    src = torch.from_numpy(rng.integers(0, span, n_e))
+    slot = torch.from_numpy(rng.integers(0, max(n_dst, 1), n_e))
+    dst = dst_nodes[slot] if n_dst else torch.zeros(0, dtype=torch.int64)
+    want = compact_block(src, dst, dst_nodes)
+    got = compact_block(src.to(DEV), dst.to(DEV), dst_nodes.to(DEV))
+    for w, g in zip(want, got):
+        assert torch.equal(w, g.cpu())
+    got = compact_block(src.to(DEV), None, dst_nodes.to(DEV), slot.to(DEV))
+    assert torch.equal(want[0], got[0].cpu()) and torch.equal(want[1], got[1].cpu())
+
+
+@pytest.mark.gpu
+def test_device_compact_block_errors():
+    from dgl_hack_b200.sampling import compact_block
+    t = lambda *v: torch.tensor(v, dtype=torch.int64, device=DEV)  # noqa: E731
+    with pytest.raises(Exception, match="not a destination node"):
+        compact_block(t(1, 2), t(5, 9), t(5, 6))
+    with pytest.raises(Exception, match="must be unique"):
+        compact_block(t(1, 2), t(5, 5), t(5, 5))
+    with pytest.raises(Exception, match="not a destination node"):
+        compact_block(t(1, 2), t(5, 1), t(5, 6))       # 1 is a source, not a destination
+    with pytest.raises(Exception, match="negative"):
+        compact_block(t(1, -2), t(5, 5), t(5, 6))
