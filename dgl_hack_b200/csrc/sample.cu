@@ -61,36 +61,44 @@ __global__ void __launch_bounds__(256) sample_simple_kernel(SampleArgs a) {
   }
 }
 
-// per-seed output counts (int32, scanned in place afterwards) + range check of the seeds
+// per-seed output counts (int32, scanned in place afterwards) + range check of the seeds; the
+// 64-bit total guards the int32 scan (repeated seeds with fanout < 0 can exceed 2^31 edges)
 __global__ void __launch_bounds__(256) sample_count_kernel(const int32_t* __restrict__ indptr,
                                                            const int64_t* __restrict__ seeds,
                                                            int64_t n_seeds, int64_t n_rows,
                                                            int fanout, int replace,
                                                            int32_t* __restrict__ cnt,
-                                                           int32_t* __restrict__ bad) {
+                                                           unsigned long long* __restrict__ flags) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  unsigned long long mine = 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= n_seeds; i += stride) {
     int c = 0;
     if (i < n_seeds) {
       const int64_t v = seeds[i];
       if (v < 0 || v >= n_rows) {
-        atomicOr(bad, 1);
+        atomicOr(flags, 1ull);
       } else {
         const int deg = __ldg(indptr + v + 1) - __ldg(indptr + v);
         c = fanout < 0 ? deg : (replace ? (deg > 0 ? fanout : 0) : min(deg, fanout));
       }
     }
     cnt[i] = c;
+    mine += (unsigned long long)c;
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(flags + 1, mine);
 }
 
+// flags[0] = 1 if a seed is out of range, flags[1] = total count in 64 bits
 __global__ void __launch_bounds__(256) sample_offsets_kernel(const int32_t* __restrict__ scanned,
-                                                             const int32_t* __restrict__ bad,
+                                                             const unsigned long long* __restrict__ flags,
                                                              int64_t n_seeds,
                                                              int64_t* __restrict__ offsets) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= n_seeds + 1; i += stride)
-    offsets[i] = i <= n_seeds ? (int64_t)scanned[i] : (int64_t)*bad;
+    offsets[i] = i <= n_seeds ? (int64_t)scanned[i]
+                              : (int64_t)(flags[0] | (flags[1] > 0x7fffffffull ? 2ull : 0ull));
 }
 
 // without replacement, in-degree above the fanout: one thread per seed
@@ -135,17 +143,19 @@ __global__ void __launch_bounds__(128) sample_distinct_kernel(SampleArgs a) {
 }  // namespace
 
 // offsets[0 .. n_seeds] = exclusive prefix sum of the per-seed output counts (so offsets[n_seeds]
-// is the number of sampled edges), offsets[n_seeds + 1] = 1 if a seed is out of range.
+// is the number of sampled edges), offsets[n_seeds + 1] = status bits: 1 a seed is out of range,
+// 2 more than 2^31 - 1 sampled edges.
 void sample_counts(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, int fanout, bool replace,
                    int64_t* offsets, cudaStream_t s) {
-  Scratch cnt((size_t)(n_seeds + 1) * 4, s), bad(4, s);
-  B200_CUDA(cudaMemsetAsync(bad.ptr, 0, 4, s));
+  Scratch cnt((size_t)(n_seeds + 1) * 4, s), flags(16, s);
+  B200_CUDA(cudaMemsetAsync(flags.ptr, 0, 16, s));
   const int blocks = (int)std::min<int64_t>((n_seeds + 2 + 255) / 256, 148 * 8);
   sample_count_kernel<<<blocks, 256, 0, s>>>(g->in.indptr, seeds, n_seeds, g->num_dst, fanout,
-                                             replace ? 1 : 0, cnt.as<int32_t>(), bad.as<int32_t>());
+                                             replace ? 1 : 0, cnt.as<int32_t>(),
+                                             flags.as<unsigned long long>());
   exclusive_scan_i32(cnt.as<int32_t>(), n_seeds + 1, s);
-  sample_offsets_kernel<<<blocks, 256, 0, s>>>(cnt.as<int32_t>(), bad.as<int32_t>(), n_seeds,
-                                               offsets);
+  sample_offsets_kernel<<<blocks, 256, 0, s>>>(cnt.as<int32_t>(), flags.as<unsigned long long>(),
+                                               n_seeds, offsets);
   note_kernel("sample_neighbors", 2);
   B200_CUDA(cudaGetLastError());
 }

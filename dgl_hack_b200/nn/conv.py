@@ -135,10 +135,16 @@ class GraphConv(nn.Module):
 
 class SAGEConv(nn.Module):
     """sageconv.py:12-161; aggregator_type in mean / gcn / pool. 'lstm' reduces through a UDF
-    over degree buckets (sageconv.py:85-96), which is outside the builtin kernel path."""
+    over degree buckets (sageconv.py:85-96), which is outside the builtin kernel path.
+
+    `project_first` (extension, off by default = the reference's order of operations): for the
+    linear aggregators (mean, gcn) apply fc_neigh's weight BEFORE the aggregation, the way
+    GraphConv does when in_feats > out_feats (graphconv.py:144-152). mean(X) W == mean(X W)
+    up to fp32 rounding, and the SpMM then gathers out_feats instead of in_feats floats per edge
+    (602 -> 16 on the Reddit-shaped config). "auto" enables it when in_feats > out_feats."""
 
     def __init__(self, in_feats, out_feats, aggregator_type, feat_drop=0., bias=True, norm=None,
-                 activation=None):
+                 activation=None, project_first=False):
         super(SAGEConv, self).__init__()
         if isinstance(in_feats, tuple):
             self._in_src_feats, self._in_dst_feats = in_feats
@@ -159,6 +165,9 @@ class SAGEConv(nn.Module):
         if aggregator_type != "gcn":
             self.fc_self = nn.Linear(self._in_dst_feats, out_feats, bias=bias)
         self.fc_neigh = nn.Linear(self._in_src_feats, out_feats, bias=bias)
+        if project_first == "auto":
+            project_first = self._in_src_feats > out_feats
+        self._project_first = bool(project_first) and aggregator_type in ("mean", "gcn")
         self.reset_parameters()
 
     def reset_parameters(self):
@@ -176,6 +185,8 @@ class SAGEConv(nn.Module):
         else:
             feat_src = feat_dst = self.feat_drop(feat)
         h_self = feat_dst
+        if self._project_first:
+            return self._forward_project_first(graph, feat, feat_src, feat_dst)
         if self._aggre_type == "mean":
             graph.srcdata["h"] = feat_src
             graph.update_all(fn.copy_src("h", "m"), fn.mean("m", "neigh"))
@@ -195,6 +206,28 @@ class SAGEConv(nn.Module):
             rst = self.fc_neigh(h_neigh)
         else:
             rst = self.fc_self(h_self) + self.fc_neigh(h_neigh)
+        if self.activation is not None:
+            rst = self.activation(rst)
+        if self.norm is not None:
+            rst = self.norm(rst)
+        return rst
+
+    def _forward_project_first(self, graph, feat, feat_src, feat_dst):
+        w, b = self.fc_neigh.weight, self.fc_neigh.bias
+        graph.srcdata["h"] = tF.linear(feat_src, w)
+        if self._aggre_type == "mean":
+            graph.update_all(fn.copy_src("h", "m"), fn.mean("m", "neigh"))
+            rst = self.fc_self(feat_dst) + graph.dstdata["neigh"]
+        else:  # gcn
+            if isinstance(feat, tuple) and feat[0].shape[1:] != feat[1].shape[1:]:
+                raise DGLError("gcn aggregator needs source and destination features of one shape")
+            graph.update_all(fn.copy_src("h", "m"), fn.sum("m", "neigh"))
+            degs = graph.in_degrees().to(feat_dst)
+            h_dst = graph.srcdata["h"] if feat_dst is feat_src else tF.linear(feat_dst, w)
+            rst = (graph.dstdata["neigh"] + h_dst[:graph.number_of_dst_nodes()]) \
+                / (degs.unsqueeze(-1) + 1)
+        if b is not None:
+            rst = rst + b
         if self.activation is not None:
             rst = self.activation(rst)
         if self.norm is not None:

@@ -70,8 +70,10 @@ def sample_neighbors(g, seeds, fanout, replace=False, rng_seed=None):
             gidx.handle, ctypes.c_void_p(seeds.data_ptr()), n, int(fanout), int(bool(replace)),
             ctypes.c_void_p(offsets.data_ptr()), stream))
     total, bad = offsets[n:].tolist()                                       # the one host sync
-    if bad:
+    if bad & 1:
         raise DGLError("seed id out of range")
+    if bad & 2:
+        raise DGLError("sample_neighbors: more than 2^31 - 1 sampled edges in one call")
     out = torch.empty((4, max(total, 1)), dtype=torch.int64, device=dev)
     if rng_seed is None:
         if _counter[0] == 0:

@@ -306,8 +306,8 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
  * a given rng_seed.
  * DGLB200SampleCounts computes those offsets on the device: offsets is a device int64
  * [n_seeds + 2]; [0 .. n_seeds] = the exclusive prefix sum (so offsets[n_seeds] = number of
- * sampled edges, which the caller reads back to size the outputs), [n_seeds + 1] = 1 if a seed
- * is outside [0, num_dst). */
+ * sampled edges, which the caller reads back to size the outputs), [n_seeds + 1] = status bits:
+ * 1 a seed is outside [0, num_dst), 2 more than 2^31 - 1 sampled edges (offsets invalid). */
 int DGLB200SampleCounts(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,
                         int fanout, int replace, int64_t* offsets, void* stream);
 int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,

@@ -179,3 +179,20 @@ def test_device_compact_block_errors():
         compact_block(t(1, 2), t(5, 1), t(5, 6))       # 1 is a source, not a destination
     with pytest.raises(Exception, match="negative"):
         compact_block(t(1, -2), t(5, 5), t(5, 6))
+
+
+@pytest.mark.gpu
+def test_sample_neighbors_rejects_more_than_int32_edges():
+    """Repeated seeds with fanout = -1 can ask for more than 2^31 - 1 edges: reported, not wrapped."""
+    from dgl_hack_b200.graph import Graph
+    from dgl_hack_b200 import sampling as S
+    deg = 70000
+    g = Graph(np.arange(1, deg + 1, dtype=np.int64), np.zeros(deg, np.int64), num_nodes=deg + 1,
+              device=DEV)
+    seeds = torch.zeros(40000, dtype=torch.int64, device=DEV)
+    with pytest.raises(Exception, match="2\\^31"):
+        S.sample_neighbors(g, seeds, -1)
+    fr = S.sample_neighbors(g, seeds[:3], -1)
+    assert fr.number_of_edges() == 3 * deg
+    with pytest.raises(Exception, match="out of range"):
+        S.sample_neighbors(g, torch.tensor([deg + 1], device=DEV), 2)
