@@ -35,6 +35,8 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--batch", type=int, default=1000)
     ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--project-first", action="store_true",
+                    help="SAGEConv(project_first='auto'): weight before the mean aggregation")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "r1_sampling.json"))
     args = ap.parse_args()
     n, e, d, hid, ncls = int(232965 * args.scale), int(114615892 * args.scale), 602, 16, 41
@@ -43,8 +45,9 @@ def main():
     del src, dst
     x = torch.rand(n, d, device=DEV) * 2 - 1
     y = torch.randint(0, ncls, (n,), device=DEV)
-    l1 = nnb.SAGEConv(d, hid, "mean", activation=torch.relu).to(DEV)
-    l2 = nnb.SAGEConv(hid, ncls, "mean").to(DEV)
+    pf = "auto" if args.project_first else False
+    l1 = nnb.SAGEConv(d, hid, "mean", activation=torch.relu, project_first=pf).to(DEV)
+    l2 = nnb.SAGEConv(hid, ncls, "mean", project_first=pf).to(DEV)
     opt = torch.optim.Adam(list(l1.parameters()) + list(l2.parameters()), lr=3e-3)
     fanouts = [10, 25]
     gen = torch.Generator(device=DEV)
@@ -81,7 +84,8 @@ def main():
     b0 = state["blocks"][0]
     line = {"metric": "sampled GraphSAGE step (sample + gather + fwd + bwd + Adam)",
             "config": {"workload": "Reddit-shaped N=%d E=%d D=%d, batch %d, fan-outs %s, replace"
-                       % (n, e, d, args.batch, fanouts)},
+                       % (n, e, d, args.batch, fanouts),
+                       "project_first": bool(args.project_first)},
             "ms_per_step": round(ms_step, 3), "ms_sampling": round(ms_sample, 3),
             "ms_train": round(ms_train, 3),
             "seeds_per_s": round(args.batch / ms_step * 1e3, 1),
