@@ -1,0 +1,172 @@
+"""Opt-in dense projections at fp32 accuracy on tensor cores.
+
+The GEMMs either side of the message-passing kernels (GraphConv's `feat @ weight`,
+graphconv.py:144-152) are plain library GEMMs. torch's bundled cuBLAS 12.8 runs them as fp32 SIMT
+kernels; the CUDA 12.9 toolkit's cuBLASLt has `CUBLAS_COMPUTE_32F_EMULATED_16BFX9`, an fp32 GEMM
+emulated with nine BF16 tensor-core products whose error is BELOW the SIMT kernel's
+(profiles/r1_bf16x9_probe.json). This module loads that library by absolute path (the bundled one
+shares its SONAME, so it must not be found by name), and exposes
+
+    matmul(a, b)            autograd-aware a @ b for 2-D fp32 CUDA tensors
+    gemm(a, b, ta, tb)      op(a) @ op(b), row-major, no autograd
+
+It is off by default: set B200_DENSE=bf16x9 (read by nn/conv.py) to route GraphConv through it.
+Shapes for which the emulated kernels are not offered run cuBLASLt's fp32 compute type.
+"""
+import ctypes as C
+import glob
+import os
+
+import torch
+
+from ._lib import DGLError
+
+_CUDA_R_32F = 0
+_COMPUTE_32F, _COMPUTE_BF16X9 = 68, 78
+_DESC_TRANSA, _DESC_TRANSB, _PREF_WS = 3, 4, 1
+_WORKSPACE = 32 << 20
+
+
+class _Heur(C.Structure):  # cublasLtMatmulHeuristicResult_t (cublasLt.h)
+    _fields_ = [("algo", C.c_uint64 * 8), ("ws", C.c_size_t), ("state", C.c_int),
+                ("waves", C.c_float), ("reserved", C.c_int * 4)]
+
+
+class _Lt(object):
+    _inst = None
+
+    def __init__(self):
+        cands = sorted(glob.glob(os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"),
+                                              "lib64", "libcublasLt.so.12.*")))
+        if not cands:
+            raise DGLError("B200_DENSE=bf16x9 needs the CUDA 12.9 toolkit's libcublasLt "
+                           "(not found under $CUDA_HOME/lib64)")
+        lt = C.CDLL(cands[-1])
+        lt.cublasLtGetVersion.restype = C.c_size_t
+        if lt.cublasLtGetVersion() < 120900:
+            raise DGLError("libcublasLt %d has no emulated fp32 compute type" % lt.cublasLtGetVersion())
+        lt.cublasLtCreate.argtypes = [C.POINTER(C.c_void_p)]
+        lt.cublasLtMatmulDescCreate.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int]
+        lt.cublasLtMatmulDescSetAttribute.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+        lt.cublasLtMatrixLayoutCreate.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_uint64,
+                                                  C.c_uint64, C.c_int64]
+        lt.cublasLtMatmulPreferenceCreate.argtypes = [C.POINTER(C.c_void_p)]
+        lt.cublasLtMatmulPreferenceSetAttribute.argtypes = [C.c_void_p, C.c_int, C.c_void_p,
+                                                            C.c_size_t]
+        lt.cublasLtMatmulAlgoGetHeuristic.argtypes = [C.c_void_p] * 7 + [
+            C.c_int, C.POINTER(_Heur), C.POINTER(C.c_int)]
+        lt.cublasLtMatmul.argtypes = [C.c_void_p] * 13 + [C.c_void_p, C.c_size_t, C.c_void_p]
+        self.lt = lt
+        self.handles, self.ws, self.plans = {}, {}, {}
+        self.alpha, self.beta = C.c_float(1.0), C.c_float(0.0)
+
+    @classmethod
+    def get(cls):
+        if cls._inst is None:
+            cls._inst = cls()
+        return cls._inst
+
+    def _check(self, st, what):
+        if st:
+            raise DGLError("cuBLASLt %s failed with status %d" % (what, st))
+
+    def _layout(self, rows, cols, ld):
+        h = C.c_void_p()
+        self._check(self.lt.cublasLtMatrixLayoutCreate(C.byref(h), _CUDA_R_32F, rows, cols, ld),
+                    "MatrixLayoutCreate")
+        return h
+
+    def plan(self, dev, M, K, N, ta, tb):
+        """Descriptor + layouts + algorithm for row-major c[M,N] = op(a) @ op(b), cached. In
+        cuBLASLt's column-major terms: C^T[N,M] = op(b)^T . op(a)^T, first operand = b's buffer."""
+        key = (dev, M, K, N, ta, tb)
+        if key in self.plans:
+            return self.plans[key]
+        lt = self.lt
+        if dev not in self.handles:
+            h = C.c_void_p()
+            self._check(lt.cublasLtCreate(C.byref(h)), "Create")
+            self.handles[dev] = h
+            self.ws[dev] = torch.empty(_WORKSPACE, dtype=torch.uint8, device="cuda:%d" % dev)
+        # b row-major [K,N] is column-major N x K (ld N); stored transposed [N,K] it is K x N (ld K)
+        la = self._layout(K, N, K) if tb else self._layout(N, K, N)
+        # a row-major [M,K] is column-major K x M (ld K); stored transposed [K,M] it is M x K (ld M)
+        lb = self._layout(M, K, M) if ta else self._layout(K, M, K)
+        lc = self._layout(N, M, N)
+        pref = C.c_void_p()
+        self._check(lt.cublasLtMatmulPreferenceCreate(C.byref(pref)), "PreferenceCreate")
+        wsz = C.c_size_t(_WORKSPACE)
+        lt.cublasLtMatmulPreferenceSetAttribute(pref, _PREF_WS, C.byref(wsz), 8)
+        chosen = None
+        for compute in (_COMPUTE_BF16X9, _COMPUTE_32F):
+            desc = C.c_void_p()
+            if lt.cublasLtMatmulDescCreate(C.byref(desc), compute, _CUDA_R_32F):
+                continue
+            for attr, flag in ((_DESC_TRANSA, tb), (_DESC_TRANSB, ta)):
+                op = C.c_int32(1 if flag else 0)
+                self._check(lt.cublasLtMatmulDescSetAttribute(desc, attr, C.byref(op), 4),
+                            "MatmulDescSetAttribute")
+            res, got = _Heur(), C.c_int(0)
+            st = lt.cublasLtMatmulAlgoGetHeuristic(self.handles[dev], desc, la, lb, lc, lc, pref,
+                                                   1, C.byref(res), C.byref(got))
+            if st == 0 and got.value > 0 and res.state == 0:
+                chosen = (desc, la, lb, lc, res, compute)
+                break
+        if chosen is None:
+            raise DGLError("cuBLASLt offers no fp32 algorithm for [%d,%d] x [%d,%d]" % (M, K, K, N))
+        self.plans[key] = chosen
+        return chosen
+
+    def run(self, a, b, c, M, K, N, ta, tb):
+        dev = a.device.index or 0
+        desc, la, lb, lc, res, _ = self.plan(dev, M, K, N, ta, tb)
+        with torch.cuda.device(dev):
+            st = self.lt.cublasLtMatmul(
+                self.handles[dev], desc, C.byref(self.alpha), b.data_ptr(), la, a.data_ptr(), lb,
+                C.byref(self.beta), c.data_ptr(), lc, c.data_ptr(), lc, C.byref(res.algo),
+                self.ws[dev].data_ptr(), res.ws,
+                C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+        self._check(st, "Matmul")
+
+
+def gemm(a, b, trans_a=False, trans_b=False):
+    """op(a) @ op(b) for 2-D fp32 CUDA tensors (made contiguous), fp32 result, no autograd."""
+    if a.dim() != 2 or b.dim() != 2 or a.dtype != torch.float32 or b.dtype != torch.float32:
+        raise DGLError("dense.gemm takes 2-D float32 tensors")
+    if not (a.is_cuda and b.is_cuda and a.device == b.device):
+        raise DGLError("dense.gemm: operands must live on one CUDA device (there is no CPU path)")
+    a, b = a.contiguous(), b.contiguous()
+    M, K = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
+    Kb, N = (b.shape[1], b.shape[0]) if trans_b else (b.shape[0], b.shape[1])
+    if K != Kb:
+        raise DGLError("dense.gemm: inner dimensions differ (%d vs %d)" % (K, Kb))
+    c = torch.empty((M, N), dtype=torch.float32, device=a.device)
+    if M == 0 or N == 0:
+        return c
+    if K == 0:
+        return c.zero_()
+    _Lt.get().run(a, b, c, M, K, N, bool(trans_a), bool(trans_b))
+    return c
+
+
+class _MatMul(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        ctx.save_for_backward(a, b)
+        return gemm(a, b)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        ga = gemm(g, b, trans_b=True) if ctx.needs_input_grad[0] else None
+        gb = gemm(a, g, trans_a=True) if ctx.needs_input_grad[1] else None
+        return ga, gb
+
+
+def matmul(a, b):
+    """a @ b with gradients, both through the emulated-fp32 tensor-core GEMM."""
+    return _MatMul.apply(a, b)
+
+
+def enabled():
+    return os.environ.get("B200_DENSE", "") == "bf16x9"

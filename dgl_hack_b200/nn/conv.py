@@ -14,6 +14,7 @@ from torch.nn import functional as tF
 from torch.nn import init
 
 from .. import backend as B
+from .. import dense
 from .. import function as fn
 from .._lib import DGLError
 from .softmax import edge_softmax
@@ -28,6 +29,14 @@ class Identity(nn.Module):
 
 def _bcast_rows(vec, like):
     return vec.reshape(vec.shape + (1,) * (like.dim() - 1))
+
+
+def _matmul(x, w):
+    """`th.matmul(x, w)`; with B200_DENSE=bf16x9 a 2-D product runs as the emulated-fp32
+    tensor-core GEMM of `dgl_hack_b200.dense` (opt-in)."""
+    if x.dim() == 2 and w.dim() == 2 and x.is_cuda and x.dtype == th.float32 and dense.enabled():
+        return dense.matmul(x, w)
+    return th.matmul(x, w)
 
 
 class GraphConv(nn.Module):
@@ -94,12 +103,12 @@ class GraphConv(nn.Module):
             w = tF.pad(weight, (0, pad)) if pad else weight
             # the reference scales the rows before the product (graphconv.py:133, 148); scaling
             # inside the aggregation is the same product per element, one rounding later
-            feat = th.matmul(feat, w)
+            feat = _matmul(feat, w)
         rst = B.scaled_copy_sum(graph.gidx, feat, cs, rs)
         if pad:
             rst = rst[..., :self._out_feats]
         if not mult_first and weight is not None:
-            rst = th.matmul(rst, weight)
+            rst = _matmul(rst, weight)
         if self.bias is not None:
             rst = rst + self.bias
         if self._activation is not None:
