@@ -708,6 +708,19 @@ int DGLB200MetisPartition(int64_t nvtxs, const int64_t* xadj, const int64_t* adj
   API_END();
 }
 
+int DGLB200SymmetrizeCOO(int64_t nvtxs, int64_t num_edges, const int64_t* src, const int64_t* dst,
+                         int64_t* xadj, int64_t* adjncy, int64_t* nnz) {
+  API_BEGIN();
+  B200_CHECK(nvtxs >= 0 && nvtxs < (1ll << 31) - 1, "SymmetrizeCOO: number of vertices out of range");
+  B200_CHECK(num_edges >= 0 && xadj && nnz && (num_edges == 0 || (src && dst && adjncy)),
+             "SymmetrizeCOO: NULL argument");
+  for (int64_t e = 0; e < num_edges; ++e)
+    B200_CHECK(src[e] >= 0 && src[e] < nvtxs && dst[e] >= 0 && dst[e] < nvtxs,
+               "SymmetrizeCOO: node id out of range");
+  *nnz = symmetrize_coo(nvtxs, num_edges, src, dst, xadj, adjncy);
+  API_END();
+}
+
 // ---- GAT attention projections (extension) ----
 static void attn_shapes(const DGLB200Tensor* feat, std::initializer_list<const DGLB200Tensor*> attn,
                         std::initializer_list<const DGLB200Tensor*> per_node, int64_t* n, int64_t* H,

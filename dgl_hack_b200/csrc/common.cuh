@@ -271,6 +271,8 @@ void fused_gat_backward(DGLB200Graph* g, const float* ft, const float* el, const
                         float* grad_ft, float* grad_el, float* grad_er, int64_t H, int64_t F,
                         float slope, cudaStream_t s);
 // kway.cu (host): multilevel k-way partitioner; returns the edge cut
+int64_t symmetrize_coo(int64_t nvtxs, int64_t num_edges, const int64_t* src, const int64_t* dst,
+                       int64_t* xadj, int64_t* adjncy);
 int64_t kway_partition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy,
                        const int64_t* vwgt, int k, uint64_t seed, double ubfactor, int64_t* part);
 // attn.cu

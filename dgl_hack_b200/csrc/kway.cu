@@ -15,7 +15,9 @@
 #include <cstdint>
 #include <cstring>
 #include <numeric>
+#include <functional>
 #include <queue>
+#include <thread>
 #include <vector>
 #include <chrono>
 #include <cstdio>
@@ -83,6 +85,8 @@ void coarsen(const LGraph& g, int32_t max_vw, Rng& rng, LGraph* c, std::vector<i
       match[pending] = u, match[u] = pending, pending = -1;
     }
   }
+  static const bool tdbg = std::getenv("B200_KWAY_DEBUG") != nullptr;
+  auto tm0 = std::chrono::steady_clock::now();
   cmap->assign(n, -1);
   int32_t nc = 0;
   std::vector<int32_t> first, second;
@@ -99,24 +103,68 @@ void coarsen(const LGraph& g, int32_t max_vw, Rng& rng, LGraph* c, std::vector<i
   c->n = nc;
   c->xadj.assign(nc + 1, 0);
   c->vw.assign(nc, 0);
-  c->adj.clear(), c->ew.clear();
-  c->adj.reserve(g.adj.size() / 2), c->ew.reserve(g.adj.size() / 2);
   c->total_vw = g.total_vw;
-  std::vector<int64_t> slot(nc, -1);  // position of a coarse neighbour in the row being built
+  // Contraction: every coarse row is the merge of its one or two fine rows (parallel edges
+  // summed, neighbours in order of first appearance). Rows are independent, so contiguous chunks
+  // of coarse vertices -- cut where the fine adjacency is split evenly -- are merged by separate
+  // threads into private buffers and concatenated; the result is the sequential one, bit for bit.
+  std::vector<int64_t> work(nc + 1, 0);
   for (int32_t cv = 0; cv < nc; ++cv) {
-    const int64_t row_beg = (int64_t)c->adj.size();
-    for (int32_t v : {first[cv], second[cv]}) {
-      if (v < 0) continue;
-      c->vw[cv] += g.vw[v];
-      for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
-        const int32_t cu = (*cmap)[g.adj[j]];
-        if (cu == cv) continue;
-        if (slot[cu] >= row_beg) c->ew[slot[cu]] += g.ew[j];
-        else slot[cu] = (int64_t)c->adj.size(), c->adj.push_back(cu), c->ew.push_back(g.ew[j]);
-      }
-    }
-    c->xadj[cv + 1] = (int64_t)c->adj.size();
+    int64_t w = g.xadj[first[cv] + 1] - g.xadj[first[cv]];
+    if (second[cv] >= 0) w += g.xadj[second[cv] + 1] - g.xadj[second[cv]];
+    work[cv + 1] = work[cv] + w + 1;
   }
+  int T = 1;
+  if (work[nc] > (1 << 20)) T = (int)std::min<unsigned>(16, std::max(1u, std::thread::hardware_concurrency()));
+  std::vector<int32_t> cut(T + 1, nc);
+  cut[0] = 0;
+  for (int t = 1; t < T; ++t)
+    cut[t] = (int32_t)(std::lower_bound(work.begin(), work.end(), work[nc] * t / T) - work.begin());
+  struct Buf { std::vector<int32_t> adj, ew; };
+  std::vector<Buf> bufs(T);
+  std::vector<int64_t> rowlen(nc, 0);
+  auto merge_rows = [&](int t) {
+    Buf& b = bufs[t];
+    const int32_t lo = std::min(cut[t], nc), hi = std::min(cut[t + 1], nc);
+    if (lo >= hi) return;
+    b.adj.reserve((size_t)(work[hi] - work[lo]) / 2 + 16), b.ew.reserve((size_t)(work[hi] - work[lo]) / 2 + 16);
+    std::vector<int64_t> slot(nc, -1);  // position of a coarse neighbour in the row being built
+    for (int32_t cv = lo; cv < hi; ++cv) {
+      const int64_t row_beg = (int64_t)b.adj.size();
+      int32_t w = 0;
+      for (int32_t v : {first[cv], second[cv]}) {
+        if (v < 0) continue;
+        w += g.vw[v];
+        for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
+          const int32_t cu = (*cmap)[g.adj[j]];
+          if (cu == cv) continue;
+          if (slot[cu] >= row_beg) b.ew[slot[cu]] += g.ew[j];
+          else slot[cu] = (int64_t)b.adj.size(), b.adj.push_back(cu), b.ew.push_back(g.ew[j]);
+        }
+      }
+      c->vw[cv] = w;
+      rowlen[cv] = (int64_t)b.adj.size() - row_beg;
+    }
+  };
+  auto run_threads = [&](const std::function<void(int)>& fn) {
+    if (T == 1) { fn(0); return; }
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; ++t) th.emplace_back(fn, t);
+    fn(0);
+    for (auto& x : th) x.join();
+  };
+  run_threads(merge_rows);
+  for (int32_t cv = 0; cv < nc; ++cv) c->xadj[cv + 1] = c->xadj[cv] + rowlen[cv];
+  c->adj.resize((size_t)c->xadj[nc]), c->ew.resize((size_t)c->xadj[nc]);
+  run_threads([&](int t) {
+    const int32_t lo = std::min(cut[t], nc);
+    if (bufs[t].adj.empty()) return;
+    std::copy(bufs[t].adj.begin(), bufs[t].adj.end(), c->adj.begin() + c->xadj[lo]);
+    std::copy(bufs[t].ew.begin(), bufs[t].ew.end(), c->ew.begin() + c->xadj[lo]);
+  });
+  if (tdbg && n > 5000)
+    std::fprintf(stderr, "[kway]   contraction n=%d %.3fs\n", n,
+                 std::chrono::duration<double>(std::chrono::steady_clock::now() - tm0).count());
 }
 
 int64_t edge_cut(const LGraph& g, const std::vector<int32_t>& part) {
@@ -138,10 +186,18 @@ void refine(const LGraph& g, int k, const std::vector<double>& target, double ub
   std::vector<int64_t> conn(k, 0);
   std::vector<int32_t> touched, order(g.n);
   std::iota(order.begin(), order.end(), 0);
+  // After the first sweep only vertices next to a vertex that moved in the previous pass can see
+  // a different neighbourhood, so later passes visit those alone (a sweep moves < 10 % of what
+  // the one before it moved). An overweight part re-opens every vertex: shedding weight is not a
+  // boundary affair.
+  std::vector<char> active(g.n, 1), next_active(g.n, 0);
   for (int pass = 0; pass < passes; ++pass) {
     shuffle(order, rng);
     int64_t moved = 0;
+    bool full = pass == 0;
+    for (int p = 0; p < k; ++p) full |= pw[p] > maxw[p];
     for (int32_t v : order) {
+      if (!full && !active[v]) continue;
       const int own = part[v];
       touched.clear();
       bool boundary = false;
@@ -181,10 +237,14 @@ void refine(const LGraph& g, int k, const std::vector<double>& target, double ub
           part[v] = best;
           pw[own] -= g.vw[v], pw[best] += g.vw[v];
           ++moved;
+          next_active[v] = 1;
+          for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) next_active[g.adj[j]] = 1;
         }
       }
       for (int p : touched) conn[p] = 0;
     }
+    active.swap(next_active);
+    std::fill(next_active.begin(), next_active.end(), 0);
     if (moved * 2000 < (int64_t)g.n + 2000 && pass >= 1) break;  // converged: < 0.05 % moved
   }
 }
@@ -414,6 +474,54 @@ void recursive_bisection(const LGraph& g, int k, int base, Rng& rng, const std::
 
 }  // namespace
 
+// Symmetrised simple graph of a COO edge list (to_bidirected + in-CSR, python/dgl/transform.py:
+// 625-626): self loops dropped, parallel edges merged, every row's neighbours ascending. xadj has
+// nvtxs + 1 entries, adjncy room for 2 * num_edges; returns the number of entries written.
+// Counting sort into rows, then sort + unique per row on a few threads, then compaction.
+int64_t symmetrize_coo(int64_t nvtxs, int64_t num_edges, const int64_t* src, const int64_t* dst,
+                       int64_t* xadj, int64_t* adjncy) {
+  std::vector<int64_t> ptr(nvtxs + 1, 0);
+  for (int64_t e = 0; e < num_edges; ++e) {
+    if (src[e] == dst[e]) continue;
+    ++ptr[src[e] + 1], ++ptr[dst[e] + 1];
+  }
+  for (int64_t v = 0; v < nvtxs; ++v) ptr[v + 1] += ptr[v];
+  std::vector<int64_t> cur(ptr.begin(), ptr.end() - 1);
+  std::vector<int32_t> tmp((size_t)ptr[nvtxs]);
+  for (int64_t e = 0; e < num_edges; ++e) {
+    const int64_t u = src[e], v = dst[e];
+    if (u == v) continue;
+    tmp[cur[u]++] = (int32_t)v;
+    tmp[cur[v]++] = (int32_t)u;
+  }
+  int T = 1;
+  if (ptr[nvtxs] > (1 << 20)) T = (int)std::min<unsigned>(16, std::max(1u, std::thread::hardware_concurrency()));
+  std::vector<int64_t> len(nvtxs, 0);
+  auto rows = [&](int t) {  // rows split where the entries are split evenly
+    const int64_t lo = std::lower_bound(ptr.begin(), ptr.end(), ptr[nvtxs] * t / T) - ptr.begin();
+    const int64_t hi = t + 1 == T ? nvtxs
+                                  : std::lower_bound(ptr.begin(), ptr.end(), ptr[nvtxs] * (t + 1) / T) - ptr.begin();
+    for (int64_t v = std::min(lo, nvtxs); v < std::min(hi, nvtxs); ++v) {
+      int32_t* b = tmp.data() + ptr[v];
+      int32_t* e = tmp.data() + ptr[v + 1];
+      std::sort(b, e);
+      len[v] = std::unique(b, e) - b;
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < T; ++t) th.emplace_back(rows, t);
+  rows(0);
+  for (auto& x : th) x.join();
+  xadj[0] = 0;
+  for (int64_t v = 0; v < nvtxs; ++v) {
+    const int32_t* b = tmp.data() + ptr[v];
+    int64_t* o = adjncy + xadj[v];
+    for (int64_t i = 0; i < len[v]; ++i) o[i] = b[i];
+    xadj[v + 1] = xadj[v] + len[v];
+  }
+  return xadj[nvtxs];
+}
+
 int64_t kway_partition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy,
                        const int64_t* vwgt, int k, uint64_t seed, double ubfactor, int64_t* part) {
   Rng rng(seed);
@@ -455,7 +563,7 @@ int64_t kway_partition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy
   std::vector<int32_t> cur(gc.n, 0), ids(gc.n);
   std::iota(ids.begin(), ids.end(), 0);
   recursive_bisection(gc, k, 0, rng, ids, &cur);
-  lap("initial", gc.n, edge_cut(gc, cur));
+  lap("initial", gc.n, dbg ? edge_cut(gc, cur) : 0);
   std::vector<double> target(k, (double)g0.total_vw / k);
   refine(gc, k, target, ubfactor, 10, rng, &cur);
   for (int lvl = (int)levels.size() - 2; lvl >= 0; --lvl) {
@@ -464,7 +572,7 @@ int64_t kway_partition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy
     for (int32_t v = 0; v < g.n; ++v) fine[v] = cur[cmaps[lvl][v]];
     cur.swap(fine);
     refine(g, k, target, ubfactor, 30, rng, &cur);
-    lap("refine", g.n, edge_cut(g, cur));
+    lap("refine", g.n, dbg ? edge_cut(g, cur) : 0);
     levels[lvl + 1] = LGraph();  // release the coarser level
   }
   for (int64_t v = 0; v < nvtxs; ++v) part[v] = cur[v];

@@ -43,6 +43,18 @@ def symmetric_csr(num_nodes, src, dst):
     src/graph/metis_partition.cc:25-31). Self loops and parallel edges are dropped."""
     src = torch.as_tensor(src, dtype=torch.int64)
     dst = torch.as_tensor(dst, dtype=torch.int64).to(src.device)
+    if not src.is_cuda:  # host arrays: counting sort + per-row sort / unique in the library
+        import ctypes
+        from ._lib import LIB, check_call
+        src, dst = src.contiguous(), dst.contiguous()
+        xadj = torch.empty(num_nodes + 1, dtype=torch.int64)
+        adjncy = torch.empty(max(2 * src.numel(), 1), dtype=torch.int64)
+        nnz = ctypes.c_int64()
+        check_call(LIB.DGLB200SymmetrizeCOO(
+            int(num_nodes), int(src.numel()), ctypes.c_void_p(src.data_ptr()),
+            ctypes.c_void_p(dst.data_ptr()), ctypes.c_void_p(xadj.data_ptr()),
+            ctypes.c_void_p(adjncy.data_ptr()), ctypes.byref(nnz)))
+        return xadj, adjncy[:nnz.value].clone()
     keep = src != dst
     u = torch.cat([src[keep], dst[keep]])
     v = torch.cat([dst[keep], src[keep]])

@@ -357,6 +357,13 @@ int DGLB200MetisPartition(int64_t nvtxs, const int64_t* xadj, const int64_t* adj
                           const int64_t* vwgt, int k, uint64_t seed, int64_t* part,
                           int64_t* objval);
 
+/* The graph the reference hands METIS: to_bidirected(g) as an in-CSR (python/dgl/transform.py:
+ * 625-626) from a COO edge list (host int64): self loops dropped, parallel edges merged,
+ * neighbours ascending. xadj[nvtxs + 1] and adjncy[2 * num_edges] are caller-allocated; *nnz
+ * receives the number of adjncy entries written. */
+int DGLB200SymmetrizeCOO(int64_t nvtxs, int64_t num_edges, const int64_t* src, const int64_t* dst,
+                         int64_t* xadj, int64_t* adjncy, int64_t* nnz);
+
 /* ---- multi-GPU halo exchange over peer memory (no reference PackedFunc; the partition semantics
  *      are partition_graph_with_halo's, python/dgl/transform.py:551-640) ---- */
 
