@@ -177,6 +177,50 @@ int64_t edge_cut(const LGraph& g, const std::vector<int32_t>& part) {
 
 // Greedy k-way boundary refinement. target[p] = desired weight of part p; a move may not push a
 // part above ub * target. Overweight parts shed vertices even at a loss.
+// Vertices a refinement pass has to look at, in ascending order: those (of the active set, if one
+// is given) that sit in an overweight part or have at least as much edge weight into some other
+// part as into their own, judged on the current assignment. Evaluated on threads over contiguous
+// vertex ranges of equal adjacency; the list is the same for any thread count.
+void collect_candidates(const LGraph& g, int k, const std::vector<int32_t>& part,
+                        const std::vector<int64_t>& pw, const std::vector<int64_t>& maxw,
+                        const std::vector<char>* active, std::vector<int32_t>* out) {
+  const int64_t total = g.xadj[g.n];
+  int T = 1;
+  if (total > (1 << 20)) T = (int)std::min<unsigned>(16, std::max(1u, std::thread::hardware_concurrency()));
+  std::vector<std::vector<int32_t>> found(T);
+  auto scan = [&](int t) {
+    const int32_t lo = (int32_t)(std::lower_bound(g.xadj.begin(), g.xadj.end(), total * t / T) - g.xadj.begin());
+    const int32_t hi = t + 1 == T ? g.n
+        : (int32_t)(std::lower_bound(g.xadj.begin(), g.xadj.end(), total * (t + 1) / T) - g.xadj.begin());
+    std::vector<int64_t> conn(k, 0);
+    std::vector<int32_t> touched;
+    for (int32_t v = std::min(lo, g.n); v < std::min(hi, g.n); ++v) {
+      if (active && !(*active)[v]) continue;
+      const int own = part[v];
+      if (pw[own] > maxw[own]) { found[t].push_back(v); continue; }
+      touched.clear();
+      for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
+        const int32_t u = g.adj[j];
+        if (u == v) continue;
+        const int p = part[u];
+        if (conn[p] == 0) touched.push_back(p);
+        conn[p] += g.ew[j];
+      }
+      const int64_t id = conn[own];
+      bool cand = false;
+      for (int p : touched) cand |= (p != own && conn[p] >= id);
+      for (int p : touched) conn[p] = 0;
+      if (cand) found[t].push_back(v);
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < T; ++t) th.emplace_back(scan, t);
+  scan(0);
+  for (auto& x : th) x.join();
+  out->clear();
+  for (int t = 0; t < T; ++t) out->insert(out->end(), found[t].begin(), found[t].end());
+}
+
 void refine(const LGraph& g, int k, const std::vector<double>& target, double ub, int passes,
             Rng& rng, std::vector<int32_t>* part_io) {
   std::vector<int32_t>& part = *part_io;
@@ -184,20 +228,21 @@ void refine(const LGraph& g, int k, const std::vector<double>& target, double ub
   for (int32_t v = 0; v < g.n; ++v) pw[part[v]] += g.vw[v];
   for (int p = 0; p < k; ++p) maxw[p] = (int64_t)(ub * target[p]) + 1;
   std::vector<int64_t> conn(k, 0);
-  std::vector<int32_t> touched, order(g.n);
-  std::iota(order.begin(), order.end(), 0);
+  std::vector<int32_t> touched, cand;
   // After the first sweep only vertices next to a vertex that moved in the previous pass can see
   // a different neighbourhood, so later passes visit those alone (a sweep moves < 10 % of what
   // the one before it moved). An overweight part re-opens every vertex: shedding weight is not a
   // boundary affair.
   std::vector<char> active(g.n, 1), next_active(g.n, 0);
   for (int pass = 0; pass < passes; ++pass) {
-    shuffle(order, rng);
     int64_t moved = 0;
     bool full = pass == 0;
     for (int p = 0; p < k; ++p) full |= pw[p] > maxw[p];
-    for (int32_t v : order) {
-      if (!full && !active[v]) continue;
+    // the sweep proper is sequential (every move changes the part weights); the threads only
+    // discard the interior vertices that cannot move, which are the bulk
+    collect_candidates(g, k, part, pw, maxw, full ? nullptr : &active, &cand);
+    shuffle(cand, rng);
+    for (int32_t v : cand) {
       const int own = part[v];
       touched.clear();
       bool boundary = false;
@@ -403,6 +448,15 @@ void flat_bisect(const LGraph& g, double frac, Rng& rng, std::vector<int32_t>* o
 // ~150 vertices, bisected there, and FM-refined at every level on the way back, so hill climbing
 // happens at every scale (one flat FM on a few thousand blurred vertices does not find the cut).
 void bisect(const LGraph& g, double frac, Rng& rng, std::vector<int32_t>* out) {
+  static const bool tdbg = std::getenv("B200_KWAY_DEBUG") != nullptr;
+  auto tb0 = std::chrono::steady_clock::now();
+  auto tlap = [&](const char* what) {
+    if (!tdbg || g.n < 2000) return;
+    auto t1 = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[kway]   bisect n=%d %s %.3fs\n", g.n, what,
+                 std::chrono::duration<double>(t1 - tb0).count());
+    tb0 = t1;
+  };
   std::vector<LGraph> levels;
   std::vector<std::vector<int32_t>> cmaps;
   const int32_t coarsen_to = 150;
@@ -418,8 +472,10 @@ void bisect(const LGraph& g, double frac, Rng& rng, std::vector<int32_t>* out) {
     levels.push_back(std::move(c));
     cur_g = &levels.back();
   }
+  tlap("coarsen");
   std::vector<int32_t> part;
   flat_bisect(*cur_g, frac, rng, &part);
+  tlap("flat");
   const double target[2] = {frac * g.total_vw, (1.0 - frac) * g.total_vw};
   for (int lvl = (int)levels.size() - 1; lvl >= 0; --lvl) {
     const LGraph& fine = lvl == 0 ? g : levels[lvl - 1];
@@ -428,6 +484,7 @@ void bisect(const LGraph& g, double frac, Rng& rng, std::vector<int32_t>* out) {
     part.swap(p);
     fm_refine(fine, target, 1.03, 6, &part);
   }
+  tlap("fm up");
   *out = part;
 }
 
