@@ -28,6 +28,13 @@
 namespace b200 {
 namespace {
 
+// Threads for the data-parallel host phases (results never depend on the count).
+// B200_KWAY_THREADS overrides the default of min(16, hardware threads).
+int host_threads() {
+  if (const char* e = std::getenv("B200_KWAY_THREADS")) return std::max(1, std::min(64, std::atoi(e)));
+  return (int)std::min<unsigned>(16, std::max(1u, std::thread::hardware_concurrency()));
+}
+
 struct Rng {
   uint64_t s;
   explicit Rng(uint64_t seed) : s(seed * 0x9E3779B97F4A7C15ull + 0x1234567ull) {}
@@ -115,7 +122,7 @@ void coarsen(const LGraph& g, int32_t max_vw, Rng& rng, LGraph* c, std::vector<i
     work[cv + 1] = work[cv] + w + 1;
   }
   int T = 1;
-  if (work[nc] > (1 << 20)) T = (int)std::min<unsigned>(16, std::max(1u, std::thread::hardware_concurrency()));
+  if (work[nc] > (1 << 20)) T = host_threads();
   std::vector<int32_t> cut(T + 1, nc);
   cut[0] = 0;
   for (int t = 1; t < T; ++t)
@@ -186,7 +193,7 @@ void collect_candidates(const LGraph& g, int k, const std::vector<int32_t>& part
                         const std::vector<char>* active, std::vector<int32_t>* out) {
   const int64_t total = g.xadj[g.n];
   int T = 1;
-  if (total > (1 << 20)) T = (int)std::min<unsigned>(16, std::max(1u, std::thread::hardware_concurrency()));
+  if (total > (1 << 20)) T = host_threads();
   std::vector<std::vector<int32_t>> found(T);
   auto scan = [&](int t) {
     const int32_t lo = (int32_t)(std::lower_bound(g.xadj.begin(), g.xadj.end(), total * t / T) - g.xadj.begin());
@@ -552,7 +559,7 @@ int64_t symmetrize_coo(int64_t nvtxs, int64_t num_edges, const int64_t* src, con
     tmp[cur[v]++] = (int32_t)u;
   }
   int T = 1;
-  if (ptr[nvtxs] > (1 << 20)) T = (int)std::min<unsigned>(16, std::max(1u, std::thread::hardware_concurrency()));
+  if (ptr[nvtxs] > (1 << 20)) T = host_threads();
   std::vector<int64_t> len(nvtxs, 0);
   auto rows = [&](int t) {  // rows split where the entries are split evenly
     const int64_t lo = std::lower_bound(ptr.begin(), ptr.end(), ptr[nvtxs] * t / T) - ptr.begin();

@@ -350,7 +350,9 @@ int64_t DGLB200LaunchCount(void);
  * reference hands METIS its in-CSR): part[v] in [0, k) minimising the edge cut with every part's
  * weight <= 1.03 * total / k (METIS' default imbalance). vwgt = NULL means unit vertex weights
  * (what the reference passes); otherwise one non-negative weight per vertex. *objval receives the
- * edge cut. Deterministic for a given seed. METIS itself is a submodule the reference links; this
+ * edge cut. Deterministic for a given seed; the data-parallel host phases run on
+ * min(16, hardware threads) std::threads (B200_KWAY_THREADS overrides) and the result does not
+ * depend on that number. METIS itself is a submodule the reference links; this
  * is an independent implementation of the same published scheme, so assignments differ while the
  * invariants the reference tests (tests/compute/test_transform.py:223-272) hold. */
 int DGLB200MetisPartition(int64_t nvtxs, const int64_t* xadj, const int64_t* adjncy,
