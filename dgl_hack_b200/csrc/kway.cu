@@ -321,13 +321,38 @@ void fm_refine(const LGraph& g, const double target[2], double ub, int max_passe
   const int limit = std::max(50, std::min(n / 5, 2000));
   for (int pass = 0; pass < max_passes; ++pass) {
     std::priority_queue<Item> q[2];
-    for (int32_t v = 0; v < n; ++v) {
-      int64_t ext = 0, in = 0;
-      for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
-        if (g.adj[j] == v) continue;
-        (part[g.adj[j]] == part[v] ? in : ext) += g.ew[j];
+    // gains of all vertices: a pure function of the assignment, evaluated on threads over
+    // vertex ranges of equal adjacency (this scan, not the moves, is what a pass costs on the
+    // dense coarse graphs); the queues are then filled in vertex order as before
+    const int64_t total_adj = g.xadj[n];
+    const int T = total_adj > (1 << 20) ? host_threads() : 1;
+    std::vector<int64_t> ext_sum(T, 0);
+    auto scan = [&](int t) {
+      const int32_t lo = (int32_t)(std::lower_bound(g.xadj.begin(), g.xadj.end(), total_adj * t / T) - g.xadj.begin());
+      const int32_t hi = t + 1 == T ? n
+          : (int32_t)(std::lower_bound(g.xadj.begin(), g.xadj.end(), total_adj * (t + 1) / T) - g.xadj.begin());
+      int64_t cut2 = 0;
+      for (int32_t v = std::min(lo, n); v < std::min(hi, n); ++v) {
+        int64_t ext = 0, in = 0;
+        for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
+          if (g.adj[j] == v) continue;
+          (part[g.adj[j]] == part[v] ? in : ext) += g.ew[j];
+        }
+        gain[v] = ext - in;
+        cut2 += ext;
       }
-      gain[v] = ext - in;
+      ext_sum[t] = cut2;
+    };
+    {
+      std::vector<std::thread> th;
+      for (int t = 1; t < T; ++t) th.emplace_back(scan, t);
+      scan(0);
+      for (auto& x : th) x.join();
+    }
+    int64_t cut_before = 0;
+    for (int t = 0; t < T; ++t) cut_before += ext_sum[t];
+    cut_before /= 2;
+    for (int32_t v = 0; v < n; ++v) {
       locked[v] = 0;
       q[part[v]].push(Item(gain[v], v));
     }
@@ -382,6 +407,9 @@ void fm_refine(const LGraph& g, const double target[2], double ub, int max_passe
       pw[part[v]] += g.vw[v];
     }
     if (best_len == 0) break;
+    // a pass that was balanced already and gained under 0.1 % of the cut: the next one will not
+    // pay for its scan
+    if (imbalance(pw) == 0 && -best * 1000 < cut_before) break;
   }
 }
 
