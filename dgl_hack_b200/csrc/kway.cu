@@ -367,7 +367,12 @@ void fm_refine(const LGraph& g, const double target[2], double ub, int max_passe
       for (int sd = 0; sd < 2; ++sd) {
         while (!q[sd].empty()) {
           const Item it = q[sd].top();
-          if (locked[it.second] || part[it.second] != sd || it.first != gain[it.second]) { q[sd].pop(); continue; }
+          if (locked[it.second] || part[it.second] != sd) { q[sd].pop(); continue; }
+          if (it.first != gain[it.second]) {  // stale: decreases are not pushed, re-enter here
+            q[sd].pop();
+            if (it.first > gain[it.second]) q[sd].push(Item(gain[it.second], it.second));
+            continue;
+          }
           cand[sd] = it.second;
           break;
         }
@@ -391,8 +396,14 @@ void fm_refine(const LGraph& g, const double target[2], double ub, int max_passe
       for (int64_t j = g.xadj[v]; j < g.xadj[v + 1]; ++j) {
         const int32_t u = g.adj[j];
         if (u == v || locked[u]) continue;
-        gain[u] += (part[u] == from ? 2 : -2) * (int64_t)g.ew[j];
-        q[part[u]].push(Item(gain[u], u));
+        // every unlocked vertex keeps an entry >= its gain in the queue: an increase is pushed,
+        // a decrease is fixed lazily when its stale entry reaches the top (half the pushes)
+        if (part[u] == from) {
+          gain[u] += 2 * (int64_t)g.ew[j];
+          q[part[u]].push(Item(gain[u], u));
+        } else {
+          gain[u] -= 2 * (int64_t)g.ew[j];
+        }
       }
       const double imb = imbalance(pw);
       if (imb < best_imb || (imb == best_imb && cur < best)) {
