@@ -6,7 +6,13 @@ on the Reddit-shaped synthetic graph of BASELINE.json configs[1]
 
 One "step" = one forward pass (out = mean over in-edges of X[src]) + one backward pass
 (grad_X = transposed SpMM of grad_out / deg) over the whole graph through the public API
-(dgl_hack_b200.copy_reduce + autograd). metric = GEdges/s = 2*E*N_gpus / step time.
+(dgl_hack_b200.copy_reduce + autograd). metric = GEdges/s = 2*E*N_gpus / step time (2*E edges per step: E forward + E backward).
+
+The same run also measures the PARTITIONED multi-GPU path (bench_partitioned.py): the
+products-shaped graph k-way partitioned over the N ranks, copy_src+sum fwd+bwd and the 3-layer GCN
+epoch with the halo exchange, asserted against the 1-GPU kernel -> the `partitioned` object of
+the JSON line (strong scaling; this is the multi-GPU result, the Reddit headline at N>1 is N
+independent replicas).
 
 Prints ONE JSON line (rank 0). Keys follow the driver's contract; see DESIGN.md "Measurement".
 --impl reference times the UNMODIFIED reference CPU kernels (oracle/_ref/libdgl.so, OpenMP/minigun,
@@ -26,6 +32,7 @@ sys.path.insert(0, ROOT)
 
 N_NODES, N_EDGES, N_FEATS, ALPHA, SEED = 232965, 114615892, 602, 0.6, 2
 WORKLOAD = "reddit_shaped_graphsage_mean_copy_src_fwd_bwd"
+METRIC = "GEdges/s (SpMM copy_src+mean fwd+bwd; 2*E edges per step)"
 
 
 def powerlaw_endpoints(n, e, alpha, gen, device):
@@ -130,6 +137,10 @@ def time_reference_cpu(n, src_np, dst_np, d, steps, warmup):
     import numpy as np
     from oracle import ref_capi as R
     cores = os.cpu_count() or 1
+    if R.available():
+        # the launcher may have exported OMP_NUM_THREADS=1 (torch.distributed.run does): the CPU
+        # arm always runs on all host threads
+        cores = R.set_num_threads(cores)
     rs = np.random.RandomState(0)
     x = rs.uniform(-1, 1, (n, d)).astype(np.float32)
     go = rs.uniform(-1, 1, (n, d)).astype(np.float32)
@@ -184,14 +195,14 @@ def run_reference(args, rank, world):
     sample = ("edges into dst rows [0, N/%d) of the same graph: %d edges, all %d sources and the "
               "full [N,%d] feature matrix kept; per step 1 fwd + 1 bwd" % (frac, es, n, d))
     line = {
-        "impl": "reference", "metric": "GEdges/s (SpMM copy_src+mean fwd+bwd)", "value": value,
+        "impl": "reference", "metric": METRIC, "value": value,
         "unit": "GEdges/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "nodes": n, "edges": e, "feats": d,
                    "sample_edges": es},
         "cpu_baseline": {"value": value, "unit": "GEdges/s", "cores": cores, "kind": kind,
-                         "sample": sample},
+                         "sample": sample, "omp_threads": cores},
         "e2e": {"value": value, "unit": "GEdges/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -342,6 +353,18 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total, ms_e2e = float(t[0]), float(t[1])
 
+    # ---- the partitioned multi-GPU path (one graph over the N ranks), same run
+    partitioned = None
+    if not args.no_partitioned:
+        del X, GO, Xb, GOb, Xh, GOh, outh, gih, g
+        torch.cuda.empty_cache()
+        from bench_partitioned import run_partitioned
+        l1 = K.launch_count()
+        partitioned = run_partitioned(rank, world, dev, scale=args.scale, steps=args.steps,
+                                      warmup=args.warmup)
+        if partitioned is not None:
+            partitioned["gpu_launches_rank0"] = K.launch_count() - l1
+
     if rank == 0:
         ms_step = ms_total / args.steps
         value = 2.0 * e * world / (ms_step * 1e-3) / 1e9
@@ -350,15 +373,19 @@ def run_ours(args, rank, world, local_rank):
         peak, peak_src = measured_peak()
         bytes_fwd = algorithmic_bytes(n, n, e, d, l2)
         achieved = bytes_fwd / (fwd_ms * 1e-3) / 1e9
-        traffic = None
+        # DRAM bytes per launch of this kernel from the committed `ncu --set full` capture of the
+        # same command (profiles/ncu_traffic.json names the kernel and the commit it was taken on)
+        traffic, traffic_src = None, None
         tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
         if os.path.exists(tp) and args.scale == 1:
             try:
-                traffic = json.load(open(tp)).get("spmm_fwd_dram_bytes_per_launch")
+                tj = json.load(open(tp))
+                traffic = tj.get("spmm_fwd_dram_bytes_per_launch")
+                traffic_src = {k: tj.get(k) for k in ("kernel", "commit", "capture", "when")}
             except Exception:
                 traffic = None
         line = {
-            "metric": "GEdges/s (SpMM copy_src+mean fwd+bwd)", "value": value,
+            "metric": METRIC, "value": value,
             "unit": "GEdges/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -369,13 +396,17 @@ def run_ours(args, rank, world, local_rank):
                        "index_prep_ms_once": index_prep_ms},
             "roofline": {"bound": "hbm", "kernel": "spmm_kernel (forward, copy_src+mean)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "frac": achieved / peak, "frac_algorithmic": achieved / peak,
+                         "frac_dram": (traffic / (fwd_ms * 1e-3) / 1e9 / peak) if traffic else None,
+                         "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": bytes_fwd, "kernel_ms": fwd_ms,
                          "gedges_per_s_kernel": e / (fwd_ms * 1e-3) / 1e9},
             "e2e": {"value": e2e_value, "unit": "GEdges/s",
                     "h2d_bytes_per_step": 2 * n * d * 4, "d2h_bytes_per_step": 2 * n * d * 4,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "clocks": clocks,
+            "partitioned": partitioned,
         }
         if cpu_sample is not None:
             sec, cores, kind = time_reference_cpu(n, cpu_sample[0], cpu_sample[1], d, 1, 1)
@@ -400,6 +431,8 @@ def main():
     ap.add_argument("--ref-frac", type=int, default=64,
                     help="CPU arm works on the edges into the first N/ref_frac destination rows")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-partitioned", action="store_true",
+                    help="skip the partitioned products-shaped multi-GPU leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -118,6 +118,8 @@ SYMBOLS = {
                                        _c.c_void_p]),
     "DGLB200KernelScaledCopySum": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP, TensorP,
                                               TensorP, _c.c_void_p]),
+    "DGLB200KernelPeerCopySum": (_c.c_int, [GraphHandle, _c.c_int, _c.c_int, _c.c_void_p, TensorP,
+                                            TensorP, TensorP, _c.c_void_p]),
     "DGLB200EdgeSoftmaxForward": (_c.c_int, [GraphHandle, TensorP, TensorP, _c.c_void_p]),
     "DGLB200EdgeSoftmaxBackward": (_c.c_int, [GraphHandle, TensorP, TensorP, TensorP,
                                               _c.c_void_p]),

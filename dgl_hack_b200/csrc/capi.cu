@@ -912,6 +912,71 @@ int DGLB200KernelScaledCopySum(DGLB200GraphHandle graph, int transpose, const DG
   API_END();
 }
 
+// ---- aggregation over a feature matrix that is spread over several GPUs (extension) ----
+int DGLB200KernelPeerCopySum(DGLB200GraphHandle graph, int transpose, int n_slots,
+                             const void* const* slot_base, const DGLB200Tensor* node_code,
+                             const DGLB200Tensor* row_scale, DGLB200Tensor* out_data,
+                             void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && slot_base && node_code && out_data, "NULL argument");
+  B200_CHECK(n_slots >= 1 && n_slots <= 16, "PeerCopySum: 1 to 16 slots");
+  check_ctx(graph, {node_code, row_scale, out_data}, {"node_code", "row_scale", "out_data"});
+  check_id_arrays({node_code}, {"node_code"});
+  check_float(out_data, "out_data");
+  check_compact(out_data, "out_data");
+  const int64_t n_cols = transpose ? graph->num_dst : graph->num_src;  // gathered side
+  const int64_t n_rows = transpose ? graph->num_src : graph->num_dst;  // written side
+  B200_CHECK(node_code->shape[0] == n_cols, "PeerCopySum: node_code needs one code per gathered node");
+  B200_CHECK(out_data->ndim >= 1 && out_data->shape[0] == n_rows,
+             "PeerCopySum: out_data must have one row per reducing node");
+  if (row_scale) {
+    check_float(row_scale, "row_scale");
+    check_compact(row_scale, "row_scale");
+    B200_CHECK(num_elements(row_scale) == n_rows, "PeerCopySum: row_scale needs one value per reducing node");
+  }
+  const float* tab[16];
+  for (int i = 0; i < n_slots; ++i) {
+    B200_CHECK(slot_base[i] != nullptr, "PeerCopySum: NULL slot base");
+    tab[i] = static_cast<const float*>(slot_base[i]);
+  }
+  KernelCall c;
+  c.g = graph;
+  c.red = kSum;
+  c.op = kUseLhs;
+  c.bc = make_bcast("use_lhs", out_data, nullptr);
+  c.lhs_tgt = kSrc;
+  c.rhs_tgt = kNone;
+  c.rhs = nullptr;
+  c.rhs_rows = 0;
+  c.out = nullptr;
+  c.dst = data_ptr<float>(out_data);
+  c.dst_rows = n_rows;
+  c.lhs_map = c.rhs_map = c.out_map = nullptr;
+  c.mean = false;
+  c.row_scale = row_scale ? data_ptr<const float>(row_scale) : nullptr;
+  c.a_tab = tab;
+  c.n_slots = n_slots;
+  c.stream = static_cast<cudaStream_t>(stream);
+  if (!transpose) {   // out[v] = rs[v] * sum_{u -> v} X[code(u)]
+    c.mode = kFwd;
+    c.lhs = tab[0];
+    c.lhs_map = data_ptr<const int32_t>(node_code);
+    c.gout = nullptr;
+    c.lhs_rows = n_cols;
+    c.out_rows = n_rows;
+  } else {            // out[u] = rs[u] * sum_{u -> v} G[code(v)]
+    c.mode = kGradLhs;
+    c.lhs = data_ptr<const float>(out_data);  // never read
+    c.gout = tab[0];
+    c.out_map = data_ptr<const int32_t>(node_code);
+    c.lhs_rows = n_rows;
+    c.out_rows = n_cols;
+  }
+  B200_CUDA(cudaSetDevice(graph->device));
+  B200_CHECK(try_spmm(c), "PeerCopySum: shape not supported by the SpMM kernel");
+  API_END();
+}
+
 // ---- fused edge_softmax (extension) ----
 static int64_t softmax_width(DGLB200Graph* g, std::initializer_list<const DGLB200Tensor*> ts) {
   const DGLB200Tensor* first = *ts.begin();

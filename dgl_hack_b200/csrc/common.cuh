@@ -256,6 +256,10 @@ struct KernelCall {
   Bcast bc;
   bool mean;  // extension: divide the row sum by max(deg, 1)
   const float* row_scale = nullptr;  // extension (SpMM only): multiply finished row r by row_scale[r]
+  // extension (SpMM only, plain copy + sum): the gathered operand lives in n_slots blocks
+  // (own HBM and peer GPUs' mapped over NVLink); the operand's id map yields (slot, row) codes
+  const float* const* a_tab = nullptr;
+  int n_slots = 0;
   cudaStream_t stream;
 };
 

@@ -182,6 +182,8 @@ bool try_spmm(const KernelCall& c) {
   a.row_scale = c.row_scale;
   a.red = c.red;
   a.op = c.op;
+  a.write_empty = 0;
+  for (int i = 0; i < kMaxSlots; ++i) a.a_tab[i] = (c.a_tab && i < c.n_slots) ? c.a_tab[i] : nullptr;
   int bmode = kBNone;
   bool use_out_csr, walk_in_plain = false;
   // (tensor, target, user map) of the two gathered operands in "row/col of the walked CSR" terms
@@ -272,6 +274,11 @@ bool try_spmm(const KernelCall& c) {
     }
   }
 
+  if (c.a_tab) {  // peer-table gather: plain copy + sum through the operand's id map only
+    B200_CHECK(bmode == kBNone && a.red == kSum && a.op == kUseLhs && a_map != nullptr &&
+                   a_tgt != kEdge && c.n_slots >= 1 && c.n_slots <= kMaxSlots && c.a_tab[0],
+               "peer-table gather supports copy + sum with a (slot, row) id map only");
+  }
   // forward: reference sum order
   const int walk = use_out_csr ? kWalkOut : (walk_in_plain ? kWalkIn : kWalkInSorted);
   const Csr& csr = walk_csr(g, walk);
@@ -290,6 +297,7 @@ bool try_spmm(const KernelCall& c) {
     bool ok = (D % vec == 0) && aligned(A, vec * 4) && aligned(c.dst, vec * 4);
     if (bmode == kBFull) ok = ok && aligned(B, vec * 4);
     if (bmode == kBHead) ok = ok && (a.b_head_div % vec == 0);
+    for (int i = 0; c.a_tab && i < c.n_slots; ++i) ok = ok && aligned(c.a_tab[i], vec * 4);
     if (ok) break;
     vec >>= 1;
   }
@@ -383,7 +391,8 @@ bool try_spmm(const KernelCall& c) {
     const int tch = round_tma_ch((nvec + 31) / 32);
     const int64_t row_bytes = D * 4;
     bool ok = (lpr == 32) && (bmode == kBNone || scalar_w) && tch > 0 && row_bytes <= 8192 &&
-              aligned(A, 16) && o_map == nullptr && c.row_scale == nullptr;  // mapped / scaled: LDG path
+              aligned(A, 16) && o_map == nullptr && c.row_scale == nullptr &&  // mapped / scaled: LDG path
+              c.a_tab == nullptr;
     const int64_t mean_deg = E / std::max<int64_t>(csr.n_rows, 1);
     // Measured on B200 (profiles/r1_spmm_paths.md): the LDG path beats the bulk-copy path on
     // this gather (TMA 1-D copies of 2.4 KB rows top out near 20-30 B/clk/SM), so it is opt-in.

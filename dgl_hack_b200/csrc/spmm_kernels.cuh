@@ -9,6 +9,9 @@ enum IdSrc { kFromCol = 0, kFromEid = 1, kFromRow = 2 };
 // kBHead: one B value per head (column / b_head_div); kBScalar: one B value per neighbour
 enum BMode { kBNone = 0, kBFull = 1, kBHead = 2, kBScalar = 3 };
 constexpr int kOpNegA = 100;  // internal: value = -A (gradient of the rhs of "sub")
+constexpr int kMaxSlots = 16;
+constexpr int kSlotShift = 27;  // up to 2^27 rows per slot
+constexpr int kRowMask = (1 << kSlotShift) - 1;
 
 struct SpmmArgs {
   const int32_t* indptr;
@@ -45,6 +48,12 @@ struct SpmmArgs {
   // the schedule with >= kLongRow edges) are served by a whole warp whose 32 / lpr lane groups
   // take every (32 / lpr)-th edge and fold their partial results at the end
   int n_wide;
+  // peer-table gather (TAB kernels only; partitioned graphs, csrc/peer.cu): a gathered id is
+  // (slot << kSlotShift) | row and reads a_tab[slot] + row * D -- slot = which GPU's staged
+  // feature block (own HBM or a peer's, mapped over NVLink), row = the node's local row there
+  const float* a_tab[kMaxSlots];
+  // out_map is a plain row list (every listed row is written, rows without edges included)
+  int write_empty;
 };
 
 template <int VEC>
@@ -110,7 +119,8 @@ constexpr int min_blocks_for(int vec, int ch, int u, int bmode) {
 // constant; otherwise lpr (< 32, CH == 1) lanes serve a row and a warp handles 32 / lpr rows.
 // MUL: the binary op is known to be "mul" (commutative: operand order irrelevant), so the
 // per-element runtime op switch disappears from the inner loop.
-template <int VEC, int CH, int U, bool SUM, int BMODE, bool FULL, bool MUL>
+// TAB: gathered ids are (slot, row) pairs resolved through a_tab (see SpmmArgs).
+template <int VEC, int CH, int U, bool SUM, int BMODE, bool FULL, bool MUL, bool TAB = false>
 __global__ void __launch_bounds__(256, min_blocks_for(VEC, CH, U, BMODE))
 spmm_kernel(const SpmmArgs a) {
   const int lane = threadIdx.x & 31;
@@ -150,7 +160,7 @@ spmm_kernel(const SpmmArgs a) {
       if (a.n_seg > 0 && deg > a.seg_len) {  // heavy row: served by its segments
         row_ok = false;
         deg = 0;
-      } else if (a.out_map && deg == 0) {
+      } else if (a.out_map && deg == 0 && !a.write_empty) {
         // with an output id map only rows that receive edges have a slot (the reference's
         // _build_idx_map holds -1 / ends early for the others, runtime/scheduler.py): the row
         // keeps the identity written by the fill and the map is never read for it
@@ -216,7 +226,12 @@ spmm_kernel(const SpmmArgs a) {
         int ib = 0;
         if (BMODE != kBNone) ib = __shfl_sync(0xffffffffu, pb, srcl, bw);
         const bool on = (ei < bw) && (base + ei < deg);
-        const float* ap = a.A + (int64_t)ia * a.D + cbase;
+        const float* ap;
+        if (TAB) {
+          ap = a.a_tab[(ia >> kSlotShift) & (kMaxSlots - 1)] + (int64_t)(ia & kRowMask) * a.D + cbase;
+        } else {
+          ap = a.A + (int64_t)ia * a.D + cbase;
+        }
         const float* bp = nullptr;
         if (BMODE != kBNone)
           bp = a.B + ((a.b_src == kFromRow) ? b_row_const : (int64_t)ib * a.b_width);
@@ -313,6 +328,15 @@ constexpr int unroll_for(int vec, int ch) {
 
 template <int VEC, int CH, int U>
 static void launch_shape(const SpmmArgs& a, int bmode, bool sum, int blocks, cudaStream_t s) {
+  if (a.a_tab[0] != nullptr) {  // peer-table gather: plain copy + sum only (checked by the caller)
+    if (a.lpr == 32) {
+      spmm_kernel<VEC, CH, U, true, kBNone, true, false, true><<<blocks, 256, 0, s>>>(a);
+    } else {
+      if constexpr (CH == 1)
+        spmm_kernel<VEC, CH, U, true, kBNone, false, false, true><<<blocks, 256, 0, s>>>(a);
+    }
+    return;
+  }
 #define B200_SPMM_LAUNCH(SUMV, BM, MULV)                                             \
   do {                                                                               \
     if (a.lpr == 32) {                                                               \

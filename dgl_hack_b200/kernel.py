@@ -204,3 +204,17 @@ def scaled_copy_sum(G, transpose, X, col_scale, row_scale, out):
         check_call(LIB.DGLB200KernelScaledCopySum(G.handle, int(bool(transpose)), *ptrs,
                                                   _stream(G)))
     del keep
+
+
+def peer_copy_sum(G, transpose, slot_bases, node_code, row_scale, out):
+    """Extension: copy_src + sum over a feature matrix spread over several GPUs' memories
+    (DGLB200KernelPeerCopySum): gathered node c reads row (code & (2^27-1)) of block
+    slot_bases[code >> 27], code = node_code[c]; slot_bases are raw device pointers (own or
+    peer-mapped buffers, row pitch = out's width)."""
+    keep, ptrs = _keep(node_code, row_scale, out)
+    k = len(slot_bases)
+    bases = (ctypes.c_void_p * k)(*[int(b) for b in slot_bases])
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelPeerCopySum(G.handle, int(bool(transpose)), k, bases, *ptrs,
+                                                _stream(G)))
+    del keep

@@ -24,6 +24,9 @@ import os
 import torch
 import torch.distributed as dist
 
+SLOT_SHIFT = 27                 # csrc/spmm_kernels.cuh kSlotShift: code = (slot << 27) | row
+MAX_SLOTS = 16
+
 
 def range_partition(num_nodes, dst, k):
     """Contiguous node ranges balanced by in-edge count (the default when the node numbering has
@@ -148,6 +151,10 @@ class Partition(object):
         self.edges_inner = self.edges_halo = None  # (src_local, dst_local) pairs
         self.n_inner = self.n_halo = 0
         self.cut_edges = self.local_edges = 0
+        # direct peer-gather plan (None when the plan was loaded from per-part files)
+        self.fwd_coo = self.bwd_coo = self.fwd_code = self.bwd_code = None
+        self.n_ohalo = 0
+        self.rows_max = 0
 
     @classmethod
     def build(cls, num_nodes, src, dst, part, rank, world):
@@ -188,7 +195,41 @@ class Partition(object):
             p.send_idx.append(g2l[need])
         p.send_counts = [int(t.numel()) for t in p.send_idx]
         p.send_cat = torch.cat(p.send_idx) if world > 1 else p.send_idx[0]
+        p._build_direct_plan(num_nodes, src, dst, part, e_src, e_dst, ls, ld, mine_src)
         return p
+
+    def _build_direct_plan(self, num_nodes, src, dst, part, e_src, e_dst, ls, ld, mine_src):
+        """Plan of the single-pass aggregation with peer loads (SURVEY 8e option iii): every node
+        is addressed as (owner rank, row inside the owner's block) = code (owner << 27) | row,
+        row = rank of the node among its owner's nodes in ascending global id (the order of
+        `inner_global` on the owner). Forward graph: ALL in-edges of the inner nodes, sources
+        numbered inner-first then halo (`fwd_code` translates them); backward graph: ALL out-edges
+        of the inner nodes, destinations numbered inner-first then the remote destinations
+        (`bwd_code`), so the gradient is one transposed walk that reads grad_out rows from the
+        peers -- no pushed halo gradients and no reduction pass at the owner."""
+        rank, world, dev = self.rank, self.world, src.device
+        counts = torch.bincount(part, minlength=world)
+        self.rows_max = int(counts.max()) if num_nodes else 0
+        if world > MAX_SLOTS or self.rows_max >= (1 << SLOT_SHIFT):
+            return
+        order = torch.argsort(part, stable=True)
+        starts = torch.cumsum(counts, 0) - counts
+        code = torch.empty(num_nodes, dtype=torch.int64, device=dev)
+        code[order] = (torch.arange(num_nodes, device=dev) - starts[part[order]]) + \
+            (part[order] << SLOT_SHIFT)
+        del order
+        self.fwd_coo = (ls, ld)                      # global edge-id order
+        self.fwd_code = torch.cat([code[self.inner_global], code[self.halo_global]]).to(torch.int32)
+        o_src, o_dst = src[mine_src], dst[mine_src]
+        away = part[o_dst] != rank
+        ohalo = torch.unique(o_dst[away])
+        self.n_ohalo = int(ohalo.numel())
+        g2c = torch.full((num_nodes,), -1, dtype=torch.int64, device=dev)
+        g2c[self.inner_global] = torch.arange(self.n_inner, device=dev)
+        lsrc = g2c[o_src]
+        g2c[ohalo] = self.n_inner + torch.arange(self.n_ohalo, device=dev)
+        self.bwd_coo = (lsrc, g2c[o_dst])
+        self.bwd_code = torch.cat([code[self.inner_global], code[ohalo]]).to(torch.int32)
 
     @classmethod
     def from_files(cls, directory, rank, world, device="cpu"):
@@ -355,17 +396,38 @@ class PartitionedGraph(object):
     """A Partition bound to the CUDA kernels: two GraphIndex objects (inner-source and
     halo-source edges, destinations = inner nodes) and the halo-exchanging aggregation."""
 
-    def __init__(self, part, device, halo="auto", max_feat=256):
-        """halo: "peer" = peer-memory pushes over NVLink (PeerExchange; needs all ranks on one
-        node), "nccl" = all-to-all-v, "auto" = peer when the environment allows it
-        (B200_HALO overrides)."""
+    def __init__(self, part, device, halo="auto", max_feat=256, blocks=None):
+        """halo: "direct" = ONE aggregation kernel per direction whose gathers read the peers'
+        staged feature blocks over NVLink (PeerGather; needs all ranks on one node), "peer" =
+        peer-memory pushes into halo buffers + two-pass aggregation (PeerExchange), "nccl" =
+        all-to-all-v + two-pass aggregation, "auto" = direct when the environment allows it
+        (B200_HALO overrides). `blocks`: an already-built block provider (LocalBlocks for
+        one-process tests / all-local timing); default = CUDA-IPC blocks agreed on by all ranks."""
         from .graph_index import GraphIndex
         self.part = part
         self.device = torch.device(device)
         halo = os.environ.get("B200_HALO", halo)
         part.peer = None
-        if part.world > 1 and halo in ("auto", "peer") and dist.is_initialized() and \
-                dist.get_backend() == "nccl":
+        self.gather = None
+        self.g_inner = self.g_halo = self.g_rev = None
+        nccl = part.world > 1 and dist.is_initialized() and dist.get_backend() == "nccl"
+        if part.world == 1:
+            # one rank: the whole graph, no staging, no codes
+            si, di = part.edges_inner
+            self.g_inner = GraphIndex.from_coo(part.n_inner, part.n_inner, si, di, device)
+            self.halo_path = "none"
+            return
+        if halo in ("auto", "direct") and part.fwd_coo is not None and \
+                (blocks is not None or nccl):
+            if blocks is None:
+                blocks = IpcBlocks.create(part, self.device, max_feat, required=(halo == "direct"))
+            if blocks is not None:
+                self.gather = PeerGather(part, self.device, blocks)
+                self.halo_path = "direct"
+                return
+        if halo == "direct":
+            raise RuntimeError("halo='direct' needs NCCL ranks on one node (or a block provider)")
+        if nccl and halo in ("auto", "peer"):
             ok = torch.ones(1, device=self.device)
             try:
                 px = PeerExchange(part, self.device, max_feat)
@@ -375,7 +437,7 @@ class PartitionedGraph(object):
                 px, ok = None, torch.zeros(1, device=self.device)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
             part.peer = px if ok.item() > 0 else None
-        self.halo_path = "peer" if part.peer is not None else ("nccl" if part.world > 1 else "none")
+        self.halo_path = "peer" if part.peer is not None else "nccl"
         si, di = part.edges_inner
         sh, dh = part.edges_halo
         self.g_inner = GraphIndex.from_coo(part.n_inner, part.n_inner, si, di, device)
@@ -383,8 +445,7 @@ class PartitionedGraph(object):
         # received halo gradients -> owners: row i of the receive buffer belongs to inner node
         # send_cat[i]; as a graph (edge i -> node send_cat[i]) the reduction is copy_e + sum, one
         # deterministic kernel instead of k-1 index_add_ launches with atomics
-        self.g_rev = None
-        if part.world > 1 and part.send_cat.numel() > 0:
+        if part.send_cat.numel() > 0:
             sc = part.send_cat.to(device)
             self.g_rev = GraphIndex.from_coo(part.n_inner, part.n_inner, sc, sc, device)
             part.reduce_received = self._reduce_received
@@ -417,6 +478,13 @@ class PartitionedGraph(object):
         norms): out[v] = dst_scale[v] * sum_{u->v} src_scale[u] * x[u], the scaling done inside the
         aggregation kernels (backend.scaled_copy_sum); the halo nodes' src_scale values are
         fetched from their owners once and cached."""
+        if self.part.world == 1:
+            from . import backend as F
+            return F.scaled_copy_sum(self.g_inner, x_inner, src_scale, dst_scale)
+        if self.gather is not None:
+            cs = src_scale.detach().reshape(-1).contiguous() if src_scale is not None else None
+            rs = dst_scale.detach().reshape(-1).contiguous() if dst_scale is not None else None
+            return _PeerCopySum.apply(self.gather, x_inner.contiguous(), cs, rs)
         if src_scale is None and dst_scale is None:
             return _HaloCopySum.apply(self.part, self._agg, self._agg_t, x_inner)
         from . import kernel as K
@@ -454,6 +522,192 @@ class PartitionedGraph(object):
             K.scaled_copy_sum(g, True, grad_out, rs, cs, grad)
             return grad[:n_src]
         return _HaloCopySum.apply(part, agg, agg_t, x_inner)
+
+
+class _PeerCopySum(torch.autograd.Function):
+    """out[v] = rs[v] * sum_{u -> v} cs[u] * x[u] over ALL in-edges of the rank's inner nodes in
+    one kernel: every rank stages cs * x in its block, one barrier, then the SpMM gathers each
+    source row from the block of its owner (own HBM or a peer's over NVLink). The gradient is the
+    same thing on the out-edges with grad_out staged (scaled by rs) and cs applied per row."""
+
+    @staticmethod
+    def forward(ctx, gather, x, cs, rs):
+        ctx.gather, ctx.scales = gather, (cs, rs)
+        return gather.run(0, x, cs, rs)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        cs, rs = ctx.scales
+        return None, ctx.gather.run(1, grad_out.contiguous(), rs, cs), None, None
+
+
+class PeerGather(object):
+    """Single-pass partitioned aggregation (SURVEY 8e option iii, csrc/spmm_kernels.cuh TAB
+    kernels). `blocks` provides, per rank, two forward and two backward staging blocks of
+    rows_max x max_feat floats that every rank of the node can read, plus a barrier. Blocks
+    alternate, so a block is rewritten only after every rank has passed the barrier that follows
+    its last readers (two barriers lie between two writes of the same block)."""
+
+    def __init__(self, part, device, blocks):
+        from .graph_index import GraphIndex
+        self.part, self.device, self.blocks = part, torch.device(device), blocks
+        fs, fd = part.fwd_coo
+        bs, bd = part.bwd_coo
+        self.g_f = GraphIndex.from_coo(part.n_inner + part.n_halo, part.n_inner, fs, fd, device)
+        self.g_b = GraphIndex.from_coo(part.n_inner, part.n_inner + part.n_ohalo, bs, bd, device)
+        self.code = (part.fwd_code.to(device).contiguous(), part.bwd_code.to(device).contiguous())
+        self._turn = [0, 0]
+
+    def stage(self, which, x, scale):
+        """Writes scale * x into this rank's next block of direction `which`; returns its index."""
+        b = 2 * which + self._turn[which]
+        self._turn[which] ^= 1
+        n, d = x.shape
+        if d > self.blocks.max_feat:
+            raise ValueError("feature width %d exceeds the staging blocks (max_feat=%d)"
+                             % (d, self.blocks.max_feat))
+        view = self.blocks.own_view(b)[: n * d].view(n, d)
+        if scale is None:
+            view.copy_(x)
+        else:
+            torch.mul(x, scale.view(-1, 1), out=view)
+        return b
+
+    def reduce(self, which, b, d, row_scale, like):
+        from . import kernel as K
+        out = like.new_empty((self.part.n_inner, d))
+        K.peer_copy_sum(self.g_f if which == 0 else self.g_b, which == 1, self.blocks.bases(b),
+                        self.code[which], row_scale, out)
+        return out
+
+    def run(self, which, x, stage_scale, row_scale):
+        shape = x.shape
+        x2 = x.reshape(shape[0], -1)
+        b = self.stage(which, x2, stage_scale)
+        self.blocks.barrier()
+        out = self.reduce(which, b, x2.shape[1], row_scale, x2)
+        return out.view((self.part.n_inner,) + tuple(shape[1:]))
+
+
+class LocalBlocks(object):
+    """Staging blocks of several ranks inside ONE process / one GPU: the in-process stand-in for
+    IpcBlocks (tests on a one-GPU box; `alias=True` maps every slot to this rank's own block --
+    same kernel, same indices, no NVLink traffic -- which is how bench.py measures the exposed
+    communication time of the real run)."""
+
+    def __init__(self, group, rank):
+        self._group, self.rank = group, rank
+        self.max_feat = group["max_feat"]
+
+    @classmethod
+    def group(cls, world, rows_max, max_feat, device, alias_rank=None):
+        bufs = [[torch.zeros(max(rows_max, 1) * max_feat, device=device) for _ in range(4)]
+                for _ in range(world if alias_rank is None else 1)]
+        g = {"bufs": bufs, "max_feat": int(max_feat), "world": world, "alias": alias_rank}
+        return [cls(g, r) for r in range(world)]
+
+    def _mine(self):
+        return self._group["bufs"][0 if self._group["alias"] is not None else self.rank]
+
+    def own_view(self, b):
+        return self._mine()[b]
+
+    def bases(self, b):
+        if self._group["alias"] is not None:
+            return [self._mine()[b].data_ptr()] * self._group["world"]
+        return [bufs[b].data_ptr() for bufs in self._group["bufs"]]
+
+    def barrier(self):
+        pass
+
+    def close(self):
+        pass
+
+
+class IpcBlocks(object):
+    """Staging blocks in cudaMalloc'ed memory mapped into every rank of the node with CUDA IPC
+    (csrc/peer.cu DGLB200PeerAlloc / PeerOpen); the barrier is one stream-ordered NCCL
+    all-reduce of a flag."""
+
+    def __init__(self):
+        self._own, self._mapped, self._ptr = [], [], None
+
+    @classmethod
+    def create(cls, part, device, max_feat, required=False):
+        """Collective over all ranks. Returns None (on every rank) when any rank cannot allocate
+        or map the blocks; raises instead when `required`."""
+        import ctypes
+        from ._lib import LIB, check_call
+        self = cls()
+        self._lib, self._ct = LIB, ctypes
+        self.max_feat, self.device = int(max_feat), torch.device(device)
+        k, me = part.world, part.rank
+        dev_index = self.device.index or 0
+        n = max(part.rows_max, 1) * self.max_feat
+        handles = torch.zeros(4, 64, dtype=torch.uint8)
+        ok, err = 1.0, None
+        try:
+            for i in range(4):
+                ptr, h = ctypes.c_void_p(), (ctypes.c_ubyte * 64)()
+                check_call(LIB.DGLB200PeerAlloc(n * 4, dev_index, ctypes.byref(ptr), h))
+                self._own.append(ptr.value)
+                handles[i] = torch.tensor(list(h), dtype=torch.uint8)
+        except Exception as e:  # agreed on below: every rank takes the same path
+            ok, err = 0.0, e
+        if not self._agree(ok):
+            self.close()
+            if required:
+                raise RuntimeError("IpcBlocks: allocation failed on some rank: %r" % (err,))
+            return None
+        hd = handles.to(self.device)
+        allh = [torch.empty_like(hd) for _ in range(k)]
+        dist.all_gather(allh, hd)
+        self._ptr = [[0] * k for _ in range(4)]
+        try:
+            for q in range(k):
+                hq = allh[q].cpu()
+                for i in range(4):
+                    if q == me:
+                        self._ptr[i][q] = self._own[i]
+                        continue
+                    ptr = ctypes.c_void_p()
+                    raw = (ctypes.c_ubyte * 64)(*hq[i].tolist())
+                    check_call(LIB.DGLB200PeerOpen(raw, dev_index, ctypes.byref(ptr)))
+                    self._ptr[i][q] = ptr.value
+                    self._mapped.append(ptr.value)
+        except Exception as e:
+            ok, err = 0.0, e
+        if not self._agree(ok):
+            self.close()
+            if required:
+                raise RuntimeError("IpcBlocks: peer mapping failed on some rank: %r" % (err,))
+            return None
+        self._views = [torch.as_tensor(_RawCuda(p, n), device=self.device) for p in self._own]
+        self._flag = torch.zeros(1, device=self.device)
+        return self
+
+    def _agree(self, ok):
+        t = torch.tensor([ok], device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return t.item() > 0
+
+    def own_view(self, b):
+        return self._views[b]
+
+    def bases(self, b):
+        return self._ptr[b]
+
+    def barrier(self):
+        dist.all_reduce(self._flag)      # stream-ordered: the current stream waits, not the host
+
+    def close(self):
+        if self._mapped or self._own:
+            torch.cuda.synchronize(self.device)
+        for p in self._mapped:
+            self._lib.DGLB200PeerClose(self._ct.c_void_p(p))
+        for p in self._own:
+            self._lib.DGLB200PeerFree(self._ct.c_void_p(p))
+        self._mapped, self._own = [], []
 
 
 class _RawCuda(object):

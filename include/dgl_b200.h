@@ -337,6 +337,20 @@ int DGLB200KernelScaledCopySum(DGLB200GraphHandle graph, int transpose,
                                const DGLB200Tensor* row_scale, DGLB200Tensor* out_data,
                                void* stream);
 
+/* copy_src + sum over a feature matrix that is spread over several GPUs of one node (partitioned
+ * graphs, SURVEY 8e option iii: peer loads inside the SpMM, no pack / send / unpack). Gathered
+ * node c of `graph` reads row (node_code[c] & (2^27 - 1)) of block slot_base[node_code[c] >> 27];
+ * every block is a row-major fp32 matrix with the width of out_data, in this GPU's memory or in a
+ * peer's (CUDA IPC mapping; the loads travel over NVLink / NVSwitch). slot_base is a HOST array of
+ * n_slots <= 16 device pointers, node_code a device int32 array with one code per gathered node.
+ * transpose = 0: out[v] = row_scale[v] * sum_{u -> v} X[code(u)] over the (src, edge id)-ordered
+ * in-CSR; transpose = 1: out[u] = row_scale[u] * sum_{u -> v} X[code(v)] over the out-CSR.
+ * row_scale may be NULL. Ordering against the writers of the blocks is the caller's (barrier). */
+int DGLB200KernelPeerCopySum(DGLB200GraphHandle graph, int transpose, int n_slots,
+                             const void* const* slot_base, const DGLB200Tensor* node_code,
+                             const DGLB200Tensor* row_scale, DGLB200Tensor* out_data,
+                             void* stream);
+
 /* Dispatch introspection for tests / bench: name of the kernel family the LAST compute call in
  * this process used ("spmm", "generic_row", "generic_edge", ...), and how many kernel launches
  * the library has issued since load (all threads). */

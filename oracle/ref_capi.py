@@ -40,6 +40,16 @@ def lib():
     return _lib
 
 
+def set_num_threads(n):
+    """omp_set_num_threads on the libgomp the reference library is linked against, so the CPU arm
+    uses the same number of host threads whatever OMP_NUM_THREADS the launcher exported
+    (torch.distributed.run sets it to 1). Returns the number now in effect."""
+    lib()
+    gomp = ctypes.CDLL("libgomp.so.1", ctypes.RTLD_GLOBAL)
+    gomp.omp_set_num_threads(int(n))
+    return int(gomp.omp_get_max_threads())
+
+
 def _check(rc):
     if rc != 0:
         raise RuntimeError(lib().DGLGetLastError().decode("utf-8", "replace"))

@@ -61,7 +61,7 @@ def test_partitioned_kernels_match_whole_graph(world, d):
     torch.testing.assert_close(grad, xg.grad, rtol=1e-5, atol=5e-4)
 
 
-def _nccl_worker(rank, world, port, q):
+def _nccl_worker(rank, world, port, halo, d, q):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -72,31 +72,47 @@ def _nccl_worker(rank, world, port, q):
         import dgl_hack_b200 as B
         from dgl_hack_b200 import backend as F
         from dgl_hack_b200.partition import Partition, PartitionedGraph, range_partition
-        n, e, d = 20000, 400000, 64
+        n, e = 20000, 400000
         src, dst = _graph(n, e, 33, dev)
         gen = torch.Generator().manual_seed(1)
         x = (torch.rand(n, d, generator=gen) * 2 - 1).to(dev)
         w = (torch.rand(n, d, generator=gen) * 2 - 1).to(dev)
+        cs = (torch.rand(n, generator=gen) + 0.5).to(dev)
+        rs = (torch.rand(n, generator=gen) + 0.5).to(dev)
         g = B.GraphIndex.from_coo(n, n, src, dst, dev)
-        xg = x.clone().requires_grad_(True)
-        ref = F.copy_reduce("sum", g, 0, xg, n)
-        ref.backward(w)
         part = range_partition(n, dst, world)
+        if world > 2:
+            part[part == world - 1] = 0          # the last rank owns no node at all
         p = Partition.build(n, src, dst, part, rank, world)
-        pg = PartitionedGraph(p, dev)
-        xi = x[p.inner_global].clone().requires_grad_(True)
-        out = pg.copy_src_sum(xi)
-        out.backward(w[p.inner_global].contiguous())
-        ok_f = torch.allclose(out.detach(), ref.detach()[p.inner_global], rtol=1e-5, atol=5e-4)
-        ok_b = torch.allclose(xi.grad, xg.grad[p.inner_global], rtol=1e-5, atol=5e-4)
-        q.put((rank, bool(ok_f), bool(ok_b)))
+        pg = PartitionedGraph(p, dev, halo=halo)
+        assert pg.halo_path == halo, (pg.halo_path, halo)
+        res = []
+        for scaled in (False, True):
+            xg = x.clone().requires_grad_(True)
+            ref = F.scaled_copy_sum(g, xg, cs, rs) if scaled else F.copy_reduce("sum", g, 0, xg, n)
+            ref.backward(w)
+            xi = x[p.inner_global].clone().requires_grad_(True)
+            for _ in range(3):   # several rounds: the alternating blocks get reused
+                xi.grad = None
+                out = pg.copy_src_sum(xi, cs[p.inner_global], rs[p.inner_global]) if scaled \
+                    else pg.copy_src_sum(xi)
+                out.backward(w[p.inner_global].contiguous())
+            res.append(torch.allclose(out.detach(), ref.detach()[p.inner_global], rtol=1e-5, atol=5e-4))
+            res.append(torch.allclose(xi.grad, xg.grad[p.inner_global], rtol=1e-5, atol=5e-4))
+        torch.cuda.synchronize()
+        q.put((rank, res))
     finally:
         dist.destroy_process_group()
 
 
-def test_partitioned_two_gpus_nccl():
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("halo,d", [("direct", 100), ("direct", 47), ("peer", 100), ("nccl", 47)])
+def test_partitioned_multi_gpu(world, halo, d):
+    """The real exchanges between processes (one per GPU): peer loads inside the SpMM
+    ("direct"), peer-memory pushes ("peer") and NCCL all-to-all-v, against the whole-graph
+    kernel; widths not divisible by 4 and a rank without nodes included."""
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
     import torch.multiprocessing as mp
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -104,14 +120,68 @@ def test_partitioned_two_gpus_nccl():
     s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, halo, d, q))
+             for r in range(world)]
     for pr in procs:
         pr.start()
-    res = [q.get(timeout=300) for _ in range(2)]
+    res = [q.get(timeout=300) for _ in range(world)]
     for pr in procs:
         pr.join(timeout=120)
         assert pr.exitcode == 0
-    assert all(r[1] and r[2] for r in res), res
+    assert all(all(r[1]) for r in res), res
+
+
+@pytest.mark.parametrize("world,method", [(2, "range"), (4, "range"), (3, "empty_rank"),
+                                          (2, "no_halo")])
+@pytest.mark.parametrize("d", [100, 47, 6])
+def test_direct_gather_one_process(world, method, d):
+    """The single-pass peer-gather kernels (TAB SpMM, forward over all in-edges, backward over
+    all out-edges) with every rank's staging block in THIS process (LocalBlocks): same kernels
+    and codes as the multi-GPU run, checked against the whole-graph kernel incl. degree scales."""
+    import dgl_hack_b200 as B
+    from dgl_hack_b200 import backend as F
+    from dgl_hack_b200.partition import (Partition, PartitionedGraph, LocalBlocks,
+                                         range_partition)
+    dev = torch.device("cuda:0")
+    n, e = 3000, 60000
+    src, dst = _graph(n, e, 21, dev)
+    if method == "no_halo":          # two disconnected halves: nothing crosses the cut
+        half = n // 2
+        src = torch.where(dst < half, src % half, half + src % half)
+    gen = torch.Generator().manual_seed(3)
+    x = (torch.rand(n, d, generator=gen) * 2 - 1).to(dev)
+    w = (torch.rand(n, d, generator=gen) * 2 - 1).to(dev)
+    cs = (torch.rand(n, generator=gen) + 0.5).to(dev)
+    rs = (torch.rand(n, generator=gen) + 0.5).to(dev)
+    g = B.GraphIndex.from_coo(n, n, src, dst, dev)
+    xg = x.clone().requires_grad_(True)
+    ref = F.scaled_copy_sum(g, xg, cs, rs)
+    ref.backward(w)
+    if method == "empty_rank":
+        part = range_partition(n, dst, world - 1)
+    elif method == "no_halo":
+        part = (torch.arange(n, device=dev) >= n // 2).long()
+    else:
+        part = range_partition(n, dst, world)
+    plans = [Partition.build(n, src, dst, part, r, world) for r in range(world)]
+    if method == "no_halo":
+        assert all(p.n_halo == 0 and p.n_ohalo == 0 for p in plans)
+    blocks = LocalBlocks.group(world, plans[0].rows_max, 128, dev)
+    pgs = [PartitionedGraph(p, dev, halo="direct", blocks=b) for p, b in zip(plans, blocks)]
+    assert all(pg.halo_path == "direct" for pg in pgs)
+    for _ in range(2):               # second round runs on the alternate blocks
+        staged = [pg.gather.stage(0, x[p.inner_global].contiguous(), cs[p.inner_global])
+                  for p, pg in zip(plans, pgs)]
+        outs = [pg.gather.reduce(0, b, d, rs[p.inner_global].contiguous(), x)
+                for p, pg, b in zip(plans, pgs, staged)]
+        staged = [pg.gather.stage(1, w[p.inner_global].contiguous(), rs[p.inner_global])
+                  for p, pg in zip(plans, pgs)]
+        grads = [pg.gather.reduce(1, b, d, cs[p.inner_global].contiguous(), x)
+                 for p, pg, b in zip(plans, pgs, staged)]
+    for p, out, grad in zip(plans, outs, grads):
+        assert out.shape == (p.n_inner, d)
+        torch.testing.assert_close(out, ref.detach()[p.inner_global], rtol=1e-5, atol=5e-4)
+        torch.testing.assert_close(grad, xg.grad[p.inner_global], rtol=1e-5, atol=5e-4)
 
 
 @pytest.mark.gpu
