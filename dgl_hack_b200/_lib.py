@@ -118,6 +118,16 @@ SYMBOLS = {
                                        _c.c_void_p]),
     "DGLB200KernelScaledCopySum": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP, TensorP,
                                               TensorP, _c.c_void_p]),
+    "DGLB200GraphCreateFromTypedCSR": (_c.c_int, [_c.c_int64, _c.c_int64, _c.c_int, _c.c_void_p,
+                                                  _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int64,
+                                                  _c.c_int, _c.c_void_p, _c.POINTER(GraphHandle)]),
+    "DGLB200RegisterInto": (_c.c_int, [_c.c_void_p]),
+    "DGLB200SetStream": (_c.c_int, [_c.c_void_p]),
+    "DGLB200PackedFuncCount": (_c.c_int, []),
+    "DGLB200PackedFuncName": (_c.c_char_p, [_c.c_int]),
+    "DGLB200PackedFuncGet": (_c.c_void_p, [_c.c_int]),
+    "DGLB200PackedCacheClear": (_c.c_int, []),
+    "DGLB200PackedStats": (_c.c_int, [_c.POINTER(_c.c_int64)]),
     "DGLB200KernelPeerCopySum": (_c.c_int, [GraphHandle, _c.c_int, _c.c_int, _c.c_void_p, TensorP,
                                             TensorP, TensorP, _c.c_void_p]),
     "DGLB200EdgeSoftmaxForward": (_c.c_int, [GraphHandle, TensorP, TensorP, _c.c_void_p]),

@@ -225,6 +225,12 @@ struct DGLB200Graph {
   b200::TypeIndex ty;
   // endpoints by edge id (lazy; the edge-output kernels walk edges in id order)
   int32_t *coo_src = nullptr, *coo_dst = nullptr;
+  // Id validation of graphs built from DEVICE arrays: out-of-range ids are clamped to 0 while the
+  // index is built (no out-of-bounds write can happen) and recorded in this device flag, which
+  // is read at the first host synchronisation the handle goes through anyway (first kernel plan,
+  // CopyCSR, Degrees). Host arrays are checked before the constructor returns.
+  int32_t* bad_ids = nullptr;
+  bool ids_checked = true;
 };
 
 namespace b200 {
@@ -240,6 +246,8 @@ const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s);
 // Segment plan of a CSR for segments of `seg_len` positions (built once; synchronises then).
 SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s);
 int segment_length(int64_t num_edges);  // spmm.cu: the segment length every plan is built with
+// Reads the deferred id-validation flag (call only where the stream is synchronised anyway).
+void ensure_valid_ids(DGLB200Graph* g, cudaStream_t s);
 void exclusive_scan_i32(int32_t* data, int64_t n, cudaStream_t s);
 void fill_f32(float* p, int64_t n, float v, cudaStream_t s);
 

@@ -80,6 +80,38 @@ __global__ void narrow_kernel(const int64_t* __restrict__ in, int32_t* __restric
   for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride)
     out[k] = (int32_t)in[k];
 }
+// int64 -> int32 with a range check against [0, hi): an id outside (negative, >= hi, or with
+// high bits set) is replaced by 0 and reported through *bad, so that nothing downstream
+// (count_keys atomics, radix scatter, gathers) can leave its arrays.
+template <typename T>
+__global__ void narrow_checked_kernel(const T* __restrict__ in, int32_t* __restrict__ out,
+                                      int64_t n, int64_t hi, int32_t* __restrict__ bad) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  bool any = false;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride) {
+    const int64_t v = (int64_t)in[k];
+    const bool ok = v >= 0 && v < hi;
+    out[k] = ok ? (int32_t)v : 0;
+    any |= !ok;
+  }
+  if (any) atomicOr(bad, 1);
+}
+
+// indptr of a caller-provided CSR: starts at 0, ends at nnz, never decreases
+__global__ void check_indptr_kernel(const int32_t* __restrict__ indptr, int64_t n_rows,
+                                    int64_t nnz, int32_t* __restrict__ bad) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  bool any = false;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k <= n_rows; k += stride) {
+    const int32_t v = indptr[k];
+    if (k == 0 && v != 0) any = true;
+    if (k == n_rows && v != nnz) any = true;
+    if (k < n_rows && indptr[k + 1] < v) any = true;
+    if (v < 0 || v > nnz) any = true;
+  }
+  if (any) atomicOr(bad, 1);
+}
+
 static void narrow(const int64_t* in, int32_t* out, int64_t n, cudaStream_t s) {
   if (n <= 0) return;
   int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
@@ -523,6 +555,7 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
       B200_CUDA(cudaMemcpyAsync(&tot[0], nseg.as<int32_t>() + c.n_rows, 4, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaMemcpyAsync(&tot[1], heavy.as<int32_t>() + c.n_rows, 4, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaStreamSynchronize(s));
+      ensure_valid_ids(g, s);
       c.n_seg = tot[0];
       c.n_heavy = tot[1];
       c.n_long = tot[3];
@@ -715,6 +748,42 @@ static bool is_device_ptr(const void* p) {
 }
 
 // copies `n` index values (int32 or int64, host or device) into a device int32 array
+// upload_idx with the range check of narrow_checked_kernel (ids must lie in [0, hi))
+static void upload_ids_checked(const void* src, int bits, int64_t n, int64_t hi, int32_t* dst,
+                               int32_t* bad, cudaStream_t s) {
+  if (n <= 0) return;
+  const bool dev = is_device_ptr(src);
+  const size_t bytes = (size_t)n * (bits / 8);
+  Scratch tmp;
+  const void* in = src;
+  if (!dev) {
+    tmp.alloc(bytes, s);
+    B200_CUDA(cudaMemcpyAsync(tmp.ptr, src, bytes, cudaMemcpyHostToDevice, s));
+    in = tmp.ptr;
+  }
+  const int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  if (bits == 64)
+    narrow_checked_kernel<int64_t><<<blocks, 256, 0, s>>>(static_cast<const int64_t*>(in), dst, n, hi, bad);
+  else
+    narrow_checked_kernel<int32_t><<<blocks, 256, 0, s>>>(static_cast<const int32_t*>(in), dst, n, hi, bad);
+  note_kernel(nullptr, 1);
+  // the host buffer must stay valid until the copy has been consumed
+  if (!dev) B200_CUDA(cudaStreamSynchronize(s));
+}
+
+static void read_bad_flag(DGLB200Graph* g, cudaStream_t s, const char* what) {
+  int32_t h = 0;
+  B200_CUDA(cudaMemcpyAsync(&h, g->bad_ids, 4, cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  g->ids_checked = true;
+  B200_CHECK(h == 0, what);
+}
+
+void ensure_valid_ids(DGLB200Graph* g, cudaStream_t s) {
+  if (g->ids_checked || !g->bad_ids) return;
+  read_bad_flag(g, s, "graph was built from node ids outside [0, num_src) x [0, num_dst)");
+}
+
 static void upload_idx(const void* src, int bits, int64_t n, int32_t* dst, cudaStream_t s) {
   if (n <= 0) return;
   const bool dev = is_device_ptr(src);
@@ -776,8 +845,15 @@ int DGLB200GraphCreateFromCOO(int64_t num_src, int64_t num_dst, int64_t num_edge
     alloc_csr(g->out, num_src, num_dst, num_edges, s);
     const int64_t e = num_edges;
     Scratch s32((size_t)std::max<int64_t>(e, 1) * 4, s), d32((size_t)std::max<int64_t>(e, 1) * 4, s);
-    upload_idx(src, 64, e, s32.as<int32_t>(), s);
-    upload_idx(dst, 64, e, d32.as<int32_t>(), s);
+    B200_CUDA(pool_alloc(&g->bad_ids, 4, s));
+    fill_i32(g->bad_ids, 1, 0, s);
+    upload_ids_checked(src, 64, e, num_src, s32.as<int32_t>(), g->bad_ids, s);
+    upload_ids_checked(dst, 64, e, num_dst, d32.as<int32_t>(), g->bad_ids, s);
+    g->ids_checked = false;
+    // host arrays: the uploads synchronised already, so the verdict costs nothing extra;
+    // device arrays: deferred to the handle's first synchronisation point (ensure_valid_ids)
+    if (e > 0 && !is_device_ptr(src))
+      read_bad_flag(g, s, "DGLB200GraphCreateFromCOO: node id outside [0, num_src) x [0, num_dst)");
     // in-CSR = COOToCSR keyed by dst (immutable_graph.cc:407-421); keep the row expansion,
     // the transpose needs it.
     B200_CUDA(pool_alloc(&g->in.row, (size_t)std::max<int64_t>(e, 1) * 4, s));
@@ -795,6 +871,7 @@ int DGLB200GraphCreateFromCOO(int64_t num_src, int64_t num_dst, int64_t num_edge
     free_csr(g->in_s, s);
     free_csr(g->in, s);
     free_csr(g->out, s);
+    pool_free(g->bad_ids, s);
     delete g;
     throw;
   }
@@ -822,12 +899,21 @@ int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edge
   try {
     alloc_csr(g->in, num_dst, num_src, num_edges, s);
     alloc_csr(g->out, num_src, num_dst, num_edges, s);
-    upload_idx(in_indptr, idx_bits, num_dst + 1, g->in.indptr, s);
-    upload_idx(in_indices, idx_bits, num_edges, g->in.indices, s);
-    upload_idx(in_eids, idx_bits, num_edges, g->in.eids, s);
-    upload_idx(out_indptr, idx_bits, num_src + 1, g->out.indptr, s);
-    upload_idx(out_indices, idx_bits, num_edges, g->out.indices, s);
-    upload_idx(out_eids, idx_bits, num_edges, g->out.eids, s);
+    B200_CUDA(pool_alloc(&g->bad_ids, 4, s));
+    fill_i32(g->bad_ids, 1, 0, s);
+    // every array is validated while it is narrowed: indptr values in [0, E] (and monotone,
+    // 0 .. E), column ids in [0, n_cols), edge ids in [0, E)
+    upload_ids_checked(in_indptr, idx_bits, num_dst + 1, num_edges + 1, g->in.indptr, g->bad_ids, s);
+    upload_ids_checked(in_indices, idx_bits, num_edges, num_src, g->in.indices, g->bad_ids, s);
+    upload_ids_checked(in_eids, idx_bits, num_edges, num_edges, g->in.eids, g->bad_ids, s);
+    upload_ids_checked(out_indptr, idx_bits, num_src + 1, num_edges + 1, g->out.indptr, g->bad_ids, s);
+    upload_ids_checked(out_indices, idx_bits, num_edges, num_dst, g->out.indices, g->bad_ids, s);
+    upload_ids_checked(out_eids, idx_bits, num_edges, num_edges, g->out.eids, g->bad_ids, s);
+    check_indptr_kernel<<<ceil_div(num_dst + 1, 256), 256, 0, s>>>(g->in.indptr, num_dst, num_edges, g->bad_ids);
+    check_indptr_kernel<<<ceil_div(num_src + 1, 256), 256, 0, s>>>(g->out.indptr, num_src, num_edges, g->bad_ids);
+    note_kernel(nullptr, 2);
+    g->ids_checked = false;
+    read_bad_flag(g, s, "DGLB200GraphCreateFromCSR: indptr / indices / edge ids out of range");
     build_in_sorted(g, s);
     B200_CUDA(cudaStreamSynchronize(s));  // host buffers may be released by the caller now
   } catch (...) {
@@ -835,6 +921,7 @@ int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edge
     free_csr(g->in_s, s);
     free_csr(g->in, s);
     free_csr(g->out, s);
+    pool_free(g->bad_ids, s);
     delete g;
     throw;
   }
@@ -851,6 +938,7 @@ int DGLB200GraphFree(DGLB200GraphHandle g) {
     free_typed(g->ty);
     pool_free(g->coo_src, s);
     pool_free(g->coo_dst, s);
+    pool_free(g->bad_ids, s);
     g->in_s.indptr = nullptr;
     free_csr(g->in_s);
     free_csr(g->in);
@@ -899,7 +987,10 @@ int DGLB200GraphCopyCSR(DGLB200GraphHandle g, int transpose, int32_t* indptr, in
   copy(indptr, c.indptr, c.n_rows + 1);
   copy(indices, c.indices, g->num_edges);
   copy(eids, c.eids, g->num_edges);
-  if (host) B200_CUDA(cudaStreamSynchronize(s));
+  if (host) {
+    B200_CUDA(cudaStreamSynchronize(s));
+    ensure_valid_ids(g, s);
+  }
   API_END();
 }
 
@@ -927,6 +1018,86 @@ int DGLB200GraphSetEdgeTypes(DGLB200GraphHandle g, const void* etypes, int idx_b
   API_END();
 }
 
+// (position p of the typed in-CSR) -> COO by edge id: src[eid] = ids[p], dst[eid] = row(p),
+// type[eid] = types[p]; an edge id outside [0, E) is reported and skipped
+__global__ void typed_csr_to_coo_kernel(const int32_t* __restrict__ row,
+                                        const int32_t* __restrict__ ids,
+                                        const int32_t* __restrict__ eids,
+                                        const int32_t* __restrict__ types, int64_t e,
+                                        int64_t* __restrict__ src, int64_t* __restrict__ dst,
+                                        int32_t* __restrict__ type_by_eid,
+                                        int32_t* __restrict__ max_type, int32_t* __restrict__ bad) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int32_t mx = 0;
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < e; p += stride) {
+    const int32_t id = eids[p];
+    if (id < 0 || id >= e) {
+      atomicOr(bad, 1);
+      continue;
+    }
+    src[id] = ids[p];
+    dst[id] = row[p];
+    const int32_t t = types[p];
+    type_by_eid[id] = t;
+    mx = max(mx, t);
+  }
+  atomicMax(max_type, mx);
+}
+
+int DGLB200GraphCreateFromTypedCSR(int64_t num_nodes, int64_t num_edges, int idx_bits,
+                                   const void* indptr, const void* ids, const void* eids,
+                                   const void* types, int64_t num_types, int device, void* stream,
+                                   DGLB200GraphHandle* out) {
+  API_BEGIN();
+  B200_CHECK(out != nullptr, "DGLB200GraphCreateFromTypedCSR: out handle is NULL");
+  B200_CHECK(idx_bits == 32 || idx_bits == 64, "idx_bits must be 32 or 64");
+  B200_CHECK(num_nodes >= 0 && num_edges >= 0 && num_nodes < (1ll << 31) - 1 &&
+                 num_edges < (1ll << 31) - 1, "graph size out of the int32 range");
+  B200_CHECK(num_edges == 0 || (indptr && ids && eids && types), "NULL typed CSR array");
+  ensure_device(device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t e = num_edges;
+  const size_t eb = (size_t)std::max<int64_t>(e, 1);
+  Scratch ip((size_t)(num_nodes + 1) * 4, s), row(eb * 4, s), id32(eb * 4, s), eid32(eb * 4, s),
+      ty32(eb * 4, s), src(eb * 8, s), dst(eb * 8, s), tye(eb * 4, s), flags(8, s);
+  fill_i32(flags.as<int32_t>(), 2, 0, s);
+  int32_t* bad = flags.as<int32_t>();
+  upload_ids_checked(indptr, idx_bits, num_nodes + 1, e + 1, ip.as<int32_t>(), bad, s);
+  check_indptr_kernel<<<ceil_div(num_nodes + 1, 256), 256, 0, s>>>(ip.as<int32_t>(), num_nodes, e, bad);
+  note_kernel(nullptr, 1);
+  upload_ids_checked(ids, idx_bits, e, num_nodes, id32.as<int32_t>(), bad, s);
+  upload_ids_checked(eids, idx_bits, e, e, eid32.as<int32_t>(), bad, s);
+  upload_ids_checked(types, idx_bits, e, (1ll << 31) - 1, ty32.as<int32_t>(), bad, s);
+  int32_t h[2] = {0, 0};
+  B200_CUDA(cudaMemcpyAsync(h, flags.ptr, 4, cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  B200_CHECK(h[0] == 0, "DGLB200GraphCreateFromTypedCSR: indptr / ids / edge ids / types out of range");
+  if (e > 0) {
+    expand_rows(ip.as<int32_t>(), num_nodes, row.as<int32_t>(), s);
+    const int blocks = (int)std::min<int64_t>((e + 255) / 256, 148 * 16);
+    typed_csr_to_coo_kernel<<<blocks, 256, 0, s>>>(
+        row.as<int32_t>(), id32.as<int32_t>(), eid32.as<int32_t>(), ty32.as<int32_t>(), e,
+        src.as<int64_t>(), dst.as<int64_t>(), tye.as<int32_t>(), flags.as<int32_t>() + 1, bad);
+    note_kernel(nullptr, 1);
+  }
+  B200_CUDA(cudaMemcpyAsync(h, flags.ptr, 8, cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  B200_CHECK(h[0] == 0, "DGLB200GraphCreateFromTypedCSR: edge ids are not a permutation of [0, E)");
+  if (num_types <= 0) num_types = (int64_t)h[1] + 1;
+  B200_CHECK(h[1] < num_types, "DGLB200GraphCreateFromTypedCSR: edge type >= num_types");
+  DGLB200GraphHandle g = nullptr;
+  B200_CHECK(DGLB200GraphCreateFromCOO(num_nodes, num_nodes, e, src.as<int64_t>(),
+                                       dst.as<int64_t>(), device, stream, &g) == 0,
+             std::string(DGLB200GetLastError()));
+  if (DGLB200GraphSetEdgeTypes(g, tye.ptr, 32, num_types, stream) != 0) {
+    const std::string msg = DGLB200GetLastError();
+    DGLB200GraphFree(g);
+    throw ApiError{msg};
+  }
+  *out = g;
+  API_END();
+}
+
 int DGLB200GraphCopyCsrSortedByEdgeType(DGLB200GraphHandle g, int transpose, int32_t* indptr,
                                         int32_t* ids, int32_t* eids, int32_t* types,
                                         void* stream) {
@@ -949,7 +1120,10 @@ int DGLB200GraphCopyCsrSortedByEdgeType(DGLB200GraphHandle g, int transpose, int
   copy(ids, t.ids, g->num_edges);
   copy(eids, t.eids, g->num_edges);
   copy(types, t.types, g->num_edges);
-  if (host) B200_CUDA(cudaStreamSynchronize(s));
+  if (host) {
+    B200_CUDA(cudaStreamSynchronize(s));
+    ensure_valid_ids(g, s);
+  }
   API_END();
 }
 
@@ -973,6 +1147,7 @@ int DGLB200GraphDegrees(DGLB200GraphHandle g, int which, int64_t* out, void* str
     if (!dev)
       B200_CUDA(cudaMemcpyAsync(out, d, (size_t)c.n_rows * 8, cudaMemcpyDeviceToHost, s));
     B200_CUDA(cudaStreamSynchronize(s));
+    ensure_valid_ids(g, s);
   }
   API_END();
 }

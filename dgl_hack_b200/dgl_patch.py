@@ -1,87 +1,112 @@
-"""Reference-side binding: route DGL 0.4's kernel wrappers to the B200 library.
+"""Reference-side binding: make DGL 0.4's own Python stack run on the B200 library.
 
-`install()` rebinds the functions of the reference's `python/dgl/kernel.py` (the module every
-backend calls, `python/dgl/backend/pytorch/tensor.py:298-360, 524-562`) to dgl_hack_b200.kernel,
-so `update_all / apply_edges / edge_softmax / GraphConv / SAGEConv / GATConv / RelGraphConv` run
-on the sm_100a kernels unchanged. Needs the reference's `dgl` package importable (it is not
-vendored here); nothing in this package depends on this module.
+`install()` registers the library's DGLPackedCFunc shims (csrc/packed.cu, DGLB200RegisterInto)
+into the global function table of the reference's libdgl with override = 1
+(include/dgl/runtime/c_runtime_api.h:319-346), under the names python/dgl/kernel.py binds with
+`_init_api("dgl.kernel")` (kernel.py:438). From then on the UNMODIFIED reference code path --
+`DGLGraph.update_all / apply_edges`, the scheduler IR, `backend/pytorch/tensor.py`'s autograd
+`BinaryReduce / CopyReduce`, `dgl.nn.pytorch.{GraphConv, SAGEConv, GATConv, RelGraphConv}`,
+`edge_softmax` -- calls the sm_100a kernels whenever its tensors are CUDA tensors, and the
+reference's own CPU kernels otherwise (the shims forward those calls to the functions that were
+registered before). No function of the reference's Python package is replaced.
 
-What changes hands at the boundary:
-  * tensors: the reference passes `dgl.ndarray.NDArray` built zero-copy from torch via DLPack
-    (`zerocopy_to_dgl_ndarray`, tensor.py:283). We go back to the torch tensor with the same
-    zero-copy hop (`to_dlpack` -> `torch.utils.dlpack.from_dlpack`).
-  * graph: the reference passes its C++ graph index handle. Its two CSRs are read once per
-    (graph, device) through the public PackedFunc `_CAPI_DGLGraphGetAdj(g, transpose, "csr")`
-    (src/graph/graph_apis.cc:285-292; `_CAPI_DGLHeteroGetAdj` for unit graphs) and wrapped with
-    GraphIndex.from_csr; the result is cached on the Python graph-index object.
+Needs the reference's `dgl` package importable; nothing else in this package depends on this
+module.
+
+What crosses the boundary:
+  * tensors: `dgl.ndarray.NDArray` containers built zero-copy from torch through DLPack
+    (`zerocopy_to_dgl_ndarray`, backend/pytorch/tensor.py:283); the shims read the DLTensor header.
+  * graph: the C++ graph object handle; the shims fetch its CSR arrays once per (graph, device)
+    with the public PackedFunc `_CAPI_DGLGraphGetAdj(g, transpose, "csr")`
+    (src/graph/graph_apis.cc:285-292; `_CAPI_DGLHeteroGetAdj` for unit graphs) and keep the
+    device copy (DGLB200GraphCreateFromCSR), replacing ImmutableGraph::CopyTo
+    (src/graph/immutable_graph.cc:548-559).
+
+One accommodation, and only when the loaded libdgl was built WITHOUT CUDA (the build available
+in this environment; a CUDA build needs none): `GraphIndex.get_immutable_gidx(gpu ctx)` /
+`HeteroGraphIndex.get_unitgraph(gpu ctx)` would ask that library to copy the graph to a device it
+has no API for, so they hand out the host index instead -- the kernels only read the CSR arrays.
 """
-import torch
-from torch.utils import dlpack as _dlpack
+import ctypes
+import os
+import sys
 
-from . import kernel as K
-from .graph_index import GraphIndex
+from ._lib import LIB, check_call
 
-_CACHE_ATTR = "_b200_graph_index"
-
-
-def _to_torch(nd_or_tensor):
-    if nd_or_tensor is None or isinstance(nd_or_tensor, torch.Tensor):
-        return nd_or_tensor
-    if nd_or_tensor.shape[0] == 0 and len(nd_or_tensor.shape) == 1:
-        return None  # nd.null()
-    return _dlpack.from_dlpack(nd_or_tensor.to_dlpack())
+_state = {"installed": False, "cpu_only_libdgl": None}
 
 
-def reference_csrs(gidx):
-    """(num_src, num_dst, in_csr, out_csr) of a reference graph index, as numpy int arrays."""
-    import dgl  # noqa: F401
+def _find_libdgl(path=None):
+    """dlopen handle of the reference library: the one `dgl` loaded, else `path`, else
+    $DGL_LIBRARY_PATH/libdgl.so (the lookup of python/dgl/_ffi/libinfo.py)."""
+    if "dgl._ffi.base" in sys.modules:
+        return sys.modules["dgl._ffi.base"]._LIB._handle
+    if path is None:
+        path = os.path.join(os.environ.get("DGL_LIBRARY_PATH", ""), "libdgl.so")
+    if not os.path.exists(path):
+        raise FileNotFoundError("libdgl.so not found (pass its path or set DGL_LIBRARY_PATH)")
+    # the same file dlopen'ed again by `import dgl` yields the same library instance
+    return ctypes.CDLL(path, ctypes.RTLD_GLOBAL)._handle
+
+
+def register(libdgl=None):
+    """Registers the PackedFunc shims; `libdgl` = path, ctypes.CDLL, dlopen handle or None.
+    Call BEFORE `import dgl` (python/dgl/kernel.py copies the global functions when it is
+    imported), or use install(), which also rebinds an already imported dgl.kernel."""
+    if isinstance(libdgl, ctypes.CDLL):
+        handle = libdgl._handle
+    elif isinstance(libdgl, int):
+        handle = libdgl
+    else:
+        handle = _find_libdgl(libdgl)
+    check_call(LIB.DGLB200RegisterInto(ctypes.c_void_p(handle)))
+    return [LIB.DGLB200PackedFuncName(i).decode() for i in range(LIB.DGLB200PackedFuncCount())]
+
+
+def _libdgl_has_cuda():
+    from dgl._ffi.function import get_global_func
+    return get_global_func("device_api.gpu", allow_missing=True) is not None
+
+
+def _route_host_index():
+    """CPU-only libdgl: GPU contexts get the host graph index (see the module docstring)."""
     from dgl import graph_index, heterograph_index
+    from dgl import ndarray as nd
 
-    def adj(rst):
-        return tuple(rst(i).asnumpy() for i in range(3))
-
-    if isinstance(gidx, graph_index.GraphIndex):
-        n = gidx.number_of_nodes()
-        return (n, n, adj(graph_index._CAPI_DGLGraphGetAdj(gidx, False, "csr")),
-                adj(graph_index._CAPI_DGLGraphGetAdj(gidx, True, "csr")))
-    ns, nd = gidx.number_of_nodes(0), gidx.number_of_nodes(1)
-    return (ns, nd, adj(heterograph_index._CAPI_DGLHeteroGetAdj(gidx, 0, False, "csr")),
-            adj(heterograph_index._CAPI_DGLHeteroGetAdj(gidx, 0, True, "csr")))
-
-
-def to_b200_graph(gidx, device):
-    cache = gidx.__dict__.setdefault(_CACHE_ATTR, {})
-    key = str(device)
-    if key not in cache:
-        ns, nd, in_csr, out_csr = reference_csrs(gidx)
-        cache[key] = GraphIndex.from_csr(ns, nd, in_csr, out_csr, device)
-    return cache[key]
+    def host_ctx(fn):
+        def get(self, ctx):
+            if ctx.device_type != 1:       # not kDLCPU
+                ctx = nd.cpu()
+            return fn(self, ctx)
+        get.__wrapped__ = fn
+        return get
+    for cls, name in ((graph_index.GraphIndex, "get_immutable_gidx"),
+                      (heterograph_index.HeteroGraphIndex, "get_unitgraph")):
+        fn = getattr(cls, name, None)
+        if fn is not None and not hasattr(fn, "__wrapped__"):
+            setattr(cls, name, host_ctx(fn))
 
 
-def _wrap(fn, graph_pos, tensor_pos):
-    def call(*args):
-        args = list(args)
-        tensors = [_to_torch(args[i]) for i in tensor_pos if i < len(args)]
-        dev = next(t.device for t in tensors if t is not None)
-        for i, t in zip(tensor_pos, tensors):
-            args[i] = t
-        args[graph_pos] = to_b200_graph(args[graph_pos], dev)
-        return fn(*args)
-    return call
+def install(libdgl=None):
+    """register() + rebinding of an already imported `dgl.kernel` (a re-run of the reference's
+    own `_init_api("dgl.kernel")`) + the host-index routing for a CPU-only libdgl. Returns the
+    registered global names."""
+    names = register(libdgl)
+    import dgl  # noqa: F401
+    from dgl._ffi.function import _init_api
+    _init_api("dgl.kernel")
+    if _state["cpu_only_libdgl"] is None:
+        _state["cpu_only_libdgl"] = not _libdgl_has_cuda()
+    if _state["cpu_only_libdgl"]:
+        _route_host_index()
+    _state["installed"] = True
+    return names
 
 
-def install():
-    """Rebind dgl.kernel.* (and the alias the torch backend imported as `K`)."""
-    import dgl.kernel as ref_kernel
-    table = {
-        "binary_op_reduce": _wrap(K.binary_op_reduce, 2, range(5, 11)),
-        "backward_lhs_binary_op_reduce": _wrap(K.backward_lhs_binary_op_reduce, 2, range(5, 13)),
-        "backward_rhs_binary_op_reduce": _wrap(K.backward_rhs_binary_op_reduce, 2, range(5, 13)),
-        "copy_reduce": _wrap(K.copy_reduce, 1, range(3, 7)),
-        "backward_copy_reduce": _wrap(K.backward_copy_reduce, 1, range(3, 9)),
-        "infer_binary_feature_shape":
-            lambda op, lhs, rhs: K.infer_binary_feature_shape(op, _to_torch(lhs), _to_torch(rhs)),
-    }
-    for name, fn in table.items():
-        setattr(ref_kernel, name, fn)
-    return sorted(table)
+def set_stream(stream=None):
+    """The CUDA stream the shims launch on (thread-local; the reference's DGLSetStream role).
+    None = torch's current stream."""
+    import torch
+    if stream is None:
+        stream = torch.cuda.current_stream()
+    check_call(LIB.DGLB200SetStream(ctypes.c_void_p(stream.cuda_stream)))

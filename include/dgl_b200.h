@@ -221,6 +221,16 @@ int DGLB200GraphCopyCsrSortedByEdgeType(DGLB200GraphHandle graph, int transpose,
                                         int32_t* ids, int32_t* eids, int32_t* types,
                                         void* stream);
 
+/* The same typed graph rebuilt from the four arrays the reference's
+ * graph_index._CAPI_DGLGraphGetCsrSortedByEdgeType(g, transpose = 0) returns
+ * (src/graph/graph_apis.cc:295-301): in-edge ranges [N+1], source ids [E], edge ids [E], edge
+ * types [E]; int32 or int64, host or device. num_types <= 0: max type + 1. This is how the
+ * PackedFunc shims of the RGCN ops obtain the graph from a reference graph object. */
+int DGLB200GraphCreateFromTypedCSR(int64_t num_nodes, int64_t num_edges, int idx_bits,
+                                   const void* indptr, const void* ids, const void* eids,
+                                   const void* types, int64_t num_types, int device, void* stream,
+                                   DGLB200GraphHandle* out);
+
 /* kernel._CAPI_DGLRgcnLayer0(graph, weight, norm, ret)  (src/kernel/binary_reduce.cc:412-420;
  * kernel src/kernel/cuda/binary_reduce_impl.cu:913-975). weight [R, N, F] (the embedding of a
  * one-hot input), norm [E,1] by edge id, ret [N, F]:
@@ -398,6 +408,46 @@ int DGLB200PeerFree(void* ptr);
 int DGLB200HaloPush(const float* x, int64_t D, int n_peers, void* const* peer, const int64_t* beg,
                     const int64_t* dst_row, const int32_t* rows, int first_peer, int device,
                     void* stream);
+
+/* ---- the PackedFunc face: drop-in registration into a loaded libdgl ----
+ * DGLValue (include/dgl/runtime/c_runtime_api.h:122-129; DGLType / DGLContext members are
+ * 8 bytes as well) and DGLPackedCFunc (:301-306). */
+typedef union {
+  int64_t v_int64;
+  double v_float64;
+  void* v_handle;
+  const char* v_str;
+} DGLB200Value;
+typedef int (*DGLB200PackedCFunc)(DGLB200Value* args, int* type_codes, int num_args, void* ret,
+                                  void* resource_handle);
+
+/* Registers DGLPackedCFunc shims for the reference's 12 kernel globals --
+ * kernel._CAPI_DGLKernel{InferBinaryFeatureShape, BinaryOpReduce, BackwardLhsBinaryOpReduce,
+ * BackwardRhsBinaryOpReduce, CopyReduce, BackwardCopyReduce}, kernel._CAPI_DGLFusedGatKernel,
+ * kernel._CAPI_DGLKernelBackwardFusedGat, kernel._CAPI_DGLRgcnLayer{0,0Backward,1,1Backward}
+ * (src/kernel/binary_reduce.cc:281, 357, 380, 412-450, 502, 529, 600, 649, 697) -- into the
+ * global function table of the libdgl whose dlopen() handle is passed, with override = 1
+ * (DGLFuncCreateFromCFunc / DGLFuncRegisterGlobal, c_runtime_api.h:319-346). Afterwards the
+ * unmodified python/dgl/kernel.py (bound by _init_api("dgl.kernel"), kernel.py:438) runs on this
+ * library whenever the tensors are on a CUDA device; calls with CPU tensors are forwarded to
+ * the functions that were registered before. Positional arguments are decoded exactly as the
+ * reference reads args[i]: kStr, kDLInt, kDLFloat, kArrayHandle / kNDArrayContainer (a DLTensor*
+ * either way), kNull, kObjectHandle for the graph, whose CSR arrays are read through
+ * graph_index._CAPI_DGLGraphGetAdj / heterograph_index._CAPI_DGLHeteroGetAdj and cached per
+ * (graph, device). Kernels run on the stream set by DGLB200SetStream (thread-local; default =
+ * the legacy default stream, as the reference's CUDAThreadEntry, cuda_common.h:51-66).
+ * Registering twice into the same process is a no-op. */
+int DGLB200RegisterInto(void* libdgl_handle);
+int DGLB200SetStream(void* stream);
+/* The shims themselves, for hosts that register them on their own. */
+int DGLB200PackedFuncCount(void);
+const char* DGLB200PackedFuncName(int i);
+DGLB200PackedCFunc DGLB200PackedFuncGet(int i);
+/* out[0] = shim invocations, out[1] = of those forwarded to the previously registered (CPU)
+ * function, out[2] = device graph indices built from reference graph objects. */
+int DGLB200PackedStats(int64_t out[3]);
+/* Drops every cached (reference graph -> device index) entry. */
+int DGLB200PackedCacheClear(void);
 
 #ifdef __cplusplus
 }

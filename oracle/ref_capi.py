@@ -73,6 +73,32 @@ class RefArray(object):
             _check(lib().DGLArrayCopyFromBytes(self.handle, arr.ctypes.data_as(ctypes.c_void_p),
                                                ctypes.c_size_t(arr.nbytes)))
 
+    @classmethod
+    def from_dlpack(cls, tensor):
+        """A reference NDArray sharing a torch tensor's memory (CPU or CUDA), the way the
+        reference's torch backend hands tensors to the kernels (`zerocopy_to_dgl_ndarray` =
+        nd.from_dlpack(to_dlpack(x)), python/dgl/backend/pytorch/tensor.py:283;
+        python/dgl/_ffi/_ctypes/ndarray.py `_from_dlpack` -> DGLArrayFromDLPack)."""
+        from torch.utils import dlpack
+        tensor = tensor.contiguous()
+        cap = dlpack.to_dlpack(tensor)
+        api = ctypes.pythonapi
+        api.PyCapsule_GetPointer.restype = ctypes.c_void_p
+        api.PyCapsule_GetPointer.argtypes = [ctypes.py_object, ctypes.c_char_p]
+        api.PyCapsule_SetName.argtypes = [ctypes.py_object, ctypes.c_char_p]
+        api.PyCapsule_SetDestructor.argtypes = [ctypes.py_object, ctypes.c_void_p]
+        ptr = api.PyCapsule_GetPointer(cap, b"dltensor")
+        self = cls.__new__(cls)
+        self.shape = tuple(tensor.shape)
+        self.dtype = None
+        self.handle = ctypes.c_void_p()
+        _check(lib().DGLArrayFromDLPack(ctypes.c_void_p(ptr), ctypes.byref(self.handle)))
+        # the NDArray now owns the managed tensor (its deleter releases torch's reference)
+        api.PyCapsule_SetName(cap, _USED)
+        api.PyCapsule_SetDestructor(cap, None)
+        self._keep = (tensor, cap)
+        return self
+
     def numpy(self):
         out = np.empty(self.shape, self.dtype)
         if out.nbytes:
@@ -88,7 +114,14 @@ class RefArray(object):
             pass
 
 
+_USED = ctypes.create_string_buffer(b"used_dltensor")   # capsule names are borrowed pointers
 _funcs = {}
+
+
+def forget_functions():
+    """Drops the cached global-function handles (DGLFuncGetGlobal returns a COPY of the registered
+    function, so a handle looked up before an override keeps calling the old body)."""
+    _funcs.clear()
 
 
 def call(name, *args):
@@ -121,6 +154,23 @@ def call(name, *args):
     ret, rcode = _Value(), ctypes.c_int()
     _check(lib().DGLFuncCall(_funcs[name], vals, codes, n, ctypes.byref(ret), ctypes.byref(rcode)))
     return ret, rcode.value
+
+
+def returned_int64_array(ret, code):
+    """A 1-D int64 CPU NDArray returned by a PackedFunc -> python list (and release it)."""
+    assert code == K_NDARRAY, code
+
+    class _DL(ctypes.Structure):
+        _fields_ = [("data", ctypes.c_void_p), ("device_type", ctypes.c_int32),
+                    ("device_id", ctypes.c_int32), ("ndim", ctypes.c_int32),
+                    ("code", ctypes.c_uint8), ("bits", ctypes.c_uint8), ("lanes", ctypes.c_uint16),
+                    ("shape", ctypes.POINTER(ctypes.c_int64)),
+                    ("strides", ctypes.POINTER(ctypes.c_int64)), ("byte_offset", ctypes.c_uint64)]
+    t = ctypes.cast(ret.v_handle, ctypes.POINTER(_DL)).contents
+    n = t.shape[0] if t.ndim else 0
+    vals = list((ctypes.c_int64 * n).from_address(t.data + t.byte_offset)) if n else []
+    lib().DGLArrayFree(ctypes.c_void_p(ret.v_handle))
+    return vals
 
 
 class RefObject(object):

@@ -110,3 +110,42 @@ def test_device_resident_coo_input():
     og = O.Graph(1000, 1000, src, dst)
     for a, b in zip(gg.in_csr + gg.out_csr, og.in_csr + og.out_csr):
         assert np.array_equal(a.astype(np.int64), b)
+
+
+@pytest.mark.parametrize("bad", [("src", 1000), ("dst", -1), ("src", 2 ** 31 + 5), ("dst", 2 ** 40)])
+@pytest.mark.parametrize("on_device", [False, True])
+def test_out_of_range_ids_are_rejected(bad, on_device):
+    """Ids outside [0, num_src) x [0, num_dst) (negative, too large, high bits set) must be an
+    error, never an out-of-bounds device write: host arrays fail in the constructor, device
+    arrays at the handle's first synchronisation point (no extra sync on the sampling path)."""
+    import torch
+    import dgl_hack_b200 as B
+    from dgl_hack_b200._lib import DGLError
+    src, dst = cases.powerlaw_graph(1000, 1000, 30000, 0.5, 3)
+    src, dst = src.copy(), dst.copy()
+    (src if bad[0] == "src" else dst)[123] = bad[1]
+    s, d = torch.from_numpy(src), torch.from_numpy(dst)
+    if on_device:
+        s, d = s.cuda(), d.cuda()
+        g = B.GraphIndex.from_coo(1000, 1000, s, d)
+        with pytest.raises(DGLError):
+            g.in_degrees()
+    else:
+        with pytest.raises(DGLError):
+            B.GraphIndex.from_coo(1000, 1000, s, d)
+    # the library is still healthy afterwards
+    ok = B.GraphIndex.from_coo(10, 10, torch.arange(10), torch.arange(10))
+    assert int(ok.in_degrees().sum()) == 10
+
+
+def test_bad_csr_arrays_are_rejected():
+    import dgl_hack_b200 as B
+    from dgl_hack_b200._lib import DGLError
+    from oracle import oracle as O
+    src, dst = cases.powerlaw_graph(50, 60, 500, 0.5, 4)
+    og = O.Graph(50, 60, src, dst)
+    for which, pos, val in ((1, 7, 50), (0, 3, 10 ** 6), (2, 0, -2), (3, 50, 499)):
+        arrs = [a.copy() for a in og.in_csr + og.out_csr]
+        arrs[which][pos] = val
+        with pytest.raises(DGLError):
+            B.GraphIndex.from_csr(50, 60, tuple(arrs[:3]), tuple(arrs[3:]))
