@@ -121,6 +121,10 @@ SYMBOLS = {
     "DGLB200GraphCreateFromTypedCSR": (_c.c_int, [_c.c_int64, _c.c_int64, _c.c_int, _c.c_void_p,
                                                   _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int64,
                                                   _c.c_int, _c.c_void_p, _c.POINTER(GraphHandle)]),
+    "DGLB200GraphCreateRelationSegments": (_c.c_int, [GraphHandle, _c.c_void_p,
+                                                      _c.POINTER(GraphHandle)]),
+    "DGLB200GraphCopyRelationSegments": (_c.c_int, [GraphHandle, _c.c_void_p, _c.c_void_p,
+                                                    _c.c_void_p]),
     "DGLB200RegisterInto": (_c.c_int, [_c.c_void_p]),
     "DGLB200SetStream": (_c.c_int, [_c.c_void_p]),
     "DGLB200PackedFuncCount": (_c.c_int, []),

@@ -8,6 +8,8 @@
 #include <sstream>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/dgl_b200.h"
 #include "common.cuh"
 
@@ -282,7 +284,14 @@ static void dispatch(const KernelCall& c) {
 
 using namespace b200;
 
-#define API_BEGIN() try {
+// Every kernel entry point is an NVTX range named after the C function (nvtx3 is header-only and
+// a no-op costing one pointer test unless a tool -- nsys, ncu --nvtx -- is attached), so a
+// profile of a training step shows the reference-level call each kernel belongs to.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+#define API_BEGIN() NvtxRange nvtx_range_(__func__); try {
 #define API_END()                                     \
   }                                                   \
   catch (const ::b200::ApiError& e) {                 \

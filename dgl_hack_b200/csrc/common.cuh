@@ -231,6 +231,9 @@ struct DGLB200Graph {
   // CopyCSR, Degrees). Host arrays are checked before the constructor returns.
   int32_t* bad_ids = nullptr;
   bool ids_checked = true;
+  // relation-segment graphs only (DGLB200GraphCreateRelationSegments): destination node and
+  // relation of every segment (= destination row of this graph)
+  int32_t *seg_dst = nullptr, *seg_type = nullptr;
 };
 
 namespace b200 {

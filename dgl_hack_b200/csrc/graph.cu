@@ -939,6 +939,8 @@ int DGLB200GraphFree(DGLB200GraphHandle g) {
     pool_free(g->coo_src, s);
     pool_free(g->coo_dst, s);
     pool_free(g->bad_ids, s);
+    pool_free(g->seg_dst, s);
+    pool_free(g->seg_type, s);
     g->in_s.indptr = nullptr;
     free_csr(g->in_s);
     free_csr(g->in);
@@ -1095,6 +1097,118 @@ int DGLB200GraphCreateFromTypedCSR(int64_t num_nodes, int64_t num_edges, int idx
     throw ApiError{msg};
   }
   *out = g;
+  API_END();
+}
+
+// ---- relation segments: every maximal run of one edge type inside a destination row of the
+// typed in-CSR is one (relation, destination) pair that receives messages
+__global__ void seg_runs_count_kernel(const int32_t* __restrict__ indptr,
+                                      const int32_t* __restrict__ types, int64_t n_rows,
+                                      int32_t* __restrict__ counts) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += stride) {
+    const int32_t b = indptr[r], e = indptr[r + 1];
+    int32_t c = 0, prev = -1;
+    for (int32_t p = b; p < e; ++p) {
+      const int32_t t = types[p];
+      c += (t != prev);
+      prev = t;
+    }
+    counts[r] = c;
+  }
+}
+
+__global__ void seg_runs_fill_kernel(const int32_t* __restrict__ indptr,
+                                     const int32_t* __restrict__ types,
+                                     const int32_t* __restrict__ eids,
+                                     const int32_t* __restrict__ src_of_eid, int64_t n_rows,
+                                     const int32_t* __restrict__ seg_ptr,
+                                     int32_t* __restrict__ seg_dst, int32_t* __restrict__ seg_type,
+                                     int64_t* __restrict__ coo_src, int64_t* __restrict__ coo_seg) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += stride) {
+    const int32_t b = indptr[r], e = indptr[r + 1];
+    int32_t seg = seg_ptr[r] - 1, prev = -1;
+    for (int32_t p = b; p < e; ++p) {
+      const int32_t t = types[p];
+      if (t != prev) {
+        ++seg;
+        seg_dst[seg] = (int32_t)r;
+        seg_type[seg] = t;
+        prev = t;
+      }
+      const int32_t id = eids[p];
+      coo_src[id] = src_of_eid[id];
+      coo_seg[id] = seg;
+    }
+  }
+}
+
+int DGLB200GraphCreateRelationSegments(DGLB200GraphHandle g, void* stream,
+                                       DGLB200GraphHandle* out) {
+  API_BEGIN();
+  B200_CHECK(g && out, "NULL argument");
+  B200_CHECK(g->ty.num_types > 0, "graph has no edge types (call DGLB200GraphSetEdgeTypes)");
+  ensure_device(g->device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t e = g->num_edges, n = g->num_dst;
+  const size_t eb = (size_t)std::max<int64_t>(e, 1);
+  Scratch seg_ptr((size_t)(n + 1) * 4, s), src64(eb * 8, s), seg64(eb * 8, s);
+  fill_i32(seg_ptr.as<int32_t>(), n + 1, 0, s);
+  const int rb = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, 148 * 16));
+  if (n > 0) {
+    seg_runs_count_kernel<<<rb, 256, 0, s>>>(g->in.indptr, g->ty.in.types, n, seg_ptr.as<int32_t>());
+    note_kernel(nullptr, 1);
+  }
+  exclusive_scan_i32(seg_ptr.as<int32_t>(), n + 1, s);
+  int32_t n_seg = 0;
+  B200_CUDA(cudaMemcpyAsync(&n_seg, seg_ptr.as<int32_t>() + n, 4, cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  ensure_valid_ids(g, s);
+  int32_t *seg_dst = nullptr, *seg_type = nullptr;
+  B200_CUDA(pool_alloc(&seg_dst, (size_t)std::max(n_seg, 1) * 4, s));
+  B200_CUDA(pool_alloc(&seg_type, (size_t)std::max(n_seg, 1) * 4, s));
+  DGLB200GraphHandle sg = nullptr;
+  try {
+    if (n > 0 && e > 0) {
+      seg_runs_fill_kernel<<<rb, 256, 0, s>>>(g->in.indptr, g->ty.in.types, g->ty.in.eids,
+                                              graph_coo(g, 0, s), n, seg_ptr.as<int32_t>(), seg_dst,
+                                              seg_type, src64.as<int64_t>(), seg64.as<int64_t>());
+      note_kernel(nullptr, 1);
+    }
+    // sources -> segments, edge ids preserved: the standard constructor gives this graph the same
+    // index invariants (and kernels, reducers, gradients) as any other
+    B200_CHECK(DGLB200GraphCreateFromCOO(g->num_src, n_seg, e, src64.as<int64_t>(),
+                                         seg64.as<int64_t>(), g->device, stream, &sg) == 0,
+               std::string(DGLB200GetLastError()));
+  } catch (...) {
+    pool_free(seg_dst, s);
+    pool_free(seg_type, s);
+    throw;
+  }
+  sg->seg_dst = seg_dst;
+  sg->seg_type = seg_type;
+  *out = sg;
+  API_END();
+}
+
+int DGLB200GraphCopyRelationSegments(DGLB200GraphHandle sg, int32_t* seg_dst, int32_t* seg_type,
+                                     void* stream) {
+  API_BEGIN();
+  B200_CHECK(sg && sg->seg_dst, "not a relation-segment graph");
+  ensure_device(sg->device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  bool host = false;
+  auto copy = [&](int32_t* dst, const int32_t* src) {
+    if (!dst || sg->num_dst <= 0) return;
+    const bool dev = is_device_ptr(dst);
+    host = host || !dev;
+    B200_CUDA(cudaMemcpyAsync(dst, src, (size_t)sg->num_dst * 4,
+                              dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+  };
+  copy(seg_dst, sg->seg_dst);
+  copy(seg_type, sg->seg_type);
+  if (host) B200_CUDA(cudaStreamSynchronize(s));
   API_END();
 }
 

@@ -394,7 +394,7 @@ bool try_spmm(const KernelCall& c) {
               aligned(A, 16) && o_map == nullptr && c.row_scale == nullptr &&  // mapped / scaled: LDG path
               c.a_tab == nullptr;
     const int64_t mean_deg = E / std::max<int64_t>(csr.n_rows, 1);
-    // Measured on B200 (profiles/r1_spmm_paths.md): the LDG path beats the bulk-copy path on
+    // Measured on B200 (profiles/sweep1.txt, profiles/microbench_v1.txt): the LDG path beats the bulk-copy path on
     // this gather (TMA 1-D copies of 2.4 KB rows top out near 20-30 B/clk/SM), so it is opt-in.
     (void)mean_deg;
     const bool want = (force == 2);

@@ -74,16 +74,18 @@ def _route_host_index():
     from dgl import ndarray as nd
 
     def host_ctx(fn):
-        def get(self, ctx):
+        def get(self, *args):              # get_immutable_gidx(ctx) / get_unitgraph(etype, ctx)
+            ctx = args[-1]
             if ctx.device_type != 1:       # not kDLCPU
-                ctx = nd.cpu()
-            return fn(self, ctx)
-        get.__wrapped__ = fn
+                args = args[:-1] + (nd.cpu(),)
+            return fn(self, *args)
+        get._b200_host_routed = True
         return get
     for cls, name in ((graph_index.GraphIndex, "get_immutable_gidx"),
                       (heterograph_index.HeteroGraphIndex, "get_unitgraph")):
         fn = getattr(cls, name, None)
-        if fn is not None and not hasattr(fn, "__wrapped__"):
+        # (functools.wraps in utils.cached_member already sets __wrapped__: use an own marker)
+        if fn is not None and not getattr(fn, "_b200_host_routed", False):
             setattr(cls, name, host_ctx(fn))
 
 

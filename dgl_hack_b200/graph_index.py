@@ -112,6 +112,27 @@ class GraphIndex(object):
                 _stream(self.device)))
         return out
 
+    def relation_segments(self):
+        """(segment graph, seg_dst, seg_type): the relation-segment graph of a typed graph
+        (DGLB200GraphCreateRelationSegments; cached). One destination row per (relation, node)
+        pair that receives edges; ONE copy_reduce / binary_reduce on it = the reference's loop
+        over the relations' unit graphs (python/dgl/nn/pytorch/hetero.py:120-171). seg_dst /
+        seg_type are int64 CUDA tensors."""
+        cached = self.__dict__.get("_rel_segments")
+        if cached is None:
+            handle = _lib.GraphHandle()
+            with torch.cuda.device(self.device):
+                check_call(LIB.DGLB200GraphCreateRelationSegments(
+                    self._handle, _stream(self.device), ctypes.byref(handle)))
+                sg = GraphIndex(handle, self.device)
+                tabs = [torch.empty((sg.num_dst,), dtype=torch.int32, device=self.device)
+                        for _ in range(2)]
+                check_call(LIB.DGLB200GraphCopyRelationSegments(
+                    handle, *[ctypes.c_void_p(t.data_ptr()) for t in tabs],
+                    _stream(self.device)))
+            cached = self.__dict__["_rel_segments"] = (sg, tabs[0].long(), tabs[1].long())
+        return cached
+
     def __del__(self):
         h, self._handle = getattr(self, "_handle", None), None
         if h:

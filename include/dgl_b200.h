@@ -231,6 +231,26 @@ int DGLB200GraphCreateFromTypedCSR(int64_t num_nodes, int64_t num_edges, int idx
                                    const void* types, int64_t num_types, int device, void* stream,
                                    DGLB200GraphHandle* out);
 
+/* Batched per-relation message passing (BASELINE config 4: HeteroGraphConv loops R
+ * BinaryOpReduce / CopyReduce calls over R UnitGraphs, python/dgl/nn/pytorch/hetero.py:120-171,
+ * src/kernel/binary_reduce.cc:246-269; R = 133 launches that each write every destination row).
+ * From a typed graph (DGLB200GraphSetEdgeTypes) builds the RELATION-SEGMENT graph: one destination
+ * row per (relation, destination node) pair that receives at least one edge, sources and edge
+ * ids unchanged. Every kernel entry point of this header accepts the new handle, so ONE
+ * CopyReduce / BinaryOpReduce call on it computes what the reference's loop over the relations'
+ * unit graphs computes, for all relations at once, writing each receiving (relation, node) row
+ * exactly once: row s of the output = the reduction over the in-edges of relation seg_type[s]
+ * into node seg_dst[s]; (relation, node) pairs without edges have no row (the loop's outputs hold
+ * the reducer identity there). Segments are ordered by (node, relation); inside one, edges are
+ * reduced in the unit graph's own order (source ascending, edge id). Synchronises `stream` once
+ * (the number of segments is needed on the host); free the handle with DGLB200GraphFree. */
+int DGLB200GraphCreateRelationSegments(DGLB200GraphHandle typed_graph, void* stream,
+                                       DGLB200GraphHandle* out);
+/* seg_dst[s], seg_type[s] of a relation-segment graph (num_dst entries each, int32; host or
+ * device buffers, either may be NULL). */
+int DGLB200GraphCopyRelationSegments(DGLB200GraphHandle segment_graph, int32_t* seg_dst,
+                                     int32_t* seg_type, void* stream);
+
 /* kernel._CAPI_DGLRgcnLayer0(graph, weight, norm, ret)  (src/kernel/binary_reduce.cc:412-420;
  * kernel src/kernel/cuda/binary_reduce_impl.cu:913-975). weight [R, N, F] (the embedding of a
  * one-hot input), norm [E,1] by edge id, ret [N, F]:

@@ -20,12 +20,59 @@ import cases
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 # Tolerances: bit-exact for index arrays and for max/min/none *values*; sums within 1e-5
-# relative (north_star), measured against the magnitude of the summed terms; prod 1e-4.
+# relative (north_star) of sum|terms| per output element (term_scale; no absolute floor);
+# prod 1e-4 of the value.
 RTOL = {"sum": 1e-5, "prod": 1e-4, "max": 0.0, "min": 0.0, "none": 0.0}
 
 
 def load(name):
     return np.load(os.path.join(GOLDEN, name))
+
+
+def _oracle_twin(g):
+    """The oracle's graph of the same edges (cached on g), for the tolerance scales below."""
+    from oracle import oracle as O
+    if isinstance(g, O.Graph):
+        return g
+    twin = getattr(g, "_oracle_twin", None)
+    if twin is None:
+        indptr, indices, eids = (np.asarray(a).astype(np.int64) for a in g.in_csr)
+        n_dst = indptr.shape[0] - 1
+        e = indices.shape[0]
+        src, dst = np.empty(e, np.int64), np.empty(e, np.int64)
+        src[eids] = indices
+        dst[eids] = np.repeat(np.arange(n_dst), np.diff(indptr))
+        n_src = np.asarray(g.out_csr[0]).shape[0] - 1
+        twin = O.Graph(n_src, n_dst, src, dst)
+        g._oracle_twin = twin
+    return twin
+
+
+def _abs_op(op):
+    return "add" if op in ("add", "sub") else op
+
+
+def term_scale(g, red, op, lt, rt, a, b, out_rows, maps, grad=None, want=None, gout=None):
+    """sum over the reduced terms of |term| for every output element: the magnitude north_star's
+    1e-5 relative tolerance for sums is measured against (instead of max(|want|, 1), an absolute
+    1e-5 floor). Evaluated by the oracle on |inputs| with the sum reducer (max/min gradients:
+    an upper bound, ties only drop terms). None for prod (kept relative to |want|)."""
+    from oracle import oracle as O
+    if red == "prod":
+        return None
+    og = _oracle_twin(g)
+    r = "none" if red == "none" else "sum"
+    a_ = np.abs(a)
+    b_ = None if b is None else np.abs(b)
+    if grad is None:
+        if b is None:
+            return np.abs(O.copy_reduce(r, og, lt, a_, out_rows, *maps))
+        return np.abs(O.binary_op_reduce(r, _abs_op(op), og, lt, rt, a_, b_, out_rows, *maps))
+    w_, g_ = np.abs(want), np.abs(gout)
+    if b is None:
+        return np.abs(O.backward_copy_reduce(r, og, lt, a_, w_, g_, *maps))
+    fn = O.backward_lhs_binary_op_reduce if grad == "lhs" else O.backward_rhs_binary_op_reduce
+    return np.abs(fn(r, _abs_op(op), og, lt, rt, a_, b_, w_, g_, *maps))
 
 
 def check(name, got, want, red, scale=None, grad=False):
@@ -45,8 +92,10 @@ def check(name, got, want, red, scale=None, grad=False):
         assert ok, "%s: not bit-exact, max abs diff %g" % (
             name, np.abs(got.astype(np.float64) - want).max())
         return
-    s = np.abs(want) if scale is None else scale
-    tol = rtol * np.maximum(s, 1.0) + 1e-6
+    if scale is None:      # prod: relative to the value itself (no additive term structure)
+        tol = rtol * np.maximum(np.abs(want), 1.0) + 1e-6
+    else:                  # 1e-5 of sum|terms| (+ a denormal-sized floor, not an absolute 1e-5)
+        tol = rtol * np.maximum(scale, np.abs(want)) + 1e-30
     err = np.abs(got.astype(np.float64) - want.astype(np.float64))
     assert (err <= tol).all(), "%s: max err %g (tol %g)" % (name, err.max(), tol.max())
 
@@ -75,16 +124,20 @@ def replay_kernel_graph(impl, subset=None):
         lt, rt = cases.TARGETS[lhs], cases.TARGETS[rhs]
         out_rows = ne if red == "none" else n
         want = gold["kg/%s/out" % name]
+        no = (None, None, None)
         out = impl.binary_op_reduce(red, op, g, lt, rt, a, b, out_rows, None, None, None)
-        check(name + "/out", out, want, red)
+        check(name + "/out", out, want, red,
+              scale=term_scale(g, red, op, lt, rt, a, b, out_rows, no))
         gout = cases.grad_out_for(want.shape)
         # feed the REFERENCE forward output to backward so max/min masks are comparable
         gl = impl.backward_lhs_binary_op_reduce(red, op, g, lt, rt, a, b, want, gout,
                                                 None, None, None)
-        check(name + "/gl", gl, gold["kg/%s/gl" % name], red, grad=True)
+        check(name + "/gl", gl, gold["kg/%s/gl" % name], red, grad=True,
+              scale=term_scale(g, red, op, lt, rt, a, b, out_rows, no, "lhs", want, gout))
         gr = impl.backward_rhs_binary_op_reduce(red, op, g, lt, rt, a, b, want, gout,
                                                 None, None, None)
-        check(name + "/gr", gr, gold["kg/%s/gr" % name], red, grad=True)
+        check(name + "/gr", gr, gold["kg/%s/gr" % name], red, grad=True,
+              scale=term_scale(g, red, op, lt, rt, a, b, out_rows, no, "rhs", want, gout))
         count += 1
     hu, hv, he = cases.generate_feature(n, ne)
     for tname, x in (("u", hu), ("e", he)):
@@ -92,12 +145,15 @@ def replay_kernel_graph(impl, subset=None):
             name = "copy_%s__%s" % (tname, red)
             out_rows = ne if red == "none" else n
             want = gold["kg/%s/out" % name]
-            out = impl.copy_reduce(red, g, cases.TARGETS[tname], x, out_rows, None, None)
-            check(name + "/out", out, want, red)
+            tg, no2 = cases.TARGETS[tname], (None, None)
+            out = impl.copy_reduce(red, g, tg, x, out_rows, None, None)
+            check(name + "/out", out, want, red,
+                  scale=term_scale(g, red, None, tg, None, x, None, out_rows, no2))
             gout = cases.grad_out_for(want.shape)
-            gi = impl.backward_copy_reduce(red, g, cases.TARGETS[tname], x, want, gout,
-                                           None, None)
-            check(name + "/gin", gi, gold["kg/%s/gin" % name], red, grad=True)
+            gi = impl.backward_copy_reduce(red, g, tg, x, want, gout, None, None)
+            check(name + "/gin", gi, gold["kg/%s/gin" % name], red, grad=True,
+                  scale=term_scale(g, red, None, tg, None, x, None, out_rows, no2, "lhs", want,
+                                   gout))
             count += 1
     return count
 
@@ -106,21 +162,26 @@ def _bin(impl, gold, key, red, op, g, lt, rt, a, b, out_rows, maps=(None,) * 3,
          bmaps=(None,) * 3):
     want = gold[key + "/out"]
     out = impl.binary_op_reduce(red, op, g, lt, rt, a, b, out_rows, *maps)
-    check(key + "/out", out, want, red)
+    check(key + "/out", out, want, red,
+          scale=term_scale(g, red, op, lt, rt, a, b, out_rows, maps))
     gout = cases.grad_out_for(want.shape)
     gl = impl.backward_lhs_binary_op_reduce(red, op, g, lt, rt, a, b, want, gout, *bmaps)
-    check(key + "/gl", gl, gold[key + "/gl"], red, grad=True)
+    check(key + "/gl", gl, gold[key + "/gl"], red, grad=True,
+          scale=term_scale(g, red, op, lt, rt, a, b, out_rows, bmaps, "lhs", want, gout))
     gr = impl.backward_rhs_binary_op_reduce(red, op, g, lt, rt, a, b, want, gout, *bmaps)
-    check(key + "/gr", gr, gold[key + "/gr"], red, grad=True)
+    check(key + "/gr", gr, gold[key + "/gr"], red, grad=True,
+          scale=term_scale(g, red, op, lt, rt, a, b, out_rows, bmaps, "rhs", want, gout))
 
 
 def _copy(impl, gold, key, red, g, tgt, x, out_rows, maps=(None,) * 2, bmaps=(None,) * 2):
     want = gold[key + "/out"]
     out = impl.copy_reduce(red, g, tgt, x, out_rows, *maps)
-    check(key + "/out", out, want, red)
+    check(key + "/out", out, want, red,
+          scale=term_scale(g, red, None, tgt, None, x, None, out_rows, maps))
     gout = cases.grad_out_for(want.shape)
     gi = impl.backward_copy_reduce(red, g, tgt, x, want, gout, *bmaps)
-    check(key + "/gin", gi, gold[key + "/gin"], red, grad=True)
+    check(key + "/gin", gi, gold[key + "/gin"], red, grad=True,
+          scale=term_scale(g, red, None, tgt, None, x, None, out_rows, bmaps, "lhs", want, gout))
 
 
 def replay_mid(impl):
