@@ -23,6 +23,8 @@ import time
 import torch
 import torch.distributed as dist
 
+from dgl_hack_b200 import dense
+
 PRODUCTS_N, PRODUCTS_E, PRODUCTS_D = 2449029, 61859140, 100
 GCN_DIMS = [100, 256, 256, 47]
 
@@ -66,15 +68,16 @@ class GCN(torch.nn.Module):
     def forward(self, agg, h):
         n = len(self.w)
         for k, (w, b) in enumerate(zip(self.w, self.b)):
+            last = k + 1 == n
             if w.shape[0] > w.shape[1]:
                 pad = (-w.shape[1]) % 4
-                h = h @ (torch.nn.functional.pad(w, (0, pad)) if pad else w)
-                h = agg(h)[:, :w.shape[1]]
+                h = dense.linear(h, torch.nn.functional.pad(w, (0, pad)) if pad else w)
+                h = agg(h)[:, :w.shape[1]] + b
+                if not last:
+                    h = torch.relu(h)
             else:
-                h = agg(h) @ w
-            h = h + b
-            if k + 1 < n:
-                h = torch.relu(h)
+                # bias and ReLU ride on the GEMM's epilogue (B200_DENSE=tf32x3: fused in-kernel)
+                h = dense.linear(agg(h), w, b, relu=not last)
         return h
 
 

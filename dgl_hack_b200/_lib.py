@@ -125,6 +125,12 @@ SYMBOLS = {
                                                       _c.POINTER(GraphHandle)]),
     "DGLB200GraphCopyRelationSegments": (_c.c_int, [GraphHandle, _c.c_void_p, _c.c_void_p,
                                                     _c.c_void_p]),
+    "DGLB200KernelCopySumBF16": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP, TensorP,
+                                            _c.c_int, TensorP, _c.c_void_p]),
+    "DGLB200DenseTF32x3": (_c.c_int, [TensorP, TensorP, _c.c_int, TensorP, _c.c_int, TensorP,
+                                      _c.c_void_p]),
+    "DGLB200GroupedDenseTF32x3": (_c.c_int, [TensorP, TensorP, _c.c_int, _c.c_void_p, _c.c_int,
+                                             TensorP, _c.c_void_p]),
     "DGLB200RegisterInto": (_c.c_int, [_c.c_void_p]),
     "DGLB200SetStream": (_c.c_int, [_c.c_void_p]),
     "DGLB200PackedFuncCount": (_c.c_int, []),

@@ -18,6 +18,7 @@ All tensors must live on the graph's CUDA device: there is no CPU fallback.
 import torch as th
 
 from . import kernel as K
+from ._lib import DGLError
 
 SRC, DST, EDGE = 0, 1, 2  # python/dgl/function/base.py TargetCode
 
@@ -324,3 +325,103 @@ def rgcn_layer1(graph, x, weight, norm):
     x, weight, norm = x.contiguous(), weight.contiguous(), norm.contiguous()
     ret = weight.new_empty((graph.num_dst, weight.size(2)))
     return RgcnSecondLayer.apply(graph, x, weight, norm, ret)
+
+
+class CopyReduceBF16(th.autograd.Function):
+    """copy_src + sum / mean on bf16 feature storage (fp32 accumulation): the explicit
+    reduced-precision tier (no reference counterpart; its kernels are fp32-only)."""
+
+    @staticmethod
+    def forward(ctx, graph, x, mean):
+        out = x.new_empty((graph.num_dst, x.shape[1]))
+        K.copy_sum_bf16(graph, False, x, None, None, mean, out)
+        ctx.backward_cache = (graph, mean)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        graph, mean = ctx.backward_cache
+        grad_out = grad_out.contiguous()
+        grad_x = grad_out.new_empty((graph.num_src, grad_out.shape[1]))
+        # d mean / d x[u] = sum_{u -> v} grad_out[v] / max(deg v, 1): a per-gathered-node scale
+        cs = (1.0 / graph.mean_divisor(th.float32)) if mean else None
+        K.copy_sum_bf16(graph, True, grad_out, cs, None, False, grad_x)
+        return None, grad_x, None
+
+
+def to_bf16_storage(x):
+    """[N, D] float tensor -> bf16 feature storage [N, ceil8(D)] (zero padded so that every row
+    is a whole number of 16-byte vectors). Slice `[:, :D]` of a result to drop the padding."""
+    pad = (-x.shape[1]) % 8
+    x = x.to(th.bfloat16)
+    return th.nn.functional.pad(x, (0, pad)).contiguous() if pad else x.contiguous()
+
+
+def copy_reduce_bf16(reducer, graph, x):
+    """`copy_src + sum|mean` on bf16 storage (see to_bf16_storage); returns bf16 [num_dst, D]."""
+    if reducer not in ("sum", "mean"):
+        raise DGLError("the bf16 tier implements the sum and mean reducers")
+    if x.dtype != th.bfloat16 or x.dim() != 2 or x.shape[1] % 8:
+        raise DGLError("copy_reduce_bf16 takes bf16 [N, D] storage with D % 8 == 0 "
+                       "(backend.to_bf16_storage)")
+    return CopyReduceBF16.apply(graph, x.contiguous(), reducer == "mean")
+
+
+class GroupedMatMul(th.autograd.Function):
+    """c[rows of group g] = a[rows of group g] @ w[g]: the per-relation dense contraction on the
+    tensor cores (csrc/gemm.cu, grouped mode). grad_a runs on the same kernel (w[g] read
+    transposed); grad_w[g] = a_g^T @ g_g reduces over the rows of a group (library GEMM per
+    non-empty group)."""
+
+    @staticmethod
+    def forward(ctx, a, w, group_ptr):
+        a, w = a.contiguous(), w.contiguous()
+        c = a.new_empty((a.shape[0], w.shape[2]))
+        K.grouped_dense_tf32x3(a, w, True, group_ptr, c)
+        ctx.group_ptr = group_ptr
+        ctx.save_for_backward(a, w)
+        return c
+
+    @staticmethod
+    def backward(ctx, g):
+        a, w = ctx.saved_tensors
+        gp = ctx.group_ptr
+        g = g.contiguous()
+        ga = gw = None
+        if ctx.needs_input_grad[0]:
+            ga = th.empty_like(a)
+            K.grouped_dense_tf32x3(g, w, False, gp, ga)
+        if ctx.needs_input_grad[1]:
+            gw = th.zeros_like(w)
+            for r in range(w.shape[0]):
+                if gp[r + 1] > gp[r]:
+                    th.matmul(a[gp[r]:gp[r + 1]].t(), g[gp[r]:gp[r + 1]], out=gw[r])
+        return ga, gw, None
+
+
+def grouped_matmul_supported(x, weight):
+    return (x.is_cuda and x.dtype == th.float32 and x.dim() == 2 and weight.dim() == 3
+            and x.shape[1] % 4 == 0 and weight.shape[2] <= 256 and weight.shape[1] <= 256)
+
+
+def rgcn_layer1_tc(graph, x, weight, norm=None):
+    """ret[v] = sum_e norm_e * h[src_e] . W[type_e] with the per-relation contraction on the
+    TENSOR CORES: (1) per-(relation, node) sums of norm_e * h[src_e] -- one SpMM launch on the
+    relation-segment graph; (2) rows of relation r times W[r] -- grouped tcgen05 GEMM; (3) the
+    relations' rows of a node added up -- one copy_e + sum launch. No [E, in, out] / [E, out]
+    temporaries; widths up to 256 (the fused SIMT kernel rgcn_layer1 stops at in * out = 1024)."""
+    sg, seg_dst, seg_type = graph.relation_segments()
+    cache = sg.__dict__.setdefault("_tc_plan", {})
+    if "group_ptr" not in cache:
+        from .graph_index import GraphIndex
+        counts = th.bincount(seg_type, minlength=weight.shape[0])
+        cache["group_ptr"] = [0] + th.cumsum(counts, 0).tolist()
+        cache["to_node"] = GraphIndex.from_coo(graph.num_dst, graph.num_dst, seg_dst, seg_dst,
+                                               graph.device)
+    n_seg = sg.num_dst
+    if norm is None:
+        s = copy_reduce("sum", sg, 0, x, n_seg)
+    else:
+        s = binary_reduce("sum", "mul", sg, 0, 2, x, norm.reshape(-1, 1), n_seg)
+    y = GroupedMatMul.apply(s, weight, cache["group_ptr"])
+    return copy_reduce("sum", cache["to_node"], 2, y, graph.num_dst)

@@ -805,6 +805,109 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
   API_END();
 }
 
+// ---- bf16 feature storage, fp32 accumulation (extension, explicit dtype) ----
+int DGLB200KernelCopySumBF16(DGLB200GraphHandle graph, int transpose, const DGLB200Tensor* in_data,
+                             const DGLB200Tensor* col_scale, const DGLB200Tensor* row_scale,
+                             int mean, DGLB200Tensor* out_data, void* stream) {
+  API_BEGIN();
+  B200_CHECK(graph && in_data && out_data, "NULL argument");
+  check_ctx(graph, {in_data, col_scale, row_scale, out_data},
+            {"in_data", "col_scale", "row_scale", "out_data"});
+  for (const DGLB200Tensor* t : {in_data, (const DGLB200Tensor*)out_data}) {
+    // kDLBfloat = 4 (dlpack.h); a float32 tensor is NOT converted silently
+    B200_CHECK(t->dtype.code == 4 && t->dtype.bits == 16 && t->dtype.lanes == 1,
+               "CopySumBF16: in_data / out_data must be bfloat16 tensors");
+    check_compact(t, "bf16 tensor");
+    B200_CHECK(t->ndim == 2, "CopySumBF16: tensors must be [rows, D]");
+  }
+  const int64_t n_cols = transpose ? graph->num_dst : graph->num_src;
+  const int64_t n_rows = transpose ? graph->num_src : graph->num_dst;
+  const int64_t D = in_data->shape[1];
+  B200_CHECK(in_data->shape[0] == n_cols, "CopySumBF16: in_data needs one row per gathered node");
+  B200_CHECK(out_data->shape[0] == n_rows && out_data->shape[1] == D,
+             "CopySumBF16: out_data must be [reducing nodes, D]");
+  B200_CHECK(D % 8 == 0 && D >= 8 && D <= 1024,
+             "CopySumBF16: D must be a multiple of 8 in [8, 1024] (pad the storage)");
+  B200_CHECK((reinterpret_cast<uintptr_t>(data_ptr<char>(in_data)) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(data_ptr<char>(out_data)) & 15) == 0,
+             "CopySumBF16: tensors must be 16-byte aligned");
+  const float *cs = nullptr, *rs = nullptr;
+  if (col_scale) {
+    check_float(col_scale, "col_scale");
+    B200_CHECK(num_elements(col_scale) == n_cols, "CopySumBF16: col_scale needs one value per gathered node");
+    cs = data_ptr<const float>(col_scale);
+  }
+  if (row_scale) {
+    check_float(row_scale, "row_scale");
+    B200_CHECK(num_elements(row_scale) == n_rows, "CopySumBF16: row_scale needs one value per reducing node");
+    rs = data_ptr<const float>(row_scale);
+  }
+  B200_CUDA(cudaSetDevice(graph->device));
+  spmm_bf16(graph, transpose ? 1 : 0, data_ptr<const void>(in_data), cs, rs, mean ? 1 : 0,
+            data_ptr<void>(out_data), D, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+// ---- dense projection on the tensor cores (extension) ----
+int DGLB200DenseTF32x3(const DGLB200Tensor* a, const DGLB200Tensor* b, int b_is_kn,
+                       const DGLB200Tensor* bias, int relu, DGLB200Tensor* c, void* stream) {
+  API_BEGIN();
+  B200_CHECK(a && b && c, "NULL argument");
+  for (const DGLB200Tensor* t : {a, b, (const DGLB200Tensor*)c}) {
+    check_float(t, "dense operand");
+    check_compact(t, "dense operand");
+    B200_CHECK(t->ndim == 2, "DenseTF32x3: operands must be 2-D");
+    B200_CHECK(t->ctx.device_type == 2 && t->ctx.device_id == a->ctx.device_id,
+               "DenseTF32x3: operands must live on one CUDA device (there is no CPU path)");
+  }
+  const int64_t M = a->shape[0], K = a->shape[1];
+  const int64_t N = b_is_kn ? b->shape[1] : b->shape[0];
+  B200_CHECK((b_is_kn ? b->shape[0] : b->shape[1]) == K, "DenseTF32x3: inner dimensions differ");
+  B200_CHECK(c->shape[0] == M && c->shape[1] == N, "DenseTF32x3: output must be [M, N]");
+  if (bias) {
+    check_float(bias, "bias");
+    check_compact(bias, "bias");
+    B200_CHECK(num_elements(bias) == N && bias->ctx.device_type == 2, "DenseTF32x3: bias must be [N]");
+  }
+  if (M == 0 || N == 0) return 0;
+  B200_CHECK(K > 0, "DenseTF32x3: K must be positive");
+  B200_CHECK(gemm_tf32x3_supported(M, N, K, data_ptr<const float>(a), K),
+             "DenseTF32x3: needs N <= 256, K divisible by 4 and a 16-byte aligned left operand");
+  B200_CUDA(cudaSetDevice(a->ctx.device_id));
+  gemm_tf32x3(data_ptr<const float>(a), K, data_ptr<const float>(b), b_is_kn ? 1 : 0,
+              bias ? data_ptr<const float>(bias) : nullptr, relu ? 1 : 0, data_ptr<float>(c), N, M,
+              N, K, 1, nullptr, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int DGLB200GroupedDenseTF32x3(const DGLB200Tensor* a, const DGLB200Tensor* b, int b_is_kn,
+                              const int64_t* group_ptr, int groups, DGLB200Tensor* c,
+                              void* stream) {
+  API_BEGIN();
+  B200_CHECK(a && b && c && group_ptr && groups >= 1, "NULL argument");
+  for (const DGLB200Tensor* t : {a, b, (const DGLB200Tensor*)c}) {
+    check_float(t, "dense operand");
+    check_compact(t, "dense operand");
+    B200_CHECK(t->ctx.device_type == 2 && t->ctx.device_id == a->ctx.device_id,
+               "GroupedDenseTF32x3: operands must live on one CUDA device");
+  }
+  B200_CHECK(a->ndim == 2 && c->ndim == 2 && b->ndim == 3 && b->shape[0] == groups,
+             "GroupedDenseTF32x3: a [M, K], b [groups, K, N] or [groups, N, K], c [M, N]");
+  const int64_t M = a->shape[0], K = a->shape[1];
+  const int64_t N = b_is_kn ? b->shape[2] : b->shape[1];
+  B200_CHECK((b_is_kn ? b->shape[1] : b->shape[2]) == K, "GroupedDenseTF32x3: inner dimensions differ");
+  B200_CHECK(c->shape[0] == M && c->shape[1] == N, "GroupedDenseTF32x3: output must be [M, N]");
+  B200_CHECK(group_ptr[0] == 0 && group_ptr[groups] == M,
+             "GroupedDenseTF32x3: group_ptr must run from 0 to M");
+  if (M == 0 || N == 0) return 0;
+  B200_CHECK(K > 0 && gemm_tf32x3_supported(M, N, K, data_ptr<const float>(a), K),
+             "GroupedDenseTF32x3: needs N <= 256, K divisible by 4 and a 16-byte aligned left operand");
+  B200_CUDA(cudaSetDevice(a->ctx.device_id));
+  gemm_tf32x3(data_ptr<const float>(a), K, data_ptr<const float>(b), b_is_kn ? 1 : 0, nullptr, 0,
+              data_ptr<float>(c), N, M, N, K, groups, group_ptr, static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
 // ---- neighbour sampling (extension) ----
 int DGLB200SampleNeighbors(DGLB200GraphHandle graph, const int64_t* seeds, int64_t n_seeds,
                            int fanout, int replace, uint64_t rng_seed, const int64_t* offsets,
@@ -929,15 +1032,25 @@ int DGLB200KernelPeerCopySum(DGLB200GraphHandle graph, int transpose, int n_slot
   API_BEGIN();
   B200_CHECK(graph && slot_base && node_code && out_data, "NULL argument");
   B200_CHECK(n_slots >= 1 && n_slots <= 16, "PeerCopySum: 1 to 16 slots");
-  check_ctx(graph, {node_code, row_scale, out_data}, {"node_code", "row_scale", "out_data"});
-  check_id_arrays({node_code}, {"node_code"});
+  check_ctx(graph, {row_scale, out_data}, {"row_scale", "out_data"});
   check_float(out_data, "out_data");
   check_compact(out_data, "out_data");
   const int64_t n_cols = transpose ? graph->num_dst : graph->num_src;  // gathered side
   const int64_t n_rows = transpose ? graph->num_src : graph->num_dst;  // written side
-  B200_CHECK(node_code->shape[0] == n_cols, "PeerCopySum: node_code needs one code per gathered node");
   B200_CHECK(out_data->ndim >= 1 && out_data->shape[0] == n_rows,
              "PeerCopySum: out_data must have one row per reducing node");
+  if (n_rows == 0) return 0;  // a rank that owns no node
+  if (graph->num_edges == 0 || n_cols == 0) {  // owned nodes without any edge: all sums are empty
+    B200_CUDA(cudaSetDevice(graph->device));
+    fill_f32(data_ptr<float>(out_data), num_elements(out_data), 0.f,
+             static_cast<cudaStream_t>(stream));
+    return 0;
+  }
+  check_ctx(graph, {node_code}, {"node_code"});
+  check_id_arrays({node_code}, {"node_code"});
+  B200_CHECK(node_code->ndim == 1 && node_code->shape[0] == n_cols,
+             "PeerCopySum: node_code needs one code per gathered node");
+
   if (row_scale) {
     check_float(row_scale, "row_scale");
     check_compact(row_scale, "row_scale");

@@ -296,6 +296,14 @@ void attn_proj_forward(const float* feat, const float* al, const float* ar, floa
 void attn_proj_backward(const float* feat, const float* al, const float* ar, const float* gl,
                         const float* gr, float* gfeat, float* gal, float* gar, int64_t n,
                         int64_t H, int64_t F, cudaStream_t s);
+// gemm.cu: fp32 dense product on the tensor cores (tcgen05, 3xTF32 error compensation)
+bool gemm_tf32x3_supported(int64_t M, int64_t N, int64_t K, const float* A, int64_t lda);
+void gemm_tf32x3(const float* A, int64_t lda, const float* B, int b_is_kn, const float* bias,
+                 int relu, float* C, int64_t ldc, int64_t M, int64_t N, int64_t K, int groups,
+                 const int64_t* group_ptr, cudaStream_t s);
+// spmm_bf16.cu: copy + sum / mean over bf16 feature rows (pitch D elements, D % 8 == 0)
+void spmm_bf16(DGLB200Graph* g, int transpose, const void* in, const float* col_scale,
+               const float* row_scale, int mean, void* out, int64_t D, cudaStream_t s);
 // sample.cu
 void sample_neighbors(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, int fanout,
                       bool replace, uint64_t rng_seed, const int64_t* offsets, int64_t* out_src,

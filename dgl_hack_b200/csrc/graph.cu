@@ -1144,6 +1144,13 @@ __global__ void seg_runs_fill_kernel(const int32_t* __restrict__ indptr,
   }
 }
 
+__global__ void remap_i64_kernel(int64_t* __restrict__ v, const int32_t* __restrict__ table,
+                                 int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += stride)
+    v[k] = table[v[k]];
+}
+
 int DGLB200GraphCreateRelationSegments(DGLB200GraphHandle g, void* stream,
                                        DGLB200GraphHandle* out) {
   API_BEGIN();
@@ -1175,6 +1182,25 @@ int DGLB200GraphCreateRelationSegments(DGLB200GraphHandle g, void* stream,
                                               graph_coo(g, 0, s), n, seg_ptr.as<int32_t>(), seg_dst,
                                               seg_type, src64.as<int64_t>(), seg64.as<int64_t>());
       note_kernel(nullptr, 1);
+    }
+    // renumber the segments relation-major (stable: nodes ascending inside a relation), so that
+    // the rows of one relation are contiguous -- "the output of relation r" is a slice, and a
+    // grouped GEMM can contract each slice with that relation's weight
+    if (n_seg > 1) {
+      const size_t sb = (size_t)n_seg * 4;
+      Scratch ka(sb, s), kb(sb, s), va(sb, s), vb(sb, s), inv(sb, s), dst_old(sb, s);
+      B200_CUDA(cudaMemcpyAsync(ka.ptr, seg_type, sb, cudaMemcpyDeviceToDevice, s));
+      B200_CUDA(cudaMemcpyAsync(dst_old.ptr, seg_dst, sb, cudaMemcpyDeviceToDevice, s));
+      int32_t *sk, *sv;
+      radix_sort_pairs(ka.as<int32_t>(), kb.as<int32_t>(), nullptr, va.as<int32_t>(),
+                       vb.as<int32_t>(), n_seg, g->ty.num_types, &sk, &sv, s);
+      B200_CUDA(cudaMemcpyAsync(seg_type, sk, sb, cudaMemcpyDeviceToDevice, s));
+      gather_i32(dst_old.as<int32_t>(), sv, seg_dst, n_seg, s);
+      const int sblocks = (int)std::min<int64_t>((n_seg + 255) / 256, 148 * 16);
+      invert_perm_kernel<<<sblocks, 256, 0, s>>>(sv, inv.as<int32_t>(), n_seg);
+      remap_i64_kernel<<<(int)std::min<int64_t>((e + 255) / 256, 148 * 16), 256, 0, s>>>(
+          seg64.as<int64_t>(), inv.as<int32_t>(), e);
+      note_kernel(nullptr, 2);
     }
     // sources -> segments, edge ids preserved: the standard constructor gives this graph the same
     // index invariants (and kernels, reducers, gradients) as any other

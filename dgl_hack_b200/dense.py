@@ -163,10 +163,89 @@ class _MatMul(torch.autograd.Function):
         return ga, gb
 
 
+def tc_supported(m, k, n, a):
+    """Shapes the library's own tensor-core GEMM (csrc/gemm.cu) takes."""
+    return n <= 256 and k % 4 == 0 and k > 0 and m > 0 and a.data_ptr() % 16 == 0
+
+
+def tc_gemm(a, b, b_is_kn=True, bias=None, relu=False):
+    """a @ (b if b_is_kn else b.T) (+ bias) (ReLU): the hand-written tcgen05 3xTF32 kernel
+    (DGLB200DenseTF32x3); no autograd. Falls back to torch for shapes it does not take."""
+    from . import kernel as K
+    a, b = a.contiguous(), b.contiguous()
+    n = b.shape[1] if b_is_kn else b.shape[0]
+    if not tc_supported(a.shape[0], a.shape[1], n, a):
+        c = a @ (b if b_is_kn else b.t())
+        if bias is not None:
+            c = c + bias
+        return torch.relu(c) if relu else c
+    c = torch.empty((a.shape[0], n), dtype=torch.float32, device=a.device)
+    K.dense_tf32x3(a, b, b_is_kn, bias, relu, c)
+    return c
+
+
+class _TcMatMul(torch.autograd.Function):
+    """a @ b on the own kernel; grad_a = g @ b.T on the same kernel (b read as [N', K']);
+    grad_b = a.T @ g reduces over the long dimension (MN-major operands): library GEMM."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        ctx.save_for_backward(a, b)
+        return tc_gemm(a, b, True)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        ga = tc_gemm(g.contiguous(), b, False) if ctx.needs_input_grad[0] else None
+        gb = a.t() @ g if ctx.needs_input_grad[1] else None
+        return ga, gb
+
+
+class _TcLinear(torch.autograd.Function):
+    """relu?(a @ w + bias) with the bias / ReLU applied while the accumulator is read out of
+    TMEM (one pass over the output instead of three)."""
+
+    @staticmethod
+    def forward(ctx, a, w, bias, relu):
+        y = tc_gemm(a, w, True, bias, relu)
+        ctx.relu = relu
+        ctx.save_for_backward(a, w, y if relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        a, w, y = ctx.saved_tensors
+        g = g.contiguous()
+        if ctx.relu:
+            g = g * (y > 0)
+        ga = tc_gemm(g, w, False) if ctx.needs_input_grad[0] else None
+        gw = a.t() @ g if ctx.needs_input_grad[1] else None
+        gb = g.sum(0) if ctx.needs_input_grad[2] else None
+        return ga, gw, gb, None
+
+
+def linear(a, w, bias=None, relu=False):
+    """relu?(a @ w + bias) with gradients. B200_DENSE=tf32x3: one fused tensor-core kernel
+    (csrc/gemm.cu); otherwise the composition of matmul / add / relu."""
+    if mode() == "tf32x3" and a.dim() == 2 and a.is_cuda and a.dtype == torch.float32:
+        return _TcLinear.apply(a, w, bias, bool(relu))
+    y = matmul(a, w) if enabled() else a @ w
+    if bias is not None:
+        y = y + bias
+    return torch.relu(y) if relu else y
+
+
+def mode():
+    return os.environ.get("B200_DENSE", "")
+
+
 def matmul(a, b):
-    """a @ b with gradients, both through the emulated-fp32 tensor-core GEMM."""
+    """a @ b with gradients on tensor cores at fp32 accuracy: B200_DENSE=tf32x3 = the library's
+    own tcgen05 kernel, B200_DENSE=bf16x9 = cuBLASLt's emulated-fp32 GEMM (a baseline)."""
+    if mode() == "tf32x3":
+        return _TcMatMul.apply(a, b)
     return _MatMul.apply(a, b)
 
 
 def enabled():
-    return os.environ.get("B200_DENSE", "") == "bf16x9"
+    return mode() in ("bf16x9", "tf32x3")

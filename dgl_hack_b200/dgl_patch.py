@@ -25,7 +25,9 @@ What crosses the boundary:
 One accommodation, and only when the loaded libdgl was built WITHOUT CUDA (the build available
 in this environment; a CUDA build needs none): `GraphIndex.get_immutable_gidx(gpu ctx)` /
 `HeteroGraphIndex.get_unitgraph(gpu ctx)` would ask that library to copy the graph to a device it
-has no API for, so they hand out the host index instead -- the kernels only read the CSR arrays.
+has no API for, so they hand out the host index instead -- the kernels only read the CSR arrays;
+and `dgl.ndarray.array(arr, ctx=gpu)` (the id maps of partial message passing) is built with torch
+and wrapped through DLPack, because that library cannot allocate device memory either.
 """
 import ctypes
 import os
@@ -89,6 +91,30 @@ def _route_host_index():
             setattr(cls, name, host_ctx(fn))
 
 
+def _route_gpu_arrays():
+    """CPU-only libdgl: `dgl.ndarray.array(arr, ctx=gpu)` (the id maps of send_and_recv / pull,
+    python/dgl/runtime/spmv.py:180) would allocate through the library's absent CUDA device API.
+    Build the array with torch and hand it over zero-copy through DLPack instead
+    (DGLArrayFromDLPack needs no device API), the way every feature tensor already arrives."""
+    import numpy as np
+    import torch
+    from torch.utils import dlpack
+    from dgl import ndarray as nd
+    if getattr(nd.array, "_b200_routed", False):
+        return
+    ref_array = nd.array
+
+    def array(arr, ctx=nd.cpu(0)):
+        if ctx.device_type == 1:
+            return ref_array(arr, ctx)
+        if isinstance(arr, nd.NDArray):
+            arr = arr.asnumpy()
+        t = torch.as_tensor(np.ascontiguousarray(arr)).to(torch.device("cuda", ctx.device_id))
+        return nd.from_dlpack(dlpack.to_dlpack(t))
+    array._b200_routed = True
+    nd.array = array
+
+
 def install(libdgl=None):
     """register() + rebinding of an already imported `dgl.kernel` (a re-run of the reference's
     own `_init_api("dgl.kernel")`) + the host-index routing for a CPU-only libdgl. Returns the
@@ -101,6 +127,7 @@ def install(libdgl=None):
         _state["cpu_only_libdgl"] = not _libdgl_has_cuda()
     if _state["cpu_only_libdgl"]:
         _route_host_index()
+        _route_gpu_arrays()
     _state["installed"] = True
     return names
 

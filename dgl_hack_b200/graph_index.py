@@ -98,6 +98,7 @@ class GraphIndex(object):
                 self._handle, ctypes.c_void_p(et.data_ptr()), 64 if et.dtype == torch.int64 else 32,
                 int(num_types), _stream(self.device)))
         self.num_types = int(num_types)
+        self.__dict__.pop("_rel_segments", None)     # derived from the previous typing
 
     def get_csr_sorted_by_edge_type(self, transpose):
         """[ranges, ids, eids, types] int32 CUDA tensors, as Graph::GetCsrSortedByEdgeType

@@ -218,3 +218,36 @@ def peer_copy_sum(G, transpose, slot_bases, node_code, row_scale, out):
         check_call(LIB.DGLB200KernelPeerCopySum(G.handle, int(bool(transpose)), k, bases, *ptrs,
                                                 _stream(G)))
     del keep
+
+
+def dense_tf32x3(a, b, b_is_kn, bias, relu, c):
+    """Extension: c = a @ (b if b_is_kn else b.T) (+ bias) (ReLU) on the tensor cores at fp32
+    accuracy (DGLB200DenseTF32x3, csrc/gemm.cu: tcgen05 + TMEM + TMA, 3xTF32)."""
+    keep, ptrs = _keep(a, b, bias, c)
+    with torch.cuda.device(a.device):
+        s = ctypes.c_void_p(torch.cuda.current_stream(a.device).cuda_stream)
+        check_call(LIB.DGLB200DenseTF32x3(ptrs[0], ptrs[1], int(bool(b_is_kn)), ptrs[2],
+                                          int(bool(relu)), ptrs[3], s))
+    del keep
+
+
+def copy_sum_bf16(G, transpose, X, col_scale, row_scale, mean, out):
+    """Extension: copy_src + sum / mean over bf16 feature rows with fp32 accumulation
+    (DGLB200KernelCopySumBF16); X / out are torch.bfloat16 [rows, D], D % 8 == 0."""
+    keep, ptrs = _keep(X, col_scale, row_scale, out)
+    with torch.cuda.device(G.device):
+        check_call(LIB.DGLB200KernelCopySumBF16(G.handle, int(bool(transpose)), ptrs[0], ptrs[1],
+                                                ptrs[2], int(bool(mean)), ptrs[3], _stream(G)))
+    del keep
+
+
+def grouped_dense_tf32x3(a, b, b_is_kn, group_ptr, c):
+    """Extension: rows [group_ptr[g], group_ptr[g+1]) of a times b[g] (or b[g].T) -> c, on the
+    tensor cores (DGLB200GroupedDenseTF32x3); group_ptr = python list of len(b) + 1 offsets."""
+    keep, ptrs = _keep(a, b, c)
+    gp = (ctypes.c_int64 * len(group_ptr))(*[int(v) for v in group_ptr])
+    with torch.cuda.device(a.device):
+        s = ctypes.c_void_p(torch.cuda.current_stream(a.device).cuda_stream)
+        check_call(LIB.DGLB200GroupedDenseTF32x3(ptrs[0], ptrs[1], int(bool(b_is_kn)), gp,
+                                                 len(group_ptr) - 1, ptrs[2], s))
+    del keep

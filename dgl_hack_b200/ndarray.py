@@ -16,6 +16,7 @@ _DTYPES = {
     torch.float32: (2, 32), torch.float64: (2, 64), torch.float16: (2, 16),
     torch.int32: (0, 32), torch.int64: (0, 64), torch.uint8: (1, 8), torch.int8: (0, 8),
     torch.int16: (0, 16), torch.bool: (1, 8),
+    torch.bfloat16: (4, 16),   # kDLBfloat: accepted by the explicit bf16 entry points only
 }
 
 
@@ -33,8 +34,6 @@ class NDArray(object):
 
     def __init__(self, tensor):
         tensor = tensor.contiguous()
-        if tensor.dtype == torch.bfloat16:
-            raise _lib.DGLError("bfloat16 tensors are not supported by the fp32 kernels")
         self.tensor = tensor
         shape = tensor.shape
         nd = len(shape)

@@ -426,17 +426,29 @@ class RelGraphConv(nn.Module):
 
     def _typed_index(self, g, etypes):
         """GraphIndex with the typed adjacency for `etypes`, cached on the graph."""
-        key = (etypes.data_ptr(), etypes._version, tuple(etypes.shape), self.num_rels)
+        # the cache holds the tensor itself: its address cannot be handed to another tensor while
+        # the entry lives, so (identity, version) identifies the contents
         cache = g.gidx.__dict__.setdefault("_typed_cache", {})
-        if cache.get("key") != key:
+        if cache.get("etypes") is not etypes or cache.get("version") != etypes._version or \
+                cache.get("num_rels") != self.num_rels:
             g.gidx.set_edge_types(etypes, self.num_rels)
-            cache["key"] = key
+            cache.update(etypes=etypes, version=etypes._version, num_rels=self.num_rels)
         return g.gidx
 
     def _fused_ok(self, x):
         return (self.regularizer == "basis" and x.is_floating_point() and x.dim() == 2
                 and self.in_feat <= 128 and self.out_feat <= 128
                 and self.in_feat * self.out_feat <= 1024)
+
+    def _tc_ok(self, x):
+        """Wide layers (beyond the fused SIMT kernel), or B200_RGCN=tc: per-relation contraction
+        on the tensor cores (backend.rgcn_layer1_tc)."""
+        if not (self.regularizer == "basis" and x.is_floating_point() and x.dim() == 2):
+            return False
+        want = os.environ.get("B200_RGCN", "") == "tc" or not self._fused_ok(x)
+        return want and os.environ.get("B200_RGCN", "") != "udf" and \
+            self.in_feat % 4 == 0 and self.in_feat <= 256 and self.out_feat <= 256 and \
+            x.is_cuda and x.dtype == th.float32
 
     def forward(self, g, x, etypes, norm=None):
         assert g.is_homograph(), \
@@ -446,7 +458,10 @@ class RelGraphConv(nn.Module):
                 loop_message = self.loop_weight.index_select(0, x)
             else:
                 loop_message = th.matmul(x, self.loop_weight)
-        if self._fused_ok(x):
+        if self._tc_ok(x):
+            gidx = self._typed_index(g, etypes)
+            node_repr = B.rgcn_layer1_tc(gidx, x, self._relation_weight(), norm)
+        elif self._fused_ok(x):
             gidx = self._typed_index(g, etypes)
             if norm is None:
                 norm = x.new_ones((g.number_of_edges(), 1))

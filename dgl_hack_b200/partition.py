@@ -493,10 +493,13 @@ class PartitionedGraph(object):
         rs = dst_scale.detach().reshape(-1).contiguous() if dst_scale is not None else None
         cs_halo = None
         if cs_in is not None:
+            # keyed on the caller's tensor, which the cache keeps alive (an address alone could be
+            # recycled for another tensor with other contents)
             cache = self.__dict__.setdefault("_halo_scale", {})
-            key = (cs_in.data_ptr(), cs_in._version)
-            if key not in cache:
+            key = (id(src_scale), src_scale._version)
+            if cache.get("owner") is not src_scale or key not in cache:
                 cache.clear()
+                cache["owner"] = src_scale
                 h = cs_in.new_ones((max(part.n_halo, 1),))
                 if part.world > 1:
                     peer, part.peer = part.peer, None      # width 1: not a peer-push shape

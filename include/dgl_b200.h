@@ -241,8 +241,9 @@ int DGLB200GraphCreateFromTypedCSR(int64_t num_nodes, int64_t num_edges, int idx
  * unit graphs computes, for all relations at once, writing each receiving (relation, node) row
  * exactly once: row s of the output = the reduction over the in-edges of relation seg_type[s]
  * into node seg_dst[s]; (relation, node) pairs without edges have no row (the loop's outputs hold
- * the reducer identity there). Segments are ordered by (node, relation); inside one, edges are
- * reduced in the unit graph's own order (source ascending, edge id). Synchronises `stream` once
+ * the reducer identity there). Segments are ordered by (relation, node), so the rows of one
+ * relation are a contiguous slice; inside a segment, edges are reduced in the unit graph's own
+ * order (source ascending, edge id). Synchronises `stream` once
  * (the number of segments is needed on the host); free the handle with DGLB200GraphFree. */
 int DGLB200GraphCreateRelationSegments(DGLB200GraphHandle typed_graph, void* stream,
                                        DGLB200GraphHandle* out);
@@ -323,6 +324,46 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
                                const DGLB200Tensor* grad_er, DGLB200Tensor* grad_feat,
                                DGLB200Tensor* grad_attn_l, DGLB200Tensor* grad_attn_r,
                                void* stream);
+
+/* copy_src + sum / mean with bf16 FEATURE STORAGE and fp32 accumulation: a second, explicit
+ * precision tier (north_star: 1e-2 relative in bf16). The reference kernels are fp32-only
+ * (DGL_DTYPE_SWITCH, src/kernel/common.h:49-55), so this has no reference PackedFunc; it halves
+ * the gathered bytes per edge. in_data / out_data are bfloat16 (DLPack code 4, 16 bits) [rows, D]
+ * with D % 8 == 0 (pad the storage; 16-byte loads of 8 features), float32 tensors are rejected,
+ * never converted silently. transpose = 0: out[v] = row_scale[v] * (1 / max(deg v, 1) if mean) *
+ * sum_{u -> v} col_scale[u] * in[u] over the (src, edge id)-ordered in-CSR; transpose = 1: the
+ * same over the out-CSR (the gradient). Scales are float32 vectors or NULL. Sums are accumulated
+ * in fp32 in a fixed order (deterministic) and rounded to bf16 once. */
+int DGLB200KernelCopySumBF16(DGLB200GraphHandle graph, int transpose, const DGLB200Tensor* in_data,
+                             const DGLB200Tensor* col_scale, const DGLB200Tensor* row_scale,
+                             int mean, DGLB200Tensor* out_data, void* stream);
+
+/* The dense projection either side of the aggregation -- GraphConv's `feat @ weight`
+ * (python/dgl/nn/pytorch/conv/graphconv.py:144-176), SAGEConv's fc_self / fc_neigh
+ * (sageconv.py:150-160), GATConv's fc (gatconv.py:125-144) -- which the reference leaves to
+ * cuBLAS' fp32 SIMT GEMM. Hand-written sm_100a kernel (csrc/gemm.cu): TMA-staged SWIZZLE_128B
+ * operand tiles, tcgen05.mma kind::tf32 into TMEM accumulators, error-compensated 3xTF32
+ * (a_hi.b_hi + a_hi.b_lo + a_lo.b_hi) so the result stays within ~1e-6 of the fp32 product
+ * relative to sum|a||b| (plain TF32: 3e-4), bias / ReLU fused into the TMEM read-out.
+ *   c[M, N] = a[M, K] . B (+ bias[N]) (ReLU);  b_is_kn != 0: B = b[K, N];  b_is_kn == 0: B = b[N, K]^T
+ * (the second form is the gradient w.r.t. the input, grad_a = grad_c . W^T with b = W).
+ * fp32 compact row-major tensors on one CUDA device; N <= 256, K % 4 == 0, a 16-byte aligned;
+ * other shapes are rejected (callers fall back to the library GEMM). bias may be NULL. */
+int DGLB200DenseTF32x3(const DGLB200Tensor* a, const DGLB200Tensor* b, int b_is_kn,
+                       const DGLB200Tensor* bias, int relu, DGLB200Tensor* c, void* stream);
+
+/* The dense PER-RELATION weight contraction of RGCN on the tensor cores (north_star (c); the
+ * reference's RgcnLayer1 kernels contract per edge with CUDA-core FMAs and atomics,
+ * src/kernel/cuda/binary_reduce_impl.cu:1082-1117, 1157-1194): rows [group_ptr[g],
+ * group_ptr[g+1]) of a[M, K] are multiplied by b[g] ([groups, K, N] if b_is_kn, else
+ * [groups, N, K] read transposed) into c[M, N]; same kernel and 3xTF32 arithmetic as
+ * DGLB200DenseTF32x3, with a tile -> (rows, group) table. With the relation-segment graph the
+ * RGCN layer is: per-(relation, node) sums (one SpMM launch) -> this contraction -> segment ->
+ * node reduction. group_ptr is a HOST array of groups + 1 ascending row offsets from 0 to M.
+ * Synchronises `stream` once when groups > 1 (the tile table is built on the host). */
+int DGLB200GroupedDenseTF32x3(const DGLB200Tensor* a, const DGLB200Tensor* b, int b_is_kn,
+                              const int64_t* group_ptr, int groups, DGLB200Tensor* c,
+                              void* stream);
 
 /* Uniform neighbour sampling on the device: dgl.sampling.sample_neighbors(g, seeds, fanout,
  * replace) / dgl.in_subgraph(g, seeds) (python/dgl/sampling/neighbor.py, used by

@@ -145,12 +145,12 @@ def test_relation_segments_at_am_like_skew():
     ety = rs.choice(r, e, p=p / p.sum())
     g = B.GraphIndex.from_coo_with_type(n, src, dst, ety, r, "cuda:0")
     sg, seg_dst, seg_type = g.relation_segments()
-    pairs = np.unique(dst.astype(np.int64) * r + ety)
+    pairs = np.unique(ety.astype(np.int64) * n + dst)
     assert sg.num_dst == len(pairs) and sg.num_src == n and sg.number_of_edges() == e
-    got_pairs = (seg_dst * r + seg_type).cpu().numpy()
-    assert np.array_equal(got_pairs, pairs)          # ordered by (node, relation), each once
+    got_pairs = (seg_type * n + seg_dst).cpu().numpy()
+    assert np.array_equal(got_pairs, pairs)          # ordered by (relation, node), each once
     x = torch.from_numpy(rs.randint(-3, 4, (n, 16)).astype(np.float32)).cuda()
     out = F.copy_reduce("sum", sg, 0, x, sg.num_dst)
-    key = torch.from_numpy(np.searchsorted(pairs, dst.astype(np.int64) * r + ety)).cuda()
+    key = torch.from_numpy(np.searchsorted(pairs, ety.astype(np.int64) * n + dst)).cuda()
     want = torch.zeros_like(out).index_add_(0, key, x[torch.from_numpy(src).cuda()])
     assert torch.equal(out, want)
