@@ -405,10 +405,15 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.empty_cache()
         from bench_partitioned import run_partitioned
         l1 = K.launch_count()
-        partitioned = run_partitioned(rank, world, dev, scale=args.scale, steps=args.steps,
-                                      warmup=args.warmup)
-        if partitioned is not None:
-            partitioned["gpu_launches_rank0"] = K.launch_count() - l1
+        try:
+            partitioned = run_partitioned(rank, world, dev, scale=args.scale, steps=args.steps,
+                                          warmup=args.warmup)
+            if partitioned is not None:
+                partitioned["gpu_launches_rank0"] = K.launch_count() - l1
+        except Exception as ex:  # the headline line must still be printed; the failure is reported
+            import traceback
+            partitioned = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:500]),
+                           "traceback_tail": traceback.format_exc()[-1500:], "n_gpus": world}
 
     if rank == 0:
         ms_step = ms_total / args.steps

@@ -129,6 +129,7 @@ SYMBOLS = {
                                             _c.c_int, TensorP, _c.c_void_p]),
     "DGLB200DenseTF32x3": (_c.c_int, [TensorP, TensorP, _c.c_int, TensorP, _c.c_int, TensorP,
                                       _c.c_void_p]),
+    "DGLB200DenseTF32x3WeightGrad": (_c.c_int, [TensorP, TensorP, TensorP, _c.c_void_p]),
     "DGLB200GroupedDenseTF32x3": (_c.c_int, [TensorP, TensorP, _c.c_int, _c.c_void_p, _c.c_int,
                                              TensorP, _c.c_void_p]),
     "DGLB200RegisterInto": (_c.c_int, [_c.c_void_p]),

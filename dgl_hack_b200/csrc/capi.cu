@@ -880,6 +880,33 @@ int DGLB200DenseTF32x3(const DGLB200Tensor* a, const DGLB200Tensor* b, int b_is_
   API_END();
 }
 
+int DGLB200DenseTF32x3WeightGrad(const DGLB200Tensor* a, const DGLB200Tensor* g, DGLB200Tensor* c,
+                                 void* stream) {
+  API_BEGIN();
+  B200_CHECK(a && g && c, "NULL argument");
+  for (const DGLB200Tensor* t : {a, g, (const DGLB200Tensor*)c}) {
+    check_float(t, "dense operand");
+    check_compact(t, "dense operand");
+    B200_CHECK(t->ndim == 2, "DenseTF32x3WeightGrad: operands must be 2-D");
+    B200_CHECK(t->ctx.device_type == 2 && t->ctx.device_id == a->ctx.device_id,
+               "DenseTF32x3WeightGrad: operands must live on one CUDA device");
+  }
+  const int64_t M = a->shape[0], Kf = a->shape[1], N = g->shape[1];
+  B200_CHECK(g->shape[0] == M, "DenseTF32x3WeightGrad: a and g need the same number of rows");
+  B200_CHECK(c->shape[0] == Kf && c->shape[1] == N, "DenseTF32x3WeightGrad: output must be [K, N]");
+  if (Kf == 0 || N == 0) return 0;
+  B200_CUDA(cudaSetDevice(a->ctx.device_id));
+  if (M == 0) {
+    fill_f32(data_ptr<float>(c), Kf * N, 0.f, static_cast<cudaStream_t>(stream));
+    return 0;
+  }
+  B200_CHECK(gemm_tn_tf32x3_supported(M, Kf, N, data_ptr<const float>(a), data_ptr<const float>(g)),
+             "DenseTF32x3WeightGrad: needs K, N <= 256 and divisible by 4, 16-byte aligned operands");
+  gemm_tn_tf32x3(data_ptr<const float>(a), data_ptr<const float>(g), data_ptr<float>(c), M, Kf, N,
+                 static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
 int DGLB200GroupedDenseTF32x3(const DGLB200Tensor* a, const DGLB200Tensor* b, int b_is_kn,
                               const int64_t* group_ptr, int groups, DGLB200Tensor* c,
                               void* stream) {

@@ -301,6 +301,9 @@ bool gemm_tf32x3_supported(int64_t M, int64_t N, int64_t K, const float* A, int6
 void gemm_tf32x3(const float* A, int64_t lda, const float* B, int b_is_kn, const float* bias,
                  int relu, float* C, int64_t ldc, int64_t M, int64_t N, int64_t K, int groups,
                  const int64_t* group_ptr, cudaStream_t s);
+bool gemm_tn_tf32x3_supported(int64_t M, int64_t Kf, int64_t N, const float* A, const float* G);
+void gemm_tn_tf32x3(const float* A, const float* G, float* C, int64_t M, int64_t Kf, int64_t N,
+                    cudaStream_t s);
 // spmm_bf16.cu: copy + sum / mean over bf16 feature rows (pitch D elements, D % 8 == 0)
 void spmm_bf16(DGLB200Graph* g, int transpose, const void* in, const float* col_scale,
                const float* row_scale, int mean, void* out, int64_t D, cudaStream_t s);

@@ -312,6 +312,198 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a,
 }
 
 
+// ---------------------------------------------------------------------------------------------
+// Weight gradient  C[Kf, N] = A[M, Kf]^T . G[M, N]  (A = layer input, G = grad of the output):
+// the contraction runs over the LONG dimension M, so both operands are MN-major for the tensor
+// core (their contiguous dimension is the MMA's M / N, not K). Shared-memory image of a stage
+// (kTnRows = 16 rows of A and G): one TMA box [16 rows x 32 floats] per 32-column block,
+// SWIZZLE_128B, blocks 2 KB apart = canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte
+// units with LBO = 2048 B (next 32-column block), SBO = 1024 B (next 8 rows). Each CTA owns a
+// contiguous chunk of rows, accumulates a full [Kf, N] partial in TMEM (Kf/128 accumulators of
+// N columns), writes it to scratch; gemm_tn_fold_kernel adds the partials in CTA order
+// (deterministic). Both operands are big, so both are split hi / lo in the kernel.
+constexpr int kTnRows = 16;
+constexpr int kTnBoxBytes = kTnRows * 128;  // 2 KB
+
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(const void* tile) {
+  return (uint64_t)((smem_u32(tile) & 0x3FFFF) >> 4) | ((uint64_t)(kTnBoxBytes >> 4) << 16) |
+         (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+struct GemmTnArgs {
+  int M, Kf, N, Npad;       // Npad = N rounded up to 16 (UMMA N)
+  int a_blocks, g_blocks;   // 32-column blocks of A (Kf padded to 128) and of G
+  int m_tiles;              // Kf / 128 rounded up
+  int rows_per_cta, stages;
+  uint32_t stage_bytes, a_bytes, g_bytes, tmem_cols;
+  float* partial;           // [gridDim.x, m_tiles * 128, Npad]
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tn_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a,
+                      const __grid_constant__ CUtensorMap map_g, const GemmTnArgs g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const int S = g.stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)S * g.stage_bytes);
+  uint64_t *full = bars, *split = bars + S, *empty = bars + 2 * S, *acc_full = bars + 3 * S;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * S + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(split + s, 128);
+      mbar_init(empty + s, 1);
+    }
+    mbar_init(acc_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  } else if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_slot)),
+                 "r"(g.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int64_t row_beg = (int64_t)blockIdx.x * g.rows_per_cta;
+  const int64_t row_end = min(row_beg + (int64_t)g.rows_per_cta, (int64_t)g.M);
+  const int n_steps = row_end > row_beg ? (int)((row_end - row_beg + kTnRows - 1) / kTnRows) : 0;
+  // stage: A (raw -> hi) | A_lo | G (raw -> hi) | G_lo
+  auto stage_ptr = [&](int s) { return smem + (size_t)s * g.stage_bytes; };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t phase = 0;
+      for (int it = 0; it < n_steps; ++it) {
+        mbar_wait(empty + s, phase ^ 1);
+        uint8_t* st = stage_ptr(s);
+        mbar_arrive_expect_tx(full + s, g.a_bytes + g.g_bytes);
+        const int r0 = (int)(row_beg + (int64_t)it * kTnRows);
+        // rows past this CTA's chunk belong to the next CTA: they are zeroed by the splitter
+        for (int j = 0; j < g.a_blocks; ++j)
+          tma_load_2d(&map_a, full + s, st + j * kTnBoxBytes, j * 32, r0);
+        for (int j = 0; j < g.g_blocks; ++j)
+          tma_load_2d(&map_g, full + s, st + 2 * g.a_bytes + j * kTnBoxBytes, j * 32, r0);
+        if (++s == S) { s = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // D = F32, A = B = TF32, BOTH MN-major (bits 15, 16), N = Npad, M = 128
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) |
+                           ((uint32_t)(g.Npad >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+    int s = 0;
+    uint32_t phase = 0;
+    for (int it = 0; it < n_steps; ++it) {
+      mbar_wait(split + s, phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (lane == 0) {
+        uint8_t* st = stage_ptr(s);
+        for (int mt = 0; mt < g.m_tiles; ++mt) {
+          const uint32_t tmem_d = tmem_base + (uint32_t)(mt * g.Npad);
+          const uint8_t* a_hi_p = st + (size_t)mt * 4 * kTnBoxBytes;  // 128 columns = 4 blocks
+          const uint64_t a_hi = umma_desc_mn_sw128(a_hi_p);
+          const uint64_t a_lo = umma_desc_mn_sw128(a_hi_p + g.a_bytes);
+          const uint64_t g_hi = umma_desc_mn_sw128(st + 2 * g.a_bytes);
+          const uint64_t g_lo = umma_desc_mn_sw128(st + 2 * g.a_bytes + g.g_bytes);
+#pragma unroll
+          for (int k = 0; k < kTnRows / kUmmaK; ++k) {
+            const uint64_t adv = (uint64_t)(k * 1024 >> 4);  // next 8 rows = SBO
+            umma_tf32(tmem_d, a_lo + adv, g_hi + adv, idesc, (it | k) != 0);
+            umma_tf32(tmem_d, a_hi + adv, g_lo + adv, idesc, 1);
+            umma_tf32(tmem_d, a_hi + adv, g_hi + adv, idesc, 1);
+          }
+        }
+        umma_commit(empty + s);
+        if (it == n_steps - 1) umma_commit(acc_full);
+      }
+      __syncwarp();
+      if (++s == S) { s = 0; phase ^= 1; }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    const int t = threadIdx.x - 128;
+    int s = 0;
+    uint32_t phase = 0;
+    for (int it = 0; it < n_steps; ++it) {
+      mbar_wait(full + s, phase);
+      const int64_t r0 = row_beg + (int64_t)it * kTnRows;
+      const int valid = (int)min((int64_t)kTnRows, row_end - r0);  // rows of this CTA's chunk
+      for (int part = 0; part < 2; ++part) {
+        uint8_t* base = stage_ptr(s) + (part ? 2 * g.a_bytes : 0);
+        const uint32_t bytes = part ? g.g_bytes : g.a_bytes;
+        uint4* hi = reinterpret_cast<uint4*>(base);
+        uint4* lo = reinterpret_cast<uint4*>(base + bytes);
+        for (uint32_t idx = t; idx < bytes / 16; idx += 128) {
+          // 16-byte chunk idx: box = idx / 128, row inside the box = (idx % 128) / 8
+          const int row = (int)((idx & 127) >> 3);
+          uint4 v = hi[idx], h, l;
+          if (row >= valid) v = make_uint4(0, 0, 0, 0);
+          h.x = v.x & 0xffffe000u; h.y = v.y & 0xffffe000u;
+          h.z = v.z & 0xffffe000u; h.w = v.w & 0xffffe000u;
+          l.x = __float_as_uint(__fsub_rn(__uint_as_float(v.x), __uint_as_float(h.x)));
+          l.y = __float_as_uint(__fsub_rn(__uint_as_float(v.y), __uint_as_float(h.y)));
+          l.z = __float_as_uint(__fsub_rn(__uint_as_float(v.z), __uint_as_float(h.z)));
+          l.w = __float_as_uint(__fsub_rn(__uint_as_float(v.w), __uint_as_float(h.w)));
+          hi[idx] = h;
+          lo[idx] = l;
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      mbar_arrive(split + s);
+      if (++s == S) { s = 0; phase ^= 1; }
+    }
+  } else if (warp >= 8) {
+    const int q = warp & 3;
+    float* pbase = g.partial + (size_t)blockIdx.x * g.m_tiles * kBM * g.Npad;
+    if (n_steps > 0) {
+      mbar_wait(acc_full, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    for (int mt = 0; mt < g.m_tiles; ++mt) {
+      float* prow = pbase + (size_t)(mt * kBM + q * 32 + lane) * g.Npad;
+      for (int c0 = 0; c0 < g.Npad; c0 += 16) {
+        uint32_t v[16];
+        if (n_steps > 0) {
+          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(mt * g.Npad + c0), v);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = 0;
+        }
+#pragma unroll
+        for (int j = 0; j < 16; j += 4)
+          *reinterpret_cast<uint4*>(prow + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 2) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"(g.tmem_cols)
+                 : "memory");
+  }
+}
+
+// C[i, j] = sum over CTAs (in CTA order) of partial[b][i][j]
+__global__ void gemm_tn_fold_kernel(const float* __restrict__ partial, int n_parts, int rows_pad,
+                                    int Npad, int Kf, int N, float* __restrict__ C) {
+  const int64_t total = (int64_t)Kf * N;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / N), cidx = (int)(i - (int64_t)r * N);
+    float acc = 0.f;
+    for (int b = 0; b < n_parts; ++b)
+      acc = __fadd_rn(acc, __ldg(partial + ((size_t)b * rows_pad + r) * Npad + cidx));
+    C[i] = acc;
+  }
+}
+
 // Bsplit[0][n][k] = hi(Bt[n][k]), Bsplit[1][n][k] = Bt[n][k] - hi; rows N..Npad-1 are zero.
 // b_is_kn: the caller's matrix is W[K, N] row-major (Y = X.W), read transposed; otherwise it
 // is Bt[N, K] row-major (Y = X.Bt^T, e.g. grad_X = grad_Y.W^T with Bt = W).
@@ -371,6 +563,53 @@ CUtensorMap make_map(const float* base, int64_t rows, int64_t cols, int64_t ld, 
 }
 
 }  // namespace
+
+bool gemm_tn_tf32x3_supported(int64_t M, int64_t Kf, int64_t N, const float* A, const float* G) {
+  return M >= 1 && M < (1ll << 31) && Kf >= 1 && Kf <= 256 && N >= 1 && N <= 256 && Kf % 4 == 0 &&
+         N % 4 == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0 &&
+         (reinterpret_cast<uintptr_t>(G) & 15) == 0;
+}
+
+// C[Kf, N] = A[M, Kf]^T . G[M, N], all compact row-major fp32 (the weight gradient of Y = X.W)
+void gemm_tn_tf32x3(const float* A, const float* G, float* C, int64_t M, int64_t Kf, int64_t N,
+                    cudaStream_t s) {
+  B200_CHECK(gemm_tn_tf32x3_supported(M, Kf, N, A, G),
+             "gemm_tn_tf32x3: needs Kf, N <= 256 and divisible by 4, 16-byte aligned operands");
+  GemmTnArgs g;
+  g.M = (int)M; g.Kf = (int)Kf; g.N = (int)N;
+  g.Npad = (int)((N + 15) / 16 * 16);
+  g.m_tiles = (int)((Kf + kBM - 1) / kBM);
+  g.a_blocks = g.m_tiles * 4;
+  g.g_blocks = (g.Npad + 31) / 32;
+  g.a_bytes = (uint32_t)g.a_blocks * kTnBoxBytes;
+  g.g_bytes = (uint32_t)g.g_blocks * kTnBoxBytes;
+  g.stage_bytes = 2 * (g.a_bytes + g.g_bytes);
+  g.stages = (int)std::max<uint32_t>(2, std::min<uint32_t>(8, (200u * 1024) / g.stage_bytes));
+  g.tmem_cols = 32;
+  while (g.tmem_cols < (uint32_t)(g.m_tiles * g.Npad)) g.tmem_cols <<= 1;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = (int)std::min<int64_t>(sms, (M + kTnRows - 1) / kTnRows);
+  g.rows_per_cta = (int)(((M + grid - 1) / grid + kTnRows - 1) / kTnRows * kTnRows);
+  Scratch partial((size_t)grid * g.m_tiles * kBM * g.Npad * 4, s);
+  g.partial = partial.as<float>();
+  const CUtensorMap map_a = make_map(A, M, Kf, Kf, kTnRows);
+  const CUtensorMap map_g = make_map(G, M, N, N, kTnRows);
+  const size_t smem = (size_t)g.stages * g.stage_bytes + (3 * g.stages + 2) * 8 + 16 + 1024;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    cudaFuncSetAttribute(gemm_tn_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         227 * 1024);
+  });
+  gemm_tn_tf32x3_kernel<<<grid, kThreads, smem, s>>>(map_a, map_g, g);
+  B200_CUDA(cudaGetLastError());
+  const int64_t tot = Kf * N;
+  gemm_tn_fold_kernel<<<(int)std::min<int64_t>((tot + 255) / 256, 592), 256, 0, s>>>(
+      partial.as<float>(), grid, g.m_tiles * kBM, g.Npad, (int)Kf, (int)N, C);
+  B200_CUDA(cudaGetLastError());
+  note_kernel("gemm_tn_tf32x3", 2);
+}
 
 bool gemm_tf32x3_supported(int64_t M, int64_t N, int64_t K, const float* A, int64_t lda) {
   return M >= 1 && N >= 1 && N <= 256 && K >= 1 && K <= 65536 && lda % 4 == 0 && lda >= K &&

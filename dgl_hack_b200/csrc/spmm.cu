@@ -131,6 +131,33 @@ __global__ void compose_ids_kernel(const int32_t* __restrict__ map,
     out[k] = map[to_other[k]];
 }
 
+// out[r, c] = in[r, c] for c < cols (row pitches ld_in / ld_out), 0 for cols <= c < ld_out:
+// re-pitches rows (pad to a 16-byte multiple, or drop the padding again)
+__global__ void repitch_rows_kernel(const float* __restrict__ in, int64_t ld_in,
+                                    float* __restrict__ out, int64_t ld_out, int64_t rows,
+                                    int64_t cols) {
+  const int64_t total = rows * ld_out;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t r = i / ld_out, cidx = i - r * ld_out;
+    out[i] = cidx < cols ? __ldg(in + r * ld_in + cidx) : 0.f;
+  }
+}
+
+static void repitch_rows(const float* in, int64_t ld_in, float* out, int64_t ld_out, int64_t rows,
+                         int64_t cols, cudaStream_t s) {
+  if (rows <= 0) return;
+  const int blocks = (int)std::min<int64_t>((rows * ld_out + 255) / 256, 148 * 32);
+  repitch_rows_kernel<<<blocks, 256, 0, s>>>(in, ld_in, out, ld_out, rows, cols);
+  note_kernel(nullptr, 1);
+}
+
+// B200_SPMM_PAD=0 keeps odd widths on the scalar-load kernels (A/B runs).
+static bool pad_enabled() {
+  const char* e = std::getenv("B200_SPMM_PAD");
+  return !(e && e[0] == '0');
+}
+
 // Describes how the narrow operand lines up against the D-wide one. Returns kBNone on "cannot".
 static int classify_b(const Bcast& bc, bool b_is_lhs, int* b_width, int* head_div) {
   const int* bs = b_is_lhs ? bc.lhs_shape : bc.rhs_shape;
@@ -287,6 +314,35 @@ bool try_spmm(const KernelCall& c) {
   const bool maps_index_out_csr = (c.mode == kFwd);
   if (a_tgt == row_tgt) return false;  // A must be gathered per edge
   if (csr.n_rows >= (1ll << 31) || E >= (1ll << 31)) return false;
+
+  // ---- odd widths: rows whose pitch is not a multiple of 16 bytes (D = 47: 188-byte rows) can
+  // only be gathered with 4-byte loads (0.41 of the HBM peak at the products shape against 0.8 at
+  // D = 48). Gather from a zero-padded copy with 16-byte rows instead and drop the padding from
+  // the result: two streaming passes over N x D against the E x D gather.
+  if (D % 4 != 0 && D >= 8 && c.bc.ndim == 1 && (bmode == kBNone || bmode == kBScalar) &&
+      !c.a_tab && pad_enabled() && forced_path() != 2 && E >= 4 * csr.n_cols) {
+    const int64_t Dp = (D + 3) / 4 * 4;
+    const int which = c.mode != kFwd ? 2 : (A == c.lhs ? 0 : 1);
+    const int64_t a_rows = which == 2 ? c.out_rows : (which == 0 ? c.lhs_rows : c.rhs_rows);
+    Scratch a_pad((size_t)std::max<int64_t>(a_rows, 1) * Dp * 4, s);
+    Scratch o_pad((size_t)std::max<int64_t>(c.dst_rows, 1) * Dp * 4, s);
+    repitch_rows(A, D, a_pad.as<float>(), Dp, a_rows, D, s);
+    KernelCall c2 = c;
+    if (which == 0) c2.lhs = a_pad.as<float>();
+    else if (which == 1) c2.rhs = a_pad.as<float>();
+    else c2.gout = a_pad.as<float>();
+    c2.dst = o_pad.as<float>();
+    auto widen = [&](int* shape, int64_t* len) {
+      if (*len == D) { shape[0] = (int)Dp; *len = Dp; }
+    };
+    widen(c2.bc.lhs_shape, &c2.bc.lhs_len);
+    widen(c2.bc.rhs_shape, &c2.bc.rhs_len);
+    widen(c2.bc.out_shape, &c2.bc.out_len);
+    if (try_spmm(c2)) {
+      repitch_rows(o_pad.as<float>(), Dp, c.dst, D, c.dst_rows, D, s);
+      return true;
+    }
+  }
 
   // ---- vector width from divisibility and pointer alignment
   auto aligned = [](const void* p, int bytes) {

@@ -184,9 +184,23 @@ def tc_gemm(a, b, b_is_kn=True, bias=None, relu=False):
     return c
 
 
+def tc_weight_grad(a, g):
+    """a.T @ g ([M, K], [M, N] -> [K, N]): the library GEMM by default; B200_DENSE_WGRAD=tc = the
+    own MN-major tcgen05 kernel (csrc/gemm.cu gemm_tn_tf32x3_kernel; under validation, opt-in)."""
+    from . import kernel as K
+    a, g = a.contiguous(), g.contiguous()
+    k, n = a.shape[1], g.shape[1]
+    if os.environ.get("B200_DENSE_WGRAD", "lib") != "tc" or k > 256 or n > 256 or k % 4 or n % 4 \
+            or a.shape[0] == 0 or a.data_ptr() % 16 or g.data_ptr() % 16:
+        return a.t() @ g
+    c = torch.empty((k, n), dtype=torch.float32, device=a.device)
+    K.dense_tf32x3_weight_grad(a, g, c)
+    return c
+
+
 class _TcMatMul(torch.autograd.Function):
     """a @ b on the own kernel; grad_a = g @ b.T on the same kernel (b read as [N', K']);
-    grad_b = a.T @ g reduces over the long dimension (MN-major operands): library GEMM."""
+    grad_b = a.T @ g reduces over the long dimension: the MN-major kernel (tc_weight_grad)."""
 
     @staticmethod
     def forward(ctx, a, b):
@@ -197,7 +211,7 @@ class _TcMatMul(torch.autograd.Function):
     def backward(ctx, g):
         a, b = ctx.saved_tensors
         ga = tc_gemm(g.contiguous(), b, False) if ctx.needs_input_grad[0] else None
-        gb = a.t() @ g if ctx.needs_input_grad[1] else None
+        gb = tc_weight_grad(a, g) if ctx.needs_input_grad[1] else None
         return ga, gb
 
 
@@ -219,7 +233,7 @@ class _TcLinear(torch.autograd.Function):
         if ctx.relu:
             g = g * (y > 0)
         ga = tc_gemm(g, w, False) if ctx.needs_input_grad[0] else None
-        gw = a.t() @ g if ctx.needs_input_grad[1] else None
+        gw = tc_weight_grad(a, g) if ctx.needs_input_grad[1] else None
         gb = g.sum(0) if ctx.needs_input_grad[2] else None
         return ga, gw, gb, None
 

@@ -251,3 +251,12 @@ def grouped_dense_tf32x3(a, b, b_is_kn, group_ptr, c):
         check_call(LIB.DGLB200GroupedDenseTF32x3(ptrs[0], ptrs[1], int(bool(b_is_kn)), gp,
                                                  len(group_ptr) - 1, ptrs[2], s))
     del keep
+
+
+def dense_tf32x3_weight_grad(a, g, c):
+    """Extension: c[K, N] = a[M, K].T @ g[M, N] on the tensor cores (DGLB200DenseTF32x3WeightGrad)."""
+    keep, ptrs = _keep(a, g, c)
+    with torch.cuda.device(a.device):
+        s = ctypes.c_void_p(torch.cuda.current_stream(a.device).cuda_stream)
+        check_call(LIB.DGLB200DenseTF32x3WeightGrad(ptrs[0], ptrs[1], ptrs[2], s))
+    del keep

@@ -352,6 +352,14 @@ int DGLB200KernelCopySumBF16(DGLB200GraphHandle graph, int transpose, const DGLB
 int DGLB200DenseTF32x3(const DGLB200Tensor* a, const DGLB200Tensor* b, int b_is_kn,
                        const DGLB200Tensor* bias, int relu, DGLB200Tensor* c, void* stream);
 
+/* Weight gradient of the dense projection, c[K, N] = a[M, K]^T . g[M, N] (a = the layer's
+ * input, g = the gradient of its output), same tensor-core arithmetic (3xTF32, fp32 accumulate in
+ * TMEM). The contraction runs over the long dimension, so both operands are MN-major; every CTA
+ * accumulates a full [K, N] partial over its chunk of rows and the partials are added in a fixed
+ * order (deterministic). K, N <= 256 and divisible by 4; 16-byte aligned. */
+int DGLB200DenseTF32x3WeightGrad(const DGLB200Tensor* a, const DGLB200Tensor* g, DGLB200Tensor* c,
+                                 void* stream);
+
 /* The dense PER-RELATION weight contraction of RGCN on the tensor cores (north_star (c); the
  * reference's RgcnLayer1 kernels contract per edge with CUDA-core FMAs and atomics,
  * src/kernel/cuda/binary_reduce_impl.cu:1082-1117, 1157-1194): rows [group_ptr[g],

@@ -35,6 +35,8 @@ def timeit(fn, reps=20, warm=3):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--wgrad", action="store_true",
+                    help="also check the MN-major weight-gradient kernel (B200_DENSE_WGRAD=tc)")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     torch.backends.cuda.matmul.allow_tf32 = False
@@ -84,6 +86,33 @@ def main():
         rows.append(row)
         print(json.dumps(row), flush=True)
         del a, b, got
+    # ---- weight gradient  c[K, N] = a[M, K].T @ g[M, N]  (MN-major kernel, split over row chunks)
+    wshapes = [(20, 8, 8), (5000, 100, 256), (4097, 256, 48), (100001, 256, 256), (300, 132, 20)]
+    if not args.quick:
+        wshapes += [(1 << 20, 256, 256), (1 << 20, 100, 256), (2449029, 256, 48)]
+    if args.wgrad:
+        os.environ["B200_DENSE_WGRAD"] = "tc"
+    for M, K, N in (wshapes if args.wgrad else []):
+        a = torch.rand(M, K, generator=gen, device=DEV) * 2 - 1
+        gg = torch.rand(M, N, generator=gen, device=DEV) * 2 - 1
+        got = dense.tc_weight_grad(a, gg)
+        torch.cuda.synchronize()
+        want = torch.zeros(K, N, dtype=torch.float64, device=DEV)
+        scale = torch.zeros(K, N, dtype=torch.float64, device=DEV)
+        for r0 in range(0, M, 1 << 18):      # fp64 in slabs (memory)
+            sl = slice(r0, min(M, r0 + (1 << 18)))
+            want += a[sl].double().t() @ gg[sl].double()
+            scale += a[sl].abs().double().t() @ gg[sl].abs().double()
+        err = ((got.double() - want).abs() / scale.clamp(min=1e-30)).max().item()
+        err32 = (((a.t() @ gg).double() - want).abs() / scale.clamp(min=1e-30)).max().item()
+        row = {"op": "weight_grad", "M": M, "K": K, "N": N, "err_tf32x3": err,
+               "err_torch_fp32": err32}
+        if M >= (1 << 20):
+            row["ms_tf32x3"] = round(timeit(lambda: dense.tc_weight_grad(a, gg)), 4)
+            row["ms_torch_fp32"] = round(timeit(lambda: a.t() @ gg, reps=5), 4)
+        rows.append(row)
+        print(json.dumps(row), flush=True)
+        del a, gg
     worst = max(max(r["err_tf32x3"], r.get("err_tf32x3_tail", 0.0)) for r in rows)
     print(json.dumps({"worst_err_tf32x3": worst, "ok": worst <= 1e-5}))
     if args.out:
