@@ -108,6 +108,7 @@ SYMBOLS = {
                                         _c.c_void_p, _c.c_void_p, _c.POINTER(_c.c_int64)]),
     "DGLB200GatAttnProj": (_c.c_int, [TensorP] * 5 + [_c.c_void_p]),
     "DGLB200GatAttnProjBackward": (_c.c_int, [TensorP] * 8 + [_c.c_void_p]),
+    "DGLB200GatAttnProjBackwardNoAlloc": (_c.c_int, [TensorP] * 8 + [_c.c_void_p]),
     "DGLB200SampleCounts": (_c.c_int, [GraphHandle, _c.c_void_p, _c.c_int64, _c.c_int, _c.c_int,
                                        _c.c_void_p, _c.c_void_p]),
     "DGLB200SampleNeighbors": (_c.c_int, [GraphHandle, _c.c_void_p, _c.c_int64, _c.c_int, _c.c_int,

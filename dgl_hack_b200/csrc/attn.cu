@@ -11,6 +11,9 @@
 // writes 4*N*D. No atomics: the reduction over nodes is two-stage with a fixed fold order.
 #include <algorithm>
 
+#include <mutex>
+#include <string>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -238,6 +241,72 @@ void attn_proj_backward(const float* feat, const float* al, const float* ar, con
                                                               (int)D);
   B200_CUDA(cudaGetLastError());
   note_kernel("attn_proj_bwd", 2);
+}
+
+// ---------------------------------------------------------------- no-allocation variant
+// attn_proj_backward for callers that may not allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc): the block partials live in a file-scope device array instead
+// of a stream-ordered Scratch buffer. Limits: H * F <= kStaticMaxD and at most kStaticMaxBlocks
+// row blocks (the B200's 148 SMs x 5 = 740 fit, so the blocking -- and with it every sum order --
+// is the one attn_proj_backward uses there: results are bit-identical). The array is
+// kStaticMaxBlocks x 2 x kStaticMaxD floats = 3 MiB, held by every GPU that loads the library.
+// ALL calls on a device share it: two calls that overlap on the GPU (different streams) race.
+// Nothing has to start at zero: the backward kernel overwrites every partial the fold reads.
+constexpr int kStaticMaxBlocks = 768;
+constexpr int kStaticMaxD = 512;
+static __device__ __align__(256) float g_attn_static_part[(size_t)kStaticMaxBlocks * 2 * kStaticMaxD];
+
+constexpr int kMaxDevices = 64;
+static float* g_static_part_addr[kMaxDevices];  // device address of the array, per device
+static std::mutex g_static_mu;
+
+// Device address of the array on `device` (which must be current). In host code the array's name
+// is only a host-side stand-in for the symbol: the kernels get the address cudaGetSymbolAddress
+// returns, looked up once per device.
+static float* static_part_on(int device) {
+  B200_CHECK(device >= 0 && device < kMaxDevices, "attn_proj (no-alloc): device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_part_addr[device]) {
+    float* ptr = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_attn_static_part));
+    B200_CHECK(ptr != nullptr, "attn_proj (no-alloc): cudaGetSymbolAddress returned NULL");
+    g_static_part_addr[device] = ptr;
+  }
+  return g_static_part_addr[device];
+}
+
+int64_t attn_proj_static_max_width() { return kStaticMaxD; }
+
+void attn_proj_backward_static(const float* feat, const float* al, const float* ar,
+                               const float* gl, const float* gr, float* gfeat, float* gal,
+                               float* gar, int64_t n, int64_t H, int64_t F, int device,
+                               cudaStream_t s) {
+  const int64_t D = H * F;
+  B200_CHECK(D >= 1 && D <= kStaticMaxD,
+             "attn_proj (no-alloc): H * F = " + std::to_string(D) + " exceeds the static scratch (" +
+                 std::to_string(kStaticMaxD) + " floats per row); use DGLB200GatAttnProjBackward");
+  int n_blocks = (int)std::min<int64_t>(std::max<int64_t>(n, 1), (int64_t)sm_count() * 5);
+  n_blocks = std::min(n_blocks, kStaticMaxBlocks);
+  const int rows = (int)((n + n_blocks - 1) / std::max(n_blocks, 1));
+  n_blocks = rows > 0 ? (int)((n + rows - 1) / rows) : 0;
+  float* part = static_part_on(device);
+  auto al16 = [](const void* p) { return !p || reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+  const bool vec = F % 4 == 0 && D / 4 <= kBwdVThreads / 2 && al16(feat) && al16(al) && al16(ar) &&
+                   al16(gfeat);
+  if (n_blocks > 0 && vec) {
+    const int lpr = (int)(D / 4), groups = kBwdVThreads / lpr;
+    const size_t smem = (size_t)2 * groups * lpr * sizeof(float4);
+    attn_proj_bwd_vec_kernel<<<n_blocks, kBwdVThreads, smem, s>>>(feat, al, ar, gl, gr, gfeat, part,
+                                                                  n, rows, (int)H, (int)F);
+    B200_CUDA(cudaGetLastError());
+  } else if (n_blocks > 0) {
+    attn_proj_bwd_kernel<<<n_blocks, kBwdThreads, 0, s>>>(feat, al, ar, gl, gr, gfeat, part, n, rows,
+                                                          (int)H, (int)F);
+    B200_CUDA(cudaGetLastError());
+  }
+  attn_proj_fold_kernel<<<(int)((D + 31) / 32), 1024, 0, s>>>(part, gal, gar, n_blocks, (int)D);
+  B200_CUDA(cudaGetLastError());
+  note_kernel("attn_proj_bwd_static", 2);
 }
 
 }  // namespace b200

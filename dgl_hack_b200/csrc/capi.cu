@@ -805,6 +805,44 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
   API_END();
 }
 
+// No-allocation variant of DGLB200GatAttnProjBackward
+// (no counterpart in the reference): same arguments, same checks, same kernels; the
+// scratch is the file-scope device array of csrc/attn.cu, so nothing is allocated or freed.
+int DGLB200GatAttnProjBackwardNoAlloc(const DGLB200Tensor* feat, const DGLB200Tensor* attn_l,
+                                      const DGLB200Tensor* attn_r, const DGLB200Tensor* grad_el,
+                                      const DGLB200Tensor* grad_er, DGLB200Tensor* grad_feat,
+                                      DGLB200Tensor* grad_attn_l, DGLB200Tensor* grad_attn_r,
+                                      void* stream) {
+  API_BEGIN();
+  B200_CHECK(feat && grad_feat && ((attn_l && grad_el) || (attn_r && grad_er)), "NULL argument");
+  B200_CHECK((attn_l != nullptr) == (grad_el != nullptr) && (attn_r != nullptr) == (grad_er != nullptr),
+             "attn_proj backward: every attention vector needs its output gradient");
+  B200_CHECK((!grad_attn_l || attn_l) && (!grad_attn_r || attn_r),
+             "attn_proj backward: gradient requested for an absent attention vector");
+  int64_t n, H, F;
+  attn_shapes(feat, {attn_l, attn_r, (const DGLB200Tensor*)grad_attn_l,
+                     (const DGLB200Tensor*)grad_attn_r},
+              {grad_el, grad_er}, &n, &H, &F);
+  check_float(grad_feat, "grad_feat");
+  check_compact(grad_feat, "grad_feat");
+  B200_CHECK(num_elements(grad_feat) == n * H * F, "attn_proj backward: grad_feat must be [N, H, F]");
+  B200_CHECK(H * F <= attn_proj_static_max_width(),
+             "DGLB200GatAttnProjBackwardNoAlloc: H * F = " + std::to_string(H * F) +
+                 " exceeds the static scratch limit of " +
+                 std::to_string(attn_proj_static_max_width()) +
+                 " floats per row; use DGLB200GatAttnProjBackward");
+  B200_CUDA(cudaSetDevice(feat->ctx.device_id));
+  attn_proj_backward_static(
+      data_ptr<const float>(feat), attn_l ? data_ptr<const float>(attn_l) : nullptr,
+      attn_r ? data_ptr<const float>(attn_r) : nullptr,
+      grad_el ? data_ptr<const float>(grad_el) : nullptr,
+      grad_er ? data_ptr<const float>(grad_er) : nullptr, data_ptr<float>(grad_feat),
+      grad_attn_l ? data_ptr<float>(grad_attn_l) : nullptr,
+      grad_attn_r ? data_ptr<float>(grad_attn_r) : nullptr, n, H, F, feat->ctx.device_id,
+      static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
 // ---- bf16 feature storage, fp32 accumulation (extension, explicit dtype) ----
 int DGLB200KernelCopySumBF16(DGLB200GraphHandle graph, int transpose, const DGLB200Tensor* in_data,
                              const DGLB200Tensor* col_scale, const DGLB200Tensor* row_scale,

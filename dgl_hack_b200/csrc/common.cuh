@@ -296,6 +296,12 @@ void attn_proj_forward(const float* feat, const float* al, const float* ar, floa
 void attn_proj_backward(const float* feat, const float* al, const float* ar, const float* gl,
                         const float* gr, float* gfeat, float* gal, float* gar, int64_t n,
                         int64_t H, int64_t F, cudaStream_t s);
+// attn.cu, no-allocation variant: block partials in a file-scope device array (3 MiB per GPU)
+void attn_proj_backward_static(const float* feat, const float* al, const float* ar,
+                               const float* gl, const float* gr, float* gfeat, float* gal,
+                               float* gar, int64_t n, int64_t H, int64_t F, int device,
+                               cudaStream_t s);
+int64_t attn_proj_static_max_width();
 // gemm.cu: fp32 dense product on the tensor cores (tcgen05, 3xTF32 error compensation)
 bool gemm_tf32x3_supported(int64_t M, int64_t N, int64_t K, const float* A, int64_t lda);
 void gemm_tf32x3(const float* A, int64_t lda, const float* B, int b_is_kn, const float* bias,

@@ -325,6 +325,24 @@ int DGLB200GatAttnProjBackward(const DGLB200Tensor* feat, const DGLB200Tensor* a
                                DGLB200Tensor* grad_attn_l, DGLB200Tensor* grad_attn_r,
                                void* stream);
 
+/* DGLB200GatAttnProjBackward for callers that cannot allocate device memory (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc). No counterpart in the
+ * reference. Same arguments, checks and results
+ * (bit-identical on a B200: same blocking, same sum orders) as DGLB200GatAttnProjBackward, but the
+ * block partials of grad_attn live in a file-scope `static __device__` array of the library
+ * (768 row blocks x 2 x 512 floats = 3 MiB, held by every GPU that loads the library until
+ * exit), so the call performs no cudaMalloc / cudaMallocAsync / cudaFree and calls no allocating
+ * library routine. Limit: H * F <= 512; larger widths are rejected with an error (use the
+ * allocating entry point). The array is shared by ALL calls on a device and keeps the previous
+ * call's contents (every partial that is read is overwritten first, nothing needs clearing):
+ * calls that overlap on the GPU -- different streams, or concurrent graph launches -- race; run
+ * them in stream order. */
+int DGLB200GatAttnProjBackwardNoAlloc(const DGLB200Tensor* feat, const DGLB200Tensor* attn_l,
+                                      const DGLB200Tensor* attn_r, const DGLB200Tensor* grad_el,
+                                      const DGLB200Tensor* grad_er, DGLB200Tensor* grad_feat,
+                                      DGLB200Tensor* grad_attn_l, DGLB200Tensor* grad_attn_r,
+                                      void* stream);
+
 /* copy_src + sum / mean with bf16 FEATURE STORAGE and fp32 accumulation: a second, explicit
  * precision tier (north_star: 1e-2 relative in bf16). The reference kernels are fp32-only
  * (DGL_DTYPE_SWITCH, src/kernel/common.h:49-55), so this has no reference PackedFunc; it halves
