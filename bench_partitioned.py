@@ -275,6 +275,6 @@ def run_partitioned(rank, world, dev, scale=1, steps=10, warmup=3, epochs=5, par
         "gcn_epoch_ms": round(epoch_ms, 3), "gcn_epochs": epochs,
         "gcn_dims": GCN_DIMS, "gcn_loss_after": round(lsum.item(), 5),
         "gcn_fwd_loss_rel_err": loss_rel, "gcn_fwd_logit_rel_err": logit_err,
-        "dense": os.environ.get("B200_DENSE", "torch_fp32"),
+        "dense": dense.mode(),
     }
     return rec

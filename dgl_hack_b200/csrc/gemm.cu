@@ -317,17 +317,23 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a,
 // the contraction runs over the LONG dimension M, so both operands are MN-major for the tensor
 // core (their contiguous dimension is the MMA's M / N, not K). Shared-memory image of a stage
 // (kTnRows = 16 rows of A and G): one TMA box [16 rows x 32 floats] per 32-column block,
-// SWIZZLE_128B, blocks 2 KB apart = canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte
-// units with LBO = 2048 B (next 32-column block), SBO = 1024 B (next 8 rows). Each CTA owns a
+// 128-byte swizzle with 32-byte atoms, blocks 2 KB apart (LBO = 2048 B: next 32-column block;
+// SBO = 512 B: next 4 rows; see umma_desc_mn_sw128). Each CTA owns a
 // contiguous chunk of rows, accumulates a full [Kf, N] partial in TMEM (Kf/128 accumulators of
 // N columns), writes it to scratch; gemm_tn_fold_kernel adds the partials in CTA order
 // (deterministic). Both operands are big, so both are split hi / lo in the kernel.
 constexpr int kTnRows = 16;
 constexpr int kTnBoxBytes = kTnRows * 128;  // 2 KB
 
+// MN-major operands of 32-bit element types have exactly one legal shared-memory layout
+// (cutlass sm100_common.inl: "for mn-major tf32 operands, SW128_32B is the only available smem
+// layout"): SWIZZLE_128B_BASE32B (layout type 1, Swizzle<2,5,2>: 32-byte atoms permuted inside a
+// 128-byte row by row % 4), canonical form ((8,n),(4,k)):((1,LBO),(8,SBO)) in 16-byte units --
+// K groups of FOUR rows (SBO = 512 B), MN blocks of 32 floats (LBO = one TMA box = 2 KB). TMA
+// writes the same pattern with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
 __device__ __forceinline__ uint64_t umma_desc_mn_sw128(const void* tile) {
   return (uint64_t)((smem_u32(tile) & 0x3FFFF) >> 4) | ((uint64_t)(kTnBoxBytes >> 4) << 16) |
-         (64ull << 32) | (1ull << 46) | (2ull << 61);
+         (32ull << 32) | (1ull << 46) | (1ull << 61);
 }
 
 struct GemmTnArgs {
@@ -413,7 +419,7 @@ gemm_tn_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a,
           const uint64_t g_lo = umma_desc_mn_sw128(st + 2 * g.a_bytes + g.g_bytes);
 #pragma unroll
           for (int k = 0; k < kTnRows / kUmmaK; ++k) {
-            const uint64_t adv = (uint64_t)(k * 1024 >> 4);  // next 8 rows = SBO
+            const uint64_t adv = (uint64_t)(k * 1024 >> 4);  // next 8 rows (two 4-row K groups)
             umma_tf32(tmem_d, a_lo + adv, g_hi + adv, idesc, (it | k) != 0);
             umma_tf32(tmem_d, a_hi + adv, g_lo + adv, idesc, 1);
             umma_tf32(tmem_d, a_hi + adv, g_hi + adv, idesc, 1);
@@ -547,7 +553,8 @@ EncodeTiledFn encode_tiled() {
 
 // [rows, cols] fp32 row-major (row pitch ld floats) as a 2-D tiled map with a
 // [box_rows x 32] box, SWIZZLE_128B; out-of-bounds elements are delivered as zeros.
-CUtensorMap make_map(const float* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+CUtensorMap make_map(const float* base, int64_t rows, int64_t cols, int64_t ld, int box_rows,
+                     CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   CUtensorMap m;
   const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
@@ -555,7 +562,7 @@ CUtensorMap make_map(const float* base, int64_t rows, int64_t cols, int64_t ld, 
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = encode_tiled()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                                     const_cast<float*>(base), dims, strides, box, estr,
-                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
                                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B200_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
@@ -594,8 +601,8 @@ void gemm_tn_tf32x3(const float* A, const float* G, float* C, int64_t M, int64_t
   g.rows_per_cta = (int)(((M + grid - 1) / grid + kTnRows - 1) / kTnRows * kTnRows);
   Scratch partial((size_t)grid * g.m_tiles * kBM * g.Npad * 4, s);
   g.partial = partial.as<float>();
-  const CUtensorMap map_a = make_map(A, M, Kf, Kf, kTnRows);
-  const CUtensorMap map_g = make_map(G, M, N, N, kTnRows);
+  const CUtensorMap map_a = make_map(A, M, Kf, Kf, kTnRows, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+  const CUtensorMap map_g = make_map(G, M, N, N, kTnRows, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
   const size_t smem = (size_t)g.stages * g.stage_bytes + (3 * g.stages + 2) * 8 + 16 + 1024;
   static std::once_flag once;
   std::call_once(once, [] {

@@ -250,7 +250,9 @@ def linear(a, w, bias=None, relu=False):
 
 
 def mode():
-    return os.environ.get("B200_DENSE", "")
+    """B200_DENSE: "tf32x3" (default) = the library's own tcgen05 kernel; "bf16x9" = cuBLASLt's
+    emulated-fp32 GEMM (library baseline); "torch" = torch.matmul (cuBLAS fp32 SIMT)."""
+    return os.environ.get("B200_DENSE", "tf32x3")
 
 
 def matmul(a, b):

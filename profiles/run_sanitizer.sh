@@ -12,10 +12,16 @@ for tool in memcheck racecheck; do
   out=gpurun_out/r2_sanitizer_$tool.txt
   : > $out
   echo "=== $tool: pytest $SEL  (LDG and TMA-ring SpMM paths are both parametrised inside)" >> $out
-  timeout 2400 compute-sanitizer --tool $tool --print-limit 5 \
-    python -m pytest $SEL -q -p no:cacheprovider 2>&1 | grep -E "ERROR SUMMARY|RACECHECK SUMMARY|passed|failed|Error|hazard" | tail -8 >> $out
+  timeout 2400 /usr/local/cuda/bin/compute-sanitizer --tool $tool --print-limit 5 \
+    python -m pytest $SEL -q -p no:cacheprovider > gpurun_out/r2_sanitizer_${tool}_pytest.raw 2>&1
+  echo "exit code $?" >> $out
+  grep -E "ERROR SUMMARY|RACECHECK SUMMARY|passed|failed|Error|hazard" gpurun_out/r2_sanitizer_${tool}_pytest.raw | tail -n 8 >> $out
+  tail -n 3 gpurun_out/r2_sanitizer_${tool}_pytest.raw >> $out
   echo "=== $tool: tcgen05 3xTF32 GEMM (profiles/gemm_check.py --quick)" >> $out
-  timeout 900 compute-sanitizer --tool $tool --print-limit 5 python profiles/gemm_check.py --quick 2>&1 \
-    | grep -E "ERROR SUMMARY|RACECHECK SUMMARY|worst_err|Error|hazard" | tail -6 >> $out
+  timeout 900 /usr/local/cuda/bin/compute-sanitizer --tool $tool --print-limit 5 \
+    python profiles/gemm_check.py --quick > gpurun_out/r2_sanitizer_${tool}_gemm.raw 2>&1
+  echo "exit code $?" >> $out
+  grep -E "ERROR SUMMARY|RACECHECK SUMMARY|worst_err|Error|hazard" gpurun_out/r2_sanitizer_${tool}_gemm.raw | tail -n 6 >> $out
+  tail -n 3 gpurun_out/r2_sanitizer_${tool}_gemm.raw >> $out
 done
-tail -40 gpurun_out/r2_sanitizer_memcheck.txt gpurun_out/r2_sanitizer_racecheck.txt
+cat gpurun_out/r2_sanitizer_memcheck.txt gpurun_out/r2_sanitizer_racecheck.txt
