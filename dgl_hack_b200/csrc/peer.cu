@@ -54,6 +54,40 @@ __global__ void __launch_bounds__(256) halo_push_kernel(const PushArgs a) {
   }
 }
 
+// Bulk pull of halo rows: row j of `out` = row (code & kPullRowMask) of block tab[code >> 27],
+// code = codes[j]. Every load is a peer load (NVLink), one warp per row, 128-bit moves: the
+// de-duplicated halo rows arrive at the link's streaming rate instead of being fetched edge by
+// edge inside the latency-bound gather.
+constexpr int kPullSlotShift = 27;
+constexpr int kPullRowMask = (1 << kPullSlotShift) - 1;
+struct PullArgs {
+  const float* tab[kMaxPeers];
+  const int32_t* codes;
+  int64_t n_rows, D;
+  float* out;
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(256) halo_pull_kernel(const PullArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int nvec = (int)(a.D / VEC);
+  for (int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < a.n_rows;
+       j += n_warps) {
+    const int32_t code = __ldg(a.codes + j);
+    const float* src = a.tab[(code >> kPullSlotShift) & (kMaxPeers - 1)] +
+                       (int64_t)(code & kPullRowMask) * a.D;
+    float* dst = a.out + j * a.D;
+    for (int c = lane; c < nvec; c += 32) {
+      if (VEC == 4) {
+        reinterpret_cast<float4*>(dst)[c] = *(reinterpret_cast<const float4*>(src) + c);
+      } else {
+        dst[c] = src[c];
+      }
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -140,6 +174,37 @@ int DGLB200HaloPush(const float* x, int64_t D, int n_peers, void* const* peer, c
   else halo_push_kernel<1><<<blocks, 256, 0, s>>>(a);
   B200_CUDA(cudaGetLastError());
   note_kernel("halo_push", 1);
+  API_END();
+}
+
+// Pulls n_rows rows of D floats: out[j] = block[codes[j] >> 27][codes[j] & (2^27 - 1)].
+// slot_base is a HOST array of n_slots <= 16 device pointers (own or peer-mapped blocks of row
+// pitch D), codes a DEVICE int32 array. Ordering against the writers of the blocks is the caller's.
+int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* codes, int64_t n_rows,
+                    int64_t D, float* out, int device, void* stream) {
+  API_BEGIN();
+  B200_CHECK(n_slots >= 1 && n_slots <= kMaxPeers && slot_base, "DGLB200HaloPull: 1 to 16 slots");
+  B200_CHECK(D > 0 && n_rows >= 0, "DGLB200HaloPull: bad size");
+  if (n_rows == 0) return 0;
+  B200_CHECK(codes && out, "DGLB200HaloPull: NULL argument");
+  PullArgs a{};
+  bool al = (D % 4 == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0);
+  for (int q = 0; q < n_slots; ++q) {
+    B200_CHECK(slot_base[q] != nullptr, "DGLB200HaloPull: NULL slot base");
+    a.tab[q] = static_cast<const float*>(slot_base[q]);
+    al = al && (reinterpret_cast<uintptr_t>(slot_base[q]) % 16 == 0);
+  }
+  a.codes = codes;
+  a.n_rows = n_rows;
+  a.D = D;
+  a.out = out;
+  B200_CUDA(cudaSetDevice(device));
+  const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((n_rows + 7) / 8, 148 * 16));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (al) halo_pull_kernel<4><<<blocks, 256, 0, s>>>(a);
+  else halo_pull_kernel<1><<<blocks, 256, 0, s>>>(a);
+  B200_CUDA(cudaGetLastError());
+  note_kernel("halo_pull", 1);
   API_END();
 }
 

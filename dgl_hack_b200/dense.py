@@ -185,12 +185,13 @@ def tc_gemm(a, b, b_is_kn=True, bias=None, relu=False):
 
 
 def tc_weight_grad(a, g):
-    """a.T @ g ([M, K], [M, N] -> [K, N]): the library GEMM by default; B200_DENSE_WGRAD=tc = the
-    own MN-major tcgen05 kernel (csrc/gemm.cu gemm_tn_tf32x3_kernel; under validation, opt-in)."""
+    """a.T @ g ([M, K], [M, N] -> [K, N]): the own MN-major tcgen05 kernel (csrc/gemm.cu
+    gemm_tn_tf32x3_kernel: 0.64 ms against 3.5 ms for torch's fp32 GEMM at [1M, 256] x [1M, 256],
+    error 3e-7 of sum|terms|, profiles/r2_gemm_check_wgrad.json); B200_DENSE_WGRAD=lib = torch."""
     from . import kernel as K
     a, g = a.contiguous(), g.contiguous()
     k, n = a.shape[1], g.shape[1]
-    if os.environ.get("B200_DENSE_WGRAD", "lib") != "tc" or k > 256 or n > 256 or k % 4 or n % 4 \
+    if os.environ.get("B200_DENSE_WGRAD", "tc") != "tc" or k > 256 or n > 256 or k % 4 or n % 4 \
             or a.shape[0] == 0 or a.data_ptr() % 16 or g.data_ptr() % 16:
         return a.t() @ g
     c = torch.empty((k, n), dtype=torch.float32, device=a.device)

@@ -551,7 +551,7 @@ class PeerGather(object):
     alternate, so a block is rewritten only after every rank has passed the barrier that follows
     its last readers (two barriers lie between two writes of the same block)."""
 
-    def __init__(self, part, device, blocks):
+    def __init__(self, part, device, blocks, pull=None):
         from .graph_index import GraphIndex
         self.part, self.device, self.blocks = part, torch.device(device), blocks
         fs, fd = part.fwd_coo
@@ -560,6 +560,22 @@ class PeerGather(object):
         self.g_b = GraphIndex.from_coo(part.n_inner, part.n_inner + part.n_ohalo, bs, bd, device)
         self.code = (part.fwd_code.to(device).contiguous(), part.bwd_code.to(device).contiguous())
         self._turn = [0, 0]
+        # "pull" mode (default; B200_HALO_PULL=0 = per-edge peer loads inside the SpMM): the
+        # de-duplicated halo rows are first pulled into a local buffer by one streaming kernel whose
+        # loads are ALL remote (full NVLink rate), then the same single-pass SpMM gathers from two
+        # local slots (own block, pulled halo). Inside the SpMM only a few percent of the loads in
+        # flight are remote, so NVLink latency caps them near 280 GB/s (measured at 2 GPUs).
+        if pull is None:
+            pull = os.environ.get("B200_HALO_PULL", "1") != "0"
+        self.pull = bool(pull)
+        n_in = part.n_inner
+        n_ext = (part.n_halo, part.n_ohalo)
+        self.pull_codes = tuple(c[n_in:].contiguous() for c in self.code)
+        self.local_code = tuple(torch.cat([
+            torch.arange(n_in, dtype=torch.int32, device=self.device),
+            (1 << SLOT_SHIFT) + torch.arange(n, dtype=torch.int32, device=self.device)]).contiguous()
+            for n in n_ext)
+        self._halo_buf = {}
 
     def stage(self, which, x, scale):
         """Writes scale * x into this rank's next block of direction `which`; returns its index."""
@@ -576,11 +592,36 @@ class PeerGather(object):
             torch.mul(x, scale.view(-1, 1), out=view)
         return b
 
+    def _pulled(self, which, b, d, like):
+        """Local copy of the rows this rank needs from its peers (one streaming pull kernel)."""
+        import ctypes
+        from ._lib import LIB, check_call
+        n = int(self.pull_codes[which].numel())
+        key = (which, d)
+        buf = self._halo_buf.get(key)
+        if buf is None or buf.dtype != like.dtype:
+            buf = self._halo_buf[key] = like.new_empty((max(n, 1), d))
+        if n:
+            bases = self.blocks.bases(b)
+            arr = (ctypes.c_void_p * len(bases))(*[int(p) for p in bases])
+            check_call(LIB.DGLB200HaloPull(
+                len(bases), arr, ctypes.c_void_p(self.pull_codes[which].data_ptr()), n, d,
+                ctypes.c_void_p(buf.data_ptr()), self.device.index or 0,
+                ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return buf
+
     def reduce(self, which, b, d, row_scale, like):
         from . import kernel as K
         out = like.new_empty((self.part.n_inner, d))
-        K.peer_copy_sum(self.g_f if which == 0 else self.g_b, which == 1, self.blocks.bases(b),
-                        self.code[which], row_scale, out)
+        g = self.g_f if which == 0 else self.g_b
+        if self.pull:
+            halo = self._pulled(which, b, d, like)
+            own = self.blocks.bases(b)[self.part.rank if len(self.blocks.bases(b)) > self.part.rank
+                                       else 0]
+            K.peer_copy_sum(g, which == 1, [own, halo.data_ptr()], self.local_code[which],
+                            row_scale, out)
+        else:
+            K.peer_copy_sum(g, which == 1, self.blocks.bases(b), self.code[which], row_scale, out)
         return out
 
     def run(self, which, x, stage_scale, row_scale):

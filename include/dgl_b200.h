@@ -496,6 +496,14 @@ int DGLB200HaloPush(const float* x, int64_t D, int n_peers, void* const* peer, c
                     const int64_t* dst_row, const int32_t* rows, int first_peer, int device,
                     void* stream);
 
+/* Bulk pull of halo rows over NVLink: out[j] = row (codes[j] & (2^27 - 1)) of block
+ * slot_base[codes[j] >> 27], j < n_rows, rows of D floats. slot_base: HOST array of n_slots <= 16
+ * device pointers (own / peer-mapped blocks), codes: device int32. One streaming kernel whose
+ * loads are all remote, so the de-duplicated halo arrives at the link rate; the aggregation then
+ * runs single-pass over two LOCAL slots (own block, pulled halo) with DGLB200KernelPeerCopySum. */
+int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* codes, int64_t n_rows,
+                    int64_t D, float* out, int device, void* stream);
+
 /* ---- the PackedFunc face: drop-in registration into a loaded libdgl ----
  * DGLValue (include/dgl/runtime/c_runtime_api.h:122-129; DGLType / DGLContext members are
  * 8 bytes as well) and DGLPackedCFunc (:301-306). */

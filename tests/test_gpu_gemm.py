@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_tf32x3_gemm_against_fp64():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "profiles", "gemm_check.py"),
-                          "--quick"], capture_output=True, text=True, timeout=300)
+                          "--quick", "--wgrad"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, (out.stdout[-2000:], out.stderr[-2000:])
     last = json.loads(out.stdout.strip().splitlines()[-1])
     assert last["ok"] and last["worst_err_tf32x3"] <= 1e-5

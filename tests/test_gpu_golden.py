@@ -192,3 +192,47 @@ def test_sddmm_widths_vs_oracle(impl, d):
                                                  None, None, None)
         assert impl.last == "sddmm"
         np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("d", [9, 47, 602])
+def test_odd_width_repitch_is_bit_identical(d, monkeypatch):
+    """Rows whose pitch is not a multiple of 16 bytes are gathered from a zero-padded copy with
+    16-byte rows (spmm.cu, B200_SPMM_PAD): same terms, same order -> bit-identical to the
+    scalar-load kernels, forward, scaled forward, gradient and max reducer. Hub rows are kept
+    sequential here (B200_SPMM_SEG=0): the segment length of the default mode depends on the row
+    pitch, so with segmentation the two routes agree to rounding, which is checked as well."""
+    import torch
+    import dgl_hack_b200 as B
+    from dgl_hack_b200 import backend as F, kernel as K
+    ns, nd, ne = 2000, 1500, 60000          # mean in-degree 40: the padded path is taken
+    src, dst = cases.powerlaw_graph(ns, nd, ne, 0.7, 21)
+    g = B.GraphIndex.from_coo(ns, nd, src, dst, "cuda:0")
+    rs = np.random.RandomState(d)
+    x = torch.from_numpy(rs.uniform(-1, 1, (ns, d)).astype(np.float32)).cuda()
+    w = torch.from_numpy(rs.uniform(0, 1, (ne, 1)).astype(np.float32)).cuda()
+    go = torch.from_numpy(rs.uniform(-1, 1, (nd, d)).astype(np.float32)).cuda()
+    cs = torch.from_numpy(rs.uniform(0.5, 1, ns).astype(np.float32)).cuda()
+    rsc = torch.from_numpy(rs.uniform(0.5, 1, nd).astype(np.float32)).cuda()
+
+    def run():
+        xr = x.clone().requires_grad_(True)
+        o1 = F.copy_reduce("sum", g, 0, xr, nd)
+        o1.backward(go)
+        o2 = F.copy_reduce("max", g, 0, x, nd)
+        o3 = F.binary_reduce("sum", "mul", g, 0, 2, x, w, nd)
+        o4 = F.scaled_copy_sum(g, x, cs, rsc)
+        o5 = F.copy_reduce("mean", g, 0, x, nd)
+        return [o1.detach(), xr.grad, o2, o3, o4, o5]
+    monkeypatch.setenv("B200_SPMM_SEG", "0")
+    monkeypatch.setenv("B200_SPMM_PAD", "0")
+    plain = run()
+    monkeypatch.setenv("B200_SPMM_PAD", "1")
+    padded = run()
+    for a, b in zip(plain, padded):
+        assert torch.equal(a, b)
+    monkeypatch.delenv("B200_SPMM_SEG")
+    segmented = run()
+    # every term is at most 1 in magnitude: sum|terms| <= the largest degree
+    mag = float(max(g.in_degrees().max().item(), g.out_degrees().max().item()))
+    for a, b in zip(plain, segmented):
+        assert (a - b).abs().max().item() <= 1e-5 * max(mag, 1.0)
