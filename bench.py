@@ -29,6 +29,9 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# the barrier of the partitioned leg is a tiny NCCL kernel: on a high-priority stream it is not
+# queued behind the CTAs of the aggregation kernel running beside it
+os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")
 
 N_NODES, N_EDGES, N_FEATS, ALPHA, SEED = 232965, 114615892, 602, 0.6, 2
 WORKLOAD = "reddit_shaped_graphsage_mean_copy_src_fwd_bwd"

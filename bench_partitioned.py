@@ -193,6 +193,27 @@ def run_partitioned(rank, world, dev, scale=1, steps=10, warmup=3, epochs=5, par
         x.grad = None
     agg_ms = _timed(agg_step, steps, warmup, dev, world)
 
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        agg_step()
+    agg_host_ms = (time.perf_counter() - t0) * 1e3 / steps
+    torch.cuda.synchronize()
+    if os.environ.get("B200_BENCH_PROFILE"):
+        from torch.profiler import profile, ProfilerActivity
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            for _ in range(4):
+                agg_step()
+            torch.cuda.synchronize()
+        if rank == 0 or rank == world - 1:
+            with open(os.environ["B200_BENCH_PROFILE"] + ".agg.rank%d" % rank, "w") as f:
+                f.write("world %d, 4 agg steps, agg_ms %.4f host_enqueue_ms %.4f\n" % (
+                    world, agg_ms, agg_host_ms))
+                f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=30,
+                                                  max_name_column_width=70))
+            if rank == 0:
+                prof.export_chrome_trace(os.environ["B200_BENCH_PROFILE"] + ".agg.trace.json")
+
     phases, local_ms = None, None
     if pg.gather is not None:
         gth = pg.gather
@@ -264,6 +285,23 @@ def run_partitioned(rank, world, dev, scale=1, steps=10, warmup=3, epochs=5, par
                     world, epoch_ms, host_ms))
                 f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45,
                                                   max_name_column_width=70))
+    # A/B of the other reduction modes on the same partition / blocks (B200_BENCH_MODES=a,b)
+    mode_cmp = {}
+    extra = [m for m in os.environ.get("B200_BENCH_MODES", "").split(",") if m]
+    if pg.gather is not None and extra:
+        from dgl_hack_b200.partition import PeerGather
+        first = pg.gather
+        mode_cmp[first.mode] = {"agg_ms_per_step": round(agg_ms, 4), "gcn_epoch_ms": round(epoch_ms, 3)}
+        for m in extra:
+            if m == first.mode:
+                continue
+            if "@" in m:     # "split@4": split mode with 4 pull CTAs per SM
+                os.environ["B200_PULL_CTAS_PER_SM"] = m.split("@")[1]
+            pg.gather = PeerGather(p, dev, first.blocks, mode=m.split("@")[0])
+            a_ms = _timed(agg_step, steps, warmup, dev, world)
+            e_ms = _timed(run_epoch, epochs, 2, dev, world)
+            mode_cmp[m] = {"agg_ms_per_step": round(a_ms, 4), "gcn_epoch_ms": round(e_ms, 3)}
+        pg.gather = first
     lsum = last[0].detach().clone()
     if world > 1:
         dist.all_reduce(lsum)
@@ -291,6 +329,7 @@ def run_partitioned(rank, world, dev, scale=1, steps=10, warmup=3, epochs=5, par
         "halo_rows_max": int(S[:, 3].max()), "halo_path": pg.halo_path,
         "halo_bytes_per_step": remote_reads * d * 4,
         "agg_ms_per_step": round(agg_ms, 4), "agg_gedges_per_s": round(2 * e / agg_ms / 1e6, 3),
+        "agg_host_enqueue_ms": round(agg_host_ms, 4),
         "agg_local_only_ms": None if local_ms is None else round(local_ms, 4),
         "exposed_comm_ms": None if local_ms is None else round(agg_ms - local_ms, 4),
         "phase_ms": phases, "steps": steps, "warmup": warmup,
@@ -301,4 +340,8 @@ def run_partitioned(rank, world, dev, scale=1, steps=10, warmup=3, epochs=5, par
         "gcn_fwd_loss_rel_err": loss_rel, "gcn_fwd_logit_rel_err": logit_err,
         "dense": dense.mode(),
     }
+    if pg.gather is not None:
+        rec["halo_mode"] = pg.gather.mode
+    if mode_cmp:
+        rec["mode_comparison"] = mode_cmp
     return rec

@@ -101,8 +101,8 @@ SYMBOLS = {
     "DGLB200PeerFree": (_c.c_int, [_c.c_void_p]),
     "DGLB200HaloPush": (_c.c_int, [_c.c_void_p, _c.c_int64, _c.c_int, _c.c_void_p, _c.c_void_p,
                                    _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p]),
-    "DGLB200HaloPull": (_c.c_int, [_c.c_int, _c.c_void_p, _c.c_void_p, _c.c_int64, _c.c_int64,
-                                   _c.c_void_p, _c.c_int, _c.c_void_p]),
+    "DGLB200HaloPull": (_c.c_int, [_c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int64,
+                                   _c.c_int64, _c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p]),
     "DGLB200MetisPartition": (_c.c_int, [_c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_void_p,
                                          _c.c_int, _c.c_uint64, _c.c_void_p,
                                          _c.POINTER(_c.c_int64)]),
@@ -121,6 +121,8 @@ SYMBOLS = {
                                        _c.c_void_p]),
     "DGLB200KernelScaledCopySum": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP, TensorP,
                                               TensorP, _c.c_void_p]),
+    "DGLB200KernelScaledCopySumAdd": (_c.c_int, [GraphHandle, _c.c_int, TensorP, TensorP, TensorP,
+                                                 TensorP, TensorP, _c.c_void_p]),
     "DGLB200GraphCreateFromTypedCSR": (_c.c_int, [_c.c_int64, _c.c_int64, _c.c_int, _c.c_void_p,
                                                   _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int64,
                                                   _c.c_int, _c.c_void_p, _c.POINTER(GraphHandle)]),

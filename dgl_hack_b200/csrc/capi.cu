@@ -1021,10 +1021,9 @@ int DGLB200CompactBlock(const int64_t* dst_nodes, int64_t n_dst, const int64_t* 
 }
 
 // ---- scaled aggregation (extension): GraphConv's degree normalisation inside the SpMM ----
-int DGLB200KernelScaledCopySum(DGLB200GraphHandle graph, int transpose, const DGLB200Tensor* in_data,
-                               const DGLB200Tensor* col_scale, const DGLB200Tensor* row_scale,
-                               DGLB200Tensor* out_data, void* stream) {
-  API_BEGIN();
+static void scaled_copy_sum(DGLB200GraphHandle graph, int transpose, const DGLB200Tensor* in_data,
+                            const DGLB200Tensor* col_scale, const DGLB200Tensor* row_scale,
+                            const DGLB200Tensor* addend, DGLB200Tensor* out_data, void* stream) {
   B200_CHECK(graph && in_data && out_data, "NULL argument");
   check_ctx(graph, {in_data, col_scale, row_scale, out_data},
             {"in_data", "col_scale", "row_scale", "out_data"});
@@ -1084,8 +1083,34 @@ int DGLB200KernelScaledCopySum(DGLB200GraphHandle graph, int transpose, const DG
     c.lhs_rows = n_rows;
     c.out_rows = n_cols;
   }
+  if (addend) {
+    check_ctx(graph, {addend}, {"addend"});
+    check_float(addend, "addend");
+    check_compact(addend, "addend");
+    B200_CHECK(addend->ndim == out_data->ndim && num_elements(addend) == num_elements(out_data) &&
+                   addend->shape[0] == n_rows,
+               "ScaledCopySumAdd: addend must have out_data's shape");
+    c.addend = data_ptr<const float>(addend);
+  }
   B200_CUDA(cudaSetDevice(graph->device));
   B200_CHECK(try_spmm(c), "ScaledCopySum: shape not supported by the SpMM kernel");
+}
+
+int DGLB200KernelScaledCopySum(DGLB200GraphHandle graph, int transpose, const DGLB200Tensor* in_data,
+                               const DGLB200Tensor* col_scale, const DGLB200Tensor* row_scale,
+                               DGLB200Tensor* out_data, void* stream) {
+  API_BEGIN();
+  scaled_copy_sum(graph, transpose, in_data, col_scale, row_scale, nullptr, out_data, stream);
+  API_END();
+}
+
+int DGLB200KernelScaledCopySumAdd(DGLB200GraphHandle graph, int transpose,
+                                  const DGLB200Tensor* in_data, const DGLB200Tensor* col_scale,
+                                  const DGLB200Tensor* row_scale, const DGLB200Tensor* addend,
+                                  DGLB200Tensor* out_data, void* stream) {
+  API_BEGIN();
+  B200_CHECK(addend, "ScaledCopySumAdd: NULL addend");
+  scaled_copy_sum(graph, transpose, in_data, col_scale, row_scale, addend, out_data, stream);
   API_END();
 }
 

@@ -271,6 +271,8 @@ struct KernelCall {
   // (own HBM and peer GPUs' mapped over NVLink); the operand's id map yields (slot, row) codes
   const float* const* a_tab = nullptr;
   int n_slots = 0;
+  // SpMM only, sum reducer: dst = row_scale * (addend + sum); addend may alias dst
+  const float* addend = nullptr;
   cudaStream_t stream;
 };
 

@@ -54,35 +54,53 @@ __global__ void __launch_bounds__(256) halo_push_kernel(const PushArgs a) {
   }
 }
 
-// Bulk pull of halo rows: row j of `out` = row (code & kPullRowMask) of block tab[code >> 27],
-// code = codes[j]. Every load is a peer load (NVLink), one warp per row, 128-bit moves: the
-// de-duplicated halo rows arrive at the link's streaming rate instead of being fetched edge by
-// edge inside the latency-bound gather.
+// Bulk pull of halo rows: out[dst_row[i]] = row (code & kPullRowMask) of block tab[code >> 27],
+// code = codes[i] (dst_row == NULL: i). Every load is a peer load (NVLink). Work item = one
+// 16-byte chunk of one row, consecutive threads = consecutive chunks (no idle lanes at D = 100),
+// four items in flight per thread (64 B x 2048 threads = 128 KB per SM against the several-us
+// NVLink round trip). The caller lists the rows ROUND-ROBIN over the owners (partition.py
+// PeerGather): with the rows grouped by owner every rank of the node would read from peer 0
+// first, then from peer 1, ... and one GPU's egress would serve all of them at a time.
 constexpr int kPullSlotShift = 27;
 constexpr int kPullRowMask = (1 << kPullSlotShift) - 1;
+constexpr int kPullUnroll = 4;
 struct PullArgs {
   const float* tab[kMaxPeers];
   const int32_t* codes;
+  const int32_t* dst_row;
   int64_t n_rows, D;
   float* out;
 };
 
 template <int VEC>
 __global__ void __launch_bounds__(256) halo_pull_kernel(const PullArgs a) {
-  const int lane = threadIdx.x & 31;
-  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const int nvec = (int)(a.D / VEC);
-  for (int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < a.n_rows;
-       j += n_warps) {
-    const int32_t code = __ldg(a.codes + j);
-    const float* src = a.tab[(code >> kPullSlotShift) & (kMaxPeers - 1)] +
-                       (int64_t)(code & kPullRowMask) * a.D;
-    float* dst = a.out + j * a.D;
-    for (int c = lane; c < nvec; c += 32) {
-      if (VEC == 4) {
-        reinterpret_cast<float4*>(dst)[c] = *(reinterpret_cast<const float4*>(src) + c);
-      } else {
-        dst[c] = src[c];
+  const int64_t total = a.n_rows * nvec;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < total;
+       base += stride * kPullUnroll) {
+    float4 v[kPullUnroll];
+    int64_t o[kPullUnroll];
+#pragma unroll
+    for (int k = 0; k < kPullUnroll; ++k) {
+      const int64_t idx = base + k * stride;
+      o[k] = -1;
+      if (idx < total) {
+        const int64_t i = idx / nvec;
+        const int c = (int)(idx - i * nvec);
+        const int32_t code = __ldg(a.codes + i);
+        const float* src = a.tab[(code >> kPullSlotShift) & (kMaxPeers - 1)] +
+                           (int64_t)(code & kPullRowMask) * a.D + c * VEC;
+        if (VEC == 4) v[k] = __ldg(reinterpret_cast<const float4*>(src));
+        else v[k].x = __ldg(src);
+        o[k] = (int64_t)(a.dst_row ? __ldg(a.dst_row + i) : i) * a.D + c * VEC;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kPullUnroll; ++k) {
+      if (o[k] >= 0) {
+        if (VEC == 4) *reinterpret_cast<float4*>(a.out + o[k]) = v[k];
+        else a.out[o[k]] = v[k].x;
       }
     }
   }
@@ -177,11 +195,13 @@ int DGLB200HaloPush(const float* x, int64_t D, int n_peers, void* const* peer, c
   API_END();
 }
 
-// Pulls n_rows rows of D floats: out[j] = block[codes[j] >> 27][codes[j] & (2^27 - 1)].
-// slot_base is a HOST array of n_slots <= 16 device pointers (own or peer-mapped blocks of row
-// pitch D), codes a DEVICE int32 array. Ordering against the writers of the blocks is the caller's.
-int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* codes, int64_t n_rows,
-                    int64_t D, float* out, int device, void* stream) {
+// Pulls n_rows rows of D floats: out[dst_row[i]] = block[codes[i] >> 27][codes[i] & (2^27 - 1)]
+// (dst_row NULL: out[i]; max_blocks <= 0: default grid). slot_base is a HOST array of n_slots <= 16 device pointers (own or
+// peer-mapped blocks of row pitch D), codes / dst_row DEVICE int32 arrays. Ordering against the
+// writers of the blocks is the caller's.
+int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* codes,
+                    const int32_t* dst_row, int64_t n_rows, int64_t D, float* out, int max_blocks,
+                    int device, void* stream) {
   API_BEGIN();
   B200_CHECK(n_slots >= 1 && n_slots <= kMaxPeers && slot_base, "DGLB200HaloPull: 1 to 16 slots");
   B200_CHECK(D > 0 && n_rows >= 0, "DGLB200HaloPull: bad size");
@@ -195,11 +215,18 @@ int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* co
     al = al && (reinterpret_cast<uintptr_t>(slot_base[q]) % 16 == 0);
   }
   a.codes = codes;
+  a.dst_row = dst_row;
   a.n_rows = n_rows;
   a.D = D;
   a.out = out;
   B200_CUDA(cudaSetDevice(device));
-  const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((n_rows + 7) / 8, 148 * 16));
+  const int64_t items = n_rows * (al ? D / 4 : D);
+  // max_blocks > 0 caps the grid: a pull that shares the GPU with a compute kernel (the
+  // inner-edge SpMM of the split mode) leaves most registers / warp slots of every SM to it;
+  // two CTAs per SM keep 32 KB of loads in flight per SM, enough for the link
+  const int cap = max_blocks > 0 ? max_blocks : 148 * 8;
+  const int blocks = (int)std::max<int64_t>(
+      1, std::min<int64_t>((items + 256 * kPullUnroll - 1) / (256 * kPullUnroll), cap));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (al) halo_pull_kernel<4><<<blocks, 256, 0, s>>>(a);
   else halo_pull_kernel<1><<<blocks, 256, 0, s>>>(a);

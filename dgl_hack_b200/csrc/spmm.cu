@@ -92,7 +92,7 @@ combine_partials_kernel(const int32_t* __restrict__ heavy_row,
                         const int32_t* __restrict__ heavy_ptr, const float* __restrict__ partial,
                         const int32_t* __restrict__ indptr, float* __restrict__ out,
                         const int32_t* __restrict__ out_map, int D, int red, int mean,
-                        const float* __restrict__ row_scale) {
+                        const float* __restrict__ row_scale, const float* addend) {
   const int h = blockIdx.x;
   const int r = heavy_row[h];
   const int p0 = heavy_ptr[h], p1 = heavy_ptr[h + 1];
@@ -103,6 +103,7 @@ combine_partials_kernel(const int32_t* __restrict__ heavy_row,
   for (int col = threadIdx.x; col < D; col += blockDim.x) {
     float acc = partial[(int64_t)p0 * D + col];
     for (int k = p0 + 1; k < p1; ++k) acc = red_call(red, acc, partial[(int64_t)k * D + col]);
+    if (addend) acc = __fadd_rn(addend[orow * D + col], acc);
     if (mean) acc = __fdiv_rn(acc, dn);
     if (row_scale) acc = __fmul_rn(acc, rs);
     out[orow * D + col] = acc;
@@ -211,6 +212,7 @@ bool try_spmm(const KernelCall& c) {
   a.op = c.op;
   a.write_empty = 0;
   for (int i = 0; i < kMaxSlots; ++i) a.a_tab[i] = (c.a_tab && i < c.n_slots) ? c.a_tab[i] : nullptr;
+  a.addend = c.addend;
   int bmode = kBNone;
   bool use_out_csr, walk_in_plain = false;
   // (tensor, target, user map) of the two gathered operands in "row/col of the walked CSR" terms
@@ -320,7 +322,7 @@ bool try_spmm(const KernelCall& c) {
   // D = 48). Gather from a zero-padded copy with 16-byte rows instead and drop the padding from
   // the result: two streaming passes over N x D against the E x D gather.
   if (D % 4 != 0 && D >= 8 && c.bc.ndim == 1 && (bmode == kBNone || bmode == kBScalar) &&
-      !c.a_tab && pad_enabled() && forced_path() != 2 && E >= 4 * csr.n_cols) {
+      !c.a_tab && !c.addend && pad_enabled() && forced_path() != 2 && E >= 4 * csr.n_cols) {
     const int64_t Dp = (D + 3) / 4 * 4;
     const int which = c.mode != kFwd ? 2 : (A == c.lhs ? 0 : 1);
     const int64_t a_rows = which == 2 ? c.out_rows : (which == 0 ? c.lhs_rows : c.rhs_rows);
@@ -412,6 +414,8 @@ bool try_spmm(const KernelCall& c) {
   a.out = c.dst;
   a.out_map = o_map;
 
+  B200_CHECK(!c.addend || (a.red == kSum && !c.mean && o_map == nullptr && c.dst_rows == csr.n_rows),
+             "an addend needs the sum reducer and one output row per reducing node");
   if (o_map != nullptr || c.dst_rows != csr.n_rows) fill_f32(c.dst, c.dst_rows * D, fill_v, s);
   if (csr.n_rows == 0) return true;
 
@@ -436,7 +440,7 @@ bool try_spmm(const KernelCall& c) {
     if (plan.n_seg == 0) return;
     combine_partials_kernel<<<plan.n_heavy, 128, 0, s>>>(
         plan.heavy_row, plan.heavy_ptr, partial.as<float>(), csr.indptr, c.dst, o_map, (int)D,
-        a.red, a.mean, a.row_scale);
+        a.red, a.mean, a.row_scale, a.addend);
     note_kernel(nullptr, 1);
   };
 
@@ -448,7 +452,7 @@ bool try_spmm(const KernelCall& c) {
     const int64_t row_bytes = D * 4;
     bool ok = (lpr == 32) && (bmode == kBNone || scalar_w) && tch > 0 && row_bytes <= 8192 &&
               aligned(A, 16) && o_map == nullptr && c.row_scale == nullptr &&  // mapped / scaled: LDG path
-              c.a_tab == nullptr;
+              c.a_tab == nullptr && c.addend == nullptr;
     const int64_t mean_deg = E / std::max<int64_t>(csr.n_rows, 1);
     // Measured on B200 (profiles/sweep1.txt, profiles/microbench_v1.txt): the LDG path beats the bulk-copy path on
     // this gather (TMA 1-D copies of 2.4 KB rows top out near 20-30 B/clk/SM), so it is opt-in.

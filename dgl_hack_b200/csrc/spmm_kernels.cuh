@@ -54,6 +54,10 @@ struct SpmmArgs {
   const float* a_tab[kMaxSlots];
   // out_map is a plain row list (every listed row is written, rows without edges included)
   int write_empty;
+  // optional (sum reducer): out[row] = row_scale * (addend[row] + sum), addend laid out like out
+  // and allowed to BE out -- the second pass of a two-pass aggregation (partitioned graphs: the
+  // halo-source edges added to the inner-source sums) without a separate add kernel
+  const float* addend;
 };
 
 template <int VEC>
@@ -294,11 +298,17 @@ spmm_kernel(const SpmmArgs a) {
       const int64_t orow = a.out_map ? __ldg(a.out_map + r) : r;
       op = a.out + orow * a.D;
     }
+    const float* addp = (a.addend && !is_seg) ? a.addend + (op - a.out) + cbase : nullptr;
     op += cbase;
     const float dn = (float)(deg > 1 ? deg : 1);
 #pragma unroll
     for (int c = 0; c < CH; ++c) {
       if (col_ok(c)) {
+        if (SUM && addp) {
+          const Vec<VEC> old = ld_vec<VEC>(addp + c * lpr * VEC);
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fadd_rn(old.v[e], acc[c].v[e]);
+        }
         if (a.mean && !is_seg) {
 #pragma unroll
           for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fdiv_rn(acc[c].v[e], dn);

@@ -196,9 +196,17 @@ def gat_attn_proj_backward(feat, attn_l, attn_r, grad_el, grad_er, grad_feat, gr
     del keep
 
 
-def scaled_copy_sum(G, transpose, X, col_scale, row_scale, out):
+def scaled_copy_sum(G, transpose, X, col_scale, row_scale, out, addend=None):
     """Extension: out[r] = row_scale[r] * sum over r's edges of col_scale[c] * X[c] on the in-CSR
-    (transpose False) or the out-CSR (True); GraphConv's normalisation inside the SpMM."""
+    (transpose False) or the out-CSR (True); GraphConv's normalisation inside the SpMM. With
+    `addend` (out's shape; may be `out` itself): out = row_scale * (addend + sum)."""
+    if addend is not None:
+        keep, ptrs = _keep(X, col_scale, row_scale, addend, out)
+        with torch.cuda.device(G.device):
+            check_call(LIB.DGLB200KernelScaledCopySumAdd(G.handle, int(bool(transpose)), *ptrs,
+                                                         _stream(G)))
+        del keep
+        return
     keep, ptrs = _keep(X, col_scale, row_scale, out)
     with torch.cuda.device(G.device):
         check_call(LIB.DGLB200KernelScaledCopySum(G.handle, int(bool(transpose)), *ptrs,

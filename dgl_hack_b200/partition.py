@@ -545,37 +545,74 @@ class _PeerCopySum(torch.autograd.Function):
 
 
 class PeerGather(object):
-    """Single-pass partitioned aggregation (SURVEY 8e option iii, csrc/spmm_kernels.cuh TAB
-    kernels). `blocks` provides, per rank, two forward and two backward staging blocks of
-    rows_max x max_feat floats that every rank of the node can read, plus a barrier. Blocks
-    alternate, so a block is rewritten only after every rank has passed the barrier that follows
-    its last readers (two barriers lie between two writes of the same block)."""
+    """Partitioned aggregation over staged feature blocks. `blocks` provides, per
+    rank, two forward and two backward staging blocks of rows_max x max_feat floats that every
+    rank of the node can read, plus a barrier. Blocks alternate, so a block is rewritten only
+    after every rank has passed the barrier that follows its last readers (two barriers lie
+    between two writes of the same block). Three ways to reduce (B200_HALO_MODE):
 
-    def __init__(self, part, device, blocks, pull=None):
+    "split" (default): the de-duplicated halo rows are pulled into a local buffer by ONE streaming
+        kernel on a side stream (all of its loads are remote; rows listed round-robin over their
+        owners) WHILE the SpMM over the inner-source edges runs; a second SpMM then adds the
+        halo-source edges to the same rows (`addend`, no add kernel, no third pass).
+        Measured at 8 GPUs the pull is the largest item of the GCN epoch, so it is the thing to
+        hide; remote bytes are the de-duplicated ones (0.7x of the per-edge reads).
+    "pull": pull first, then ONE SpMM over all edges gathering from two local slots.
+    "direct": ONE SpMM whose gathers read the peers' blocks in place (SURVEY 8e option iii;
+        per-edge remote reads, no halo buffer)."""
+
+    def __init__(self, part, device, blocks, mode=None):
         from .graph_index import GraphIndex
         self.part, self.device, self.blocks = part, torch.device(device), blocks
-        fs, fd = part.fwd_coo
-        bs, bd = part.bwd_coo
-        self.g_f = GraphIndex.from_coo(part.n_inner + part.n_halo, part.n_inner, fs, fd, device)
-        self.g_b = GraphIndex.from_coo(part.n_inner, part.n_inner + part.n_ohalo, bs, bd, device)
-        self.code = (part.fwd_code.to(device).contiguous(), part.bwd_code.to(device).contiguous())
-        self._turn = [0, 0]
-        # "pull" mode (default; B200_HALO_PULL=0 = per-edge peer loads inside the SpMM): the
-        # de-duplicated halo rows are first pulled into a local buffer by one streaming kernel whose
-        # loads are ALL remote (full NVLink rate), then the same single-pass SpMM gathers from two
-        # local slots (own block, pulled halo). Inside the SpMM only a few percent of the loads in
-        # flight are remote, so NVLink latency caps them near 280 GB/s (measured at 2 GPUs).
-        if pull is None:
-            pull = os.environ.get("B200_HALO_PULL", "1") != "0"
-        self.pull = bool(pull)
+        if mode is None:
+            mode = os.environ.get("B200_HALO_MODE", "split")
+        if mode not in ("split", "pull", "direct"):
+            raise ValueError("B200_HALO_MODE must be split, pull or direct (got %r)" % (mode,))
+        self.mode = mode
         n_in = part.n_inner
         n_ext = (part.n_halo, part.n_ohalo)
-        self.pull_codes = tuple(c[n_in:].contiguous() for c in self.code)
-        self.local_code = tuple(torch.cat([
-            torch.arange(n_in, dtype=torch.int32, device=self.device),
-            (1 << SLOT_SHIFT) + torch.arange(n, dtype=torch.int32, device=self.device)]).contiguous()
-            for n in n_ext)
+        dev = self.device
+        self.code = (part.fwd_code.to(dev).contiguous(), part.bwd_code.to(dev).contiguous())
+        self._turn = [0, 0]
         self._halo_buf = {}
+        if mode in ("pull", "direct"):
+            fs, fd = part.fwd_coo
+            bs, bd = part.bwd_coo
+            self.g_f = GraphIndex.from_coo(n_in + part.n_halo, n_in, fs, fd, dev)
+            self.g_b = GraphIndex.from_coo(n_in, n_in + part.n_ohalo, bs, bd, dev)
+            self.local_code = tuple(torch.cat([
+                torch.arange(n_in, dtype=torch.int32, device=dev),
+                (1 << SLOT_SHIFT) + torch.arange(n, dtype=torch.int32, device=dev)]).contiguous()
+                for n in n_ext)
+        else:
+            # inner -> inner edges serve both directions (in-CSR forward, out-CSR backward)
+            si, di = part.edges_inner
+            self.g_ii = GraphIndex.from_coo(n_in, n_in, si, di, dev)
+            sh, dh = part.edges_halo
+            self.g_fh = GraphIndex.from_coo(max(part.n_halo, 1), n_in, sh, dh, dev)
+            bs, bd = part.bwd_coo
+            away = bd >= n_in
+            self.g_bh = GraphIndex.from_coo(n_in, max(part.n_ohalo, 1), bs[away], bd[away] - n_in,
+                                            dev)
+            # high priority: the pull's few CTAs get onto the SMs as soon as CTAs of the SpMM
+            # that was launched first retire, instead of queueing behind its whole grid
+            self._side = torch.cuda.Stream(device=dev, priority=-1)
+            self._pull_blocks = int(os.environ.get("B200_PULL_CTAS_PER_SM", "2")) * \
+                torch.cuda.get_device_properties(dev).multi_processor_count
+        # pull lists: the remote rows of each direction, round-robin over their owners starting
+        # at rank + 1 (every GPU's egress serves all its readers at once instead of one GPU
+        # serving everybody in turn); dst_row = position in the halo buffer
+        self.pull_codes, self.pull_rows = [], []
+        for c, n in zip(self.code, n_ext):
+            ext = c[n_in:].to(torch.int64)
+            owner = ext >> SLOT_SHIFT
+            cnt = torch.bincount(owner, minlength=part.world)
+            first = torch.cumsum(cnt, 0) - cnt
+            pos = torch.arange(n, device=dev) - first[owner]      # index inside the owner's group
+            key = pos * part.world + (owner - part.rank - 1) % part.world
+            order = torch.argsort(key)
+            self.pull_codes.append(ext[order].to(torch.int32).contiguous())
+            self.pull_rows.append(order.to(torch.int32).contiguous())
 
     def stage(self, which, x, scale):
         """Writes scale * x into this rank's next block of direction `which`; returns its index."""
@@ -592,8 +629,9 @@ class PeerGather(object):
             torch.mul(x, scale.view(-1, 1), out=view)
         return b
 
-    def _pulled(self, which, b, d, like):
-        """Local copy of the rows this rank needs from its peers (one streaming pull kernel)."""
+    def _pulled(self, which, b, d, like, max_blocks=0):
+        """Local copy of the rows this rank needs from its peers (one streaming pull kernel on
+        the current stream)."""
         import ctypes
         from ._lib import LIB, check_call
         n = int(self.pull_codes[which].numel())
@@ -605,21 +643,45 @@ class PeerGather(object):
             bases = self.blocks.bases(b)
             arr = (ctypes.c_void_p * len(bases))(*[int(p) for p in bases])
             check_call(LIB.DGLB200HaloPull(
-                len(bases), arr, ctypes.c_void_p(self.pull_codes[which].data_ptr()), n, d,
-                ctypes.c_void_p(buf.data_ptr()), self.device.index or 0,
+                len(bases), arr, ctypes.c_void_p(self.pull_codes[which].data_ptr()),
+                ctypes.c_void_p(self.pull_rows[which].data_ptr()), n, d,
+                ctypes.c_void_p(buf.data_ptr()), int(max_blocks), self.device.index or 0,
                 ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
         return buf
 
-    def reduce(self, which, b, d, row_scale, like):
+    def _own_base(self, b):
+        bases = self.blocks.bases(b)
+        return bases[self.part.rank if len(bases) > self.part.rank else 0]
+
+    def reduce(self, which, b, d, row_scale, like, barrier=False):
+        """The aggregation of direction `which` over the blocks staged as index b. `barrier`:
+        issue the blocks' barrier first (run() does; tests and phase timings call it themselves)."""
         from . import kernel as K
-        out = like.new_empty((self.part.n_inner, d))
+        n_in = self.part.n_inner
+        out = like.new_empty((n_in, d))
+        if self.mode == "split":
+            n_ext = self.part.n_halo if which == 0 else self.part.n_ohalo
+            cur = torch.cuda.current_stream(self.device)
+            self._side.wait_stream(cur)                       # the staged block is complete
+            with torch.cuda.stream(self._side):
+                if barrier:
+                    self.blocks.barrier()
+                halo = self._pulled(which, b, d, like, self._pull_blocks)
+            own = self.blocks.own_view(b)[: n_in * d].view(n_in, d)
+            # inner-source edges while the halo rows arrive
+            K.scaled_copy_sum(self.g_ii, which == 1, own, None, None if n_ext else row_scale, out)
+            cur.wait_stream(self._side)
+            if n_ext:
+                g = self.g_fh if which == 0 else self.g_bh
+                K.scaled_copy_sum(g, which == 1, halo[:n_ext], None, row_scale, out, addend=out)
+            return out
+        if barrier:
+            self.blocks.barrier()
         g = self.g_f if which == 0 else self.g_b
-        if self.pull:
+        if self.mode == "pull":
             halo = self._pulled(which, b, d, like)
-            own = self.blocks.bases(b)[self.part.rank if len(self.blocks.bases(b)) > self.part.rank
-                                       else 0]
-            K.peer_copy_sum(g, which == 1, [own, halo.data_ptr()], self.local_code[which],
-                            row_scale, out)
+            K.peer_copy_sum(g, which == 1, [self._own_base(b), halo.data_ptr()],
+                            self.local_code[which], row_scale, out)
         else:
             K.peer_copy_sum(g, which == 1, self.blocks.bases(b), self.code[which], row_scale, out)
         return out
@@ -628,8 +690,7 @@ class PeerGather(object):
         shape = x.shape
         x2 = x.reshape(shape[0], -1)
         b = self.stage(which, x2, stage_scale)
-        self.blocks.barrier()
-        out = self.reduce(which, b, x2.shape[1], row_scale, x2)
+        out = self.reduce(which, b, x2.shape[1], row_scale, x2, barrier=True)
         return out.view((self.part.n_inner,) + tuple(shape[1:]))
 
 

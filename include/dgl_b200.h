@@ -434,6 +434,16 @@ int DGLB200KernelScaledCopySum(DGLB200GraphHandle graph, int transpose,
                                const DGLB200Tensor* row_scale, DGLB200Tensor* out_data,
                                void* stream);
 
+/* The same with a second term: out = row_scale * (addend + sum ...), addend shaped like out_data
+ * and allowed to BE out_data (each element is read, then written, by one thread). This is the
+ * second pass of a two-pass aggregation -- partitioned graphs add the halo-source edges to the
+ * inner-source sums with it (python/dgl/transform.py:551-586 semantics: inner and halo edges of a
+ * part) -- without a separate add kernel or a third pass over the rows. */
+int DGLB200KernelScaledCopySumAdd(DGLB200GraphHandle graph, int transpose,
+                                  const DGLB200Tensor* in_data, const DGLB200Tensor* col_scale,
+                                  const DGLB200Tensor* row_scale, const DGLB200Tensor* addend,
+                                  DGLB200Tensor* out_data, void* stream);
+
 /* copy_src + sum over a feature matrix that is spread over several GPUs of one node (partitioned
  * graphs, SURVEY 8e option iii: peer loads inside the SpMM, no pack / send / unpack). Gathered
  * node c of `graph` reads row (node_code[c] & (2^27 - 1)) of block slot_base[node_code[c] >> 27];
@@ -496,13 +506,17 @@ int DGLB200HaloPush(const float* x, int64_t D, int n_peers, void* const* peer, c
                     const int64_t* dst_row, const int32_t* rows, int first_peer, int device,
                     void* stream);
 
-/* Bulk pull of halo rows over NVLink: out[j] = row (codes[j] & (2^27 - 1)) of block
- * slot_base[codes[j] >> 27], j < n_rows, rows of D floats. slot_base: HOST array of n_slots <= 16
- * device pointers (own / peer-mapped blocks), codes: device int32. One streaming kernel whose
- * loads are all remote, so the de-duplicated halo arrives at the link rate; the aggregation then
- * runs single-pass over two LOCAL slots (own block, pulled halo) with DGLB200KernelPeerCopySum. */
-int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* codes, int64_t n_rows,
-                    int64_t D, float* out, int device, void* stream);
+/* Bulk pull of halo rows over NVLink: out[dst_row[i]] = row (codes[i] & (2^27 - 1)) of block
+ * slot_base[codes[i] >> 27], i < n_rows, rows of D floats (dst_row NULL: out[i]). slot_base: HOST
+ * array of n_slots <= 16 device pointers (own / peer-mapped blocks), codes, dst_row: device
+ * int32. One streaming kernel whose loads are all remote, so the de-duplicated halo arrives at
+ * the link rate (list the rows round-robin over their owners: grouped by owner, every rank of
+ * the node reads from the same peer at the same time); the aggregation then gathers from local
+ * memory only. max_blocks > 0 caps the grid (a pull running beside a compute kernel on another
+ * stream leaves it most of every SM; 2 CTAs per SM still saturate the link), <= 0 = default. */
+int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* codes,
+                    const int32_t* dst_row, int64_t n_rows, int64_t D, float* out, int max_blocks,
+                    int device, void* stream);
 
 /* ---- the PackedFunc face: drop-in registration into a loaded libdgl ----
  * DGLValue (include/dgl/runtime/c_runtime_api.h:122-129; DGLType / DGLContext members are

@@ -1,6 +1,6 @@
 """Only the partitioned leg of bench.py (bench_partitioned.run_partitioned), for A/B runs:
 
-    [B200_HALO_PULL=0|1] [B200_BENCH_PROFILE=gpurun_out/x.txt] python -m torch.distributed.run \
+    [B200_HALO_MODE=split|pull|direct] [B200_BENCH_PROFILE=gpurun_out/x.txt] python -m torch.distributed.run \
         --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29533 \
         profiles/bench_partitioned_only.py [--scale 1] [--steps 5] [--tag name]
 
@@ -11,8 +11,9 @@ import json
 import os
 import sys
 
-import torch
-import torch.distributed as dist
+os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")   # barriers are not queued behind SpMM CTAs
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)

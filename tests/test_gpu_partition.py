@@ -63,6 +63,8 @@ def test_partitioned_kernels_match_whole_graph(world, d):
 
 def _nccl_worker(rank, world, port, halo, d, q):
     import torch.distributed as dist
+    if ":" in halo:                      # "direct:<B200_HALO_MODE>"
+        halo, os.environ["B200_HALO_MODE"] = halo.split(":")
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dev = torch.device("cuda", rank)
@@ -106,7 +108,8 @@ def _nccl_worker(rank, world, port, halo, d, q):
 
 
 @pytest.mark.parametrize("world", [2, 4])
-@pytest.mark.parametrize("halo,d", [("direct", 100), ("direct", 47), ("peer", 100), ("nccl", 47)])
+@pytest.mark.parametrize("halo,d", [("direct", 100), ("direct", 47), ("direct:pull", 100),
+                                    ("direct:direct", 100), ("peer", 100), ("nccl", 47)])
 def test_partitioned_multi_gpu(world, halo, d):
     """The real exchanges between processes (one per GPU): peer loads inside the SpMM
     ("direct"), peer-memory pushes ("peer") and NCCL all-to-all-v, against the whole-graph
@@ -133,8 +136,9 @@ def test_partitioned_multi_gpu(world, halo, d):
 
 @pytest.mark.parametrize("world,method", [(2, "range"), (4, "range"), (3, "empty_rank"),
                                           (2, "no_halo")])
-@pytest.mark.parametrize("d", [100, 47, 6])
-def test_direct_gather_one_process(world, method, d):
+@pytest.mark.parametrize("d", [100, 256, 47, 6])
+@pytest.mark.parametrize("mode", ["split", "pull", "direct"])
+def test_direct_gather_one_process(world, method, d, mode, monkeypatch):
     """The single-pass peer-gather kernels (TAB SpMM, forward over all in-edges, backward over
     all out-edges) with every rank's staging block in THIS process (LocalBlocks): same kernels
     and codes as the multi-GPU run, checked against the whole-graph kernel incl. degree scales."""
@@ -142,6 +146,10 @@ def test_direct_gather_one_process(world, method, d):
     from dgl_hack_b200 import backend as F
     from dgl_hack_b200.partition import (Partition, PartitionedGraph, LocalBlocks,
                                          range_partition)
+    # split: halo rows pulled into a local buffer on a side stream while the inner-source edges
+    # are reduced, halo-source edges added by a second pass; pull: pull, then one pass over two
+    # local slots; direct: one pass gathering in place from every rank's block
+    monkeypatch.setenv("B200_HALO_MODE", mode)
     dev = torch.device("cuda:0")
     n, e = 3000, 60000
     src, dst = _graph(n, e, 21, dev)
@@ -166,8 +174,9 @@ def test_direct_gather_one_process(world, method, d):
     plans = [Partition.build(n, src, dst, part, r, world) for r in range(world)]
     if method == "no_halo":
         assert all(p.n_halo == 0 and p.n_ohalo == 0 for p in plans)
-    blocks = LocalBlocks.group(world, plans[0].rows_max, 128, dev)
+    blocks = LocalBlocks.group(world, plans[0].rows_max, 256, dev)
     pgs = [PartitionedGraph(p, dev, halo="direct", blocks=b) for p, b in zip(plans, blocks)]
+    assert all(pg.gather.mode == mode for pg in pgs)
     assert all(pg.halo_path == "direct" for pg in pgs)
     for _ in range(2):               # second round runs on the alternate blocks
         staged = [pg.gather.stage(0, x[p.inner_global].contiguous(), cs[p.inner_global])
