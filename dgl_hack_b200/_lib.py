@@ -50,6 +50,7 @@ SYMBOLS = {
                                              _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_void_p,
                                              _c.POINTER(GraphHandle)]),
     "DGLB200GraphFree": (_c.c_int, [GraphHandle]),
+    "DGLB200GraphIndexBytes": (_c.c_int, [GraphHandle, _c.POINTER(_c.c_int64)]),
     "DGLB200GraphInfo": (_c.c_int, [GraphHandle, _c.POINTER(_c.c_int64)]),
     "DGLB200GraphGetCSR": (_c.c_int, [GraphHandle, _c.c_int, _c.POINTER(_c.c_void_p),
                                       _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_void_p)]),

@@ -240,8 +240,14 @@ namespace b200 {
 
 // graph.cu
 enum Walk { kWalkIn = 0, kWalkOut = 1, kWalkInSorted = 2 };
-inline const Csr& walk_csr(const DGLB200Graph* g, int walk) {
-  return walk == kWalkOut ? g->out : (walk == kWalkInSorted ? g->in_s : g->in);
+// The plain in-CSR's indices / eids (edge-id order inside a row) are NOT resident for graphs
+// built from COO: the hot paths walk in_s and out only, so the handle keeps 4 x E ids (the
+// reference's two CSRs) and rebuilds these two arrays from the out-CSR the first time something
+// asks for them (GetCSR / CopyCSR, dst-operand gradients, id-mapped calls, the fused GAT
+// kernels, the sampler). in.indptr is always there.
+const Csr& in_plain(DGLB200Graph* g, cudaStream_t s);
+inline const Csr& walk_csr(DGLB200Graph* g, int walk, cudaStream_t s) {
+  return walk == kWalkOut ? g->out : (walk == kWalkInSorted ? g->in_s : in_plain(g, s));
 }
 const int32_t* csr_rows(DGLB200Graph* g, int walk, cudaStream_t s);      // row-of-position
 // position in the "other" CSR: in -> out, out -> in, in_sorted -> out

@@ -704,9 +704,10 @@ void fused_gat_forward(DGLB200Graph* g, const float* ft, const float* el, const 
   GatArgs a{};
   int vec, ch;
   gat_plan(H, F, ft, ret, &vec, &ch, &a);
-  a.indptr = g->in.indptr;
-  a.indices = g->in.indices;
-  a.eids = g->in.eids;
+  const Csr& in = in_plain(g, s);
+  a.indptr = in.indptr;
+  a.indices = in.indices;
+  a.eids = in.eids;
   a.n_rows = (int)g->num_dst;
   a.ft = ft;
   a.el = el;

@@ -204,7 +204,7 @@ void run_generic(const KernelCall& c) {
   }
   const bool use_out_csr = (walk == kWalkOut);
   const bool maps_index_out_csr = (c.mode == kFwd);
-  const Csr& csr = walk_csr(g, walk);
+  const Csr& csr = walk_csr(g, walk, s);
 
   GArgs a;
   a.indptr = csr.indptr;

@@ -424,9 +424,9 @@ const int32_t* csr_rows(DGLB200Graph* g, int walk, cudaStream_t s) {
 }
 
 const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s) {
-  if (walk == kWalkInSorted) return g->in_s.to_other;  // built with the index
   const bool out_csr = (walk == kWalkOut);
-  Csr& c = out_csr ? g->out : g->in;
+  if (walk != kWalkInSorted) in_plain(g, s);  // both directions read the in-CSR's edge ids
+  Csr& c = out_csr ? g->out : (walk == kWalkInSorted ? g->in_s : g->in);
   Csr& o = out_csr ? g->in : g->out;
   if (!c.to_other) {
     const int64_t e = g->num_edges;
@@ -633,6 +633,54 @@ static void build_in_sorted(DGLB200Graph* g, cudaStream_t s) {
                     c.indices, c.eids, nullptr, c.to_other, s);
 }
 
+// The plain in-CSR's indices / eids, rebuilt on demand: COOToCSR keyed by dst of the edges in
+// edge-id order (immutable_graph.cc:407-421), the endpoints by edge id coming from the out-CSR.
+const Csr& in_plain(DGLB200Graph* g, cudaStream_t s) {
+  Csr& c = g->in;
+  if (c.indices) return c;
+  const int64_t e = g->num_edges;
+  B200_CUDA(pool_alloc(&c.indices, (size_t)std::max<int64_t>(e, 1) * 4, s));
+  B200_CUDA(pool_alloc(&c.eids, (size_t)std::max<int64_t>(e, 1) * 4, s));
+  if (e == 0) return c;
+  const bool had_coo = g->coo_src != nullptr;
+  const int32_t* src_of = graph_coo(g, 0, s);
+  const int32_t* dst_of = graph_coo(g, 1, s);
+  Scratch ip((size_t)(g->num_dst + 1) * 4, s);
+  coo_to_csr_device(g->num_dst, e, dst_of, src_of, nullptr, ip.as<int32_t>(), c.indices, c.eids,
+                    nullptr, nullptr, s);
+  if (!had_coo) {  // built for this only: not worth 2 x E resident ids
+    pool_free(g->coo_src, s);
+    pool_free(g->coo_dst, s);
+    g->coo_src = g->coo_dst = nullptr;
+  }
+  return c;
+}
+
+// B200_INDEX_LEAN=0 keeps every by-product of the construction resident (A/B runs).
+static bool index_lean() {
+  const char* e = std::getenv("B200_INDEX_LEAN");
+  return !(e && e[0] == '0');
+}
+
+// After construction from COO only the arrays the hot paths walk stay resident: in.indptr,
+// out.(indptr, indices, eids), in_s.(indices, eids) = 4 x E ids, the reference's two CSRs
+// (1.83 GB at the Reddit shape; 11 x E with every by-product kept). Row expansions, position
+// maps and the plain in-CSR come back on demand (csr_rows, csr_to_other, in_plain).
+static void drop_construction_byproducts(DGLB200Graph* g, bool keep_in_plain, cudaStream_t s) {
+  if (!index_lean()) return;
+  auto drop = [&](int32_t*& p) {
+    pool_free(p, s);
+    p = nullptr;
+  };
+  drop(g->in.row);
+  drop(g->out.row);
+  drop(g->out.to_other);
+  drop(g->in_s.to_other);
+  if (keep_in_plain) return;  // a caller-supplied in-CSR may order a row's edges its own way
+  drop(g->in.indices);
+  drop(g->in.eids);
+}
+
 // ---------------------------------------------------------------- typed adjacency
 __global__ void scatter_coo_kernel(const int32_t* __restrict__ row, const int32_t* __restrict__ col,
                                    const int32_t* __restrict__ eid, int64_t n,
@@ -660,9 +708,10 @@ const int32_t* graph_coo(DGLB200Graph* g, int which, cudaStream_t s) {
     B200_CUDA(pool_alloc(&cs, eb, s));
     B200_CUDA(pool_alloc(&cd, eb, s));
     if (e > 0) {
-      const int32_t* in_row = csr_rows(g, kWalkIn, s);
+      // from the out-CSR (always resident): row = src, column = dst
+      const int32_t* out_row = csr_rows(g, kWalkOut, s);
       const int blocks = (int)std::min<int64_t>((e + 255) / 256, 148 * 16);
-      scatter_coo_kernel<<<blocks, 256, 0, s>>>(in_row, g->in.indices, g->in.eids, e, cd, cs);
+      scatter_coo_kernel<<<blocks, 256, 0, s>>>(out_row, g->out.indices, g->out.eids, e, cs, cd);
       note_kernel(nullptr, 1);
     }
     g->coo_dst = cd;
@@ -866,6 +915,7 @@ int DGLB200GraphCreateFromCOO(int64_t num_src, int64_t num_dst, int64_t num_edge
     coo_to_csr_device(num_src, e, g->in.indices, g->in.row, g->in.eids, g->out.indptr,
                       g->out.indices, g->out.eids, nullptr, g->out.to_other, s);
     build_in_sorted(g, s);
+    drop_construction_byproducts(g, false, s);
   } catch (...) {
     g->in_s.indptr = nullptr;
     free_csr(g->in_s, s);
@@ -915,6 +965,7 @@ int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edge
     g->ids_checked = false;
     read_bad_flag(g, s, "DGLB200GraphCreateFromCSR: indptr / indices / edge ids out of range");
     build_in_sorted(g, s);
+    drop_construction_byproducts(g, true, s);
     B200_CUDA(cudaStreamSynchronize(s));  // host buffers may be released by the caller now
   } catch (...) {
     g->in_s.indptr = nullptr;
@@ -950,6 +1001,29 @@ int DGLB200GraphFree(DGLB200GraphHandle g) {
   API_END();
 }
 
+// Bytes of index arrays the handle holds right now (CSR arrays, lazily built by-products,
+// COO by edge id, typed adjacency, segment plans excluded).
+int DGLB200GraphIndexBytes(DGLB200GraphHandle g, int64_t* bytes) {
+  API_BEGIN();
+  B200_CHECK(g && bytes, "NULL argument");
+  const int64_t e4 = std::max<int64_t>(g->num_edges, 1) * 4;
+  int64_t n = 0;
+  auto csr = [&](const Csr& c, bool own_indptr) {
+    if (c.indptr && own_indptr) n += (c.n_rows + 1) * 4;
+    for (const int32_t* p : {c.indices, c.eids, c.row, c.to_other})
+      if (p) n += e4;
+  };
+  csr(g->in, true);
+  csr(g->out, true);
+  csr(g->in_s, false);
+  for (const int32_t* p : {g->coo_src, g->coo_dst, g->ty.in.ids, g->ty.in.eids, g->ty.in.types,
+                           g->ty.out.ids, g->ty.out.eids, g->ty.out.types, g->ty.bt_src,
+                           g->ty.bt_dst, g->ty.bt_eid})
+    if (p) n += e4;
+  *bytes = n;
+  API_END();
+}
+
 int DGLB200GraphInfo(DGLB200GraphHandle g, int64_t* info) {
   API_BEGIN();
   B200_CHECK(g && info, "NULL argument");
@@ -964,6 +1038,11 @@ int DGLB200GraphGetCSR(DGLB200GraphHandle g, int transpose, const int32_t** indp
                        const int32_t** indices, const int32_t** eids) {
   API_BEGIN();
   B200_CHECK(g, "NULL graph");
+  if (!transpose && !g->in.indices) {  // rebuilt on the default stream; usable from any stream
+    ensure_device(g->device);
+    in_plain(g, nullptr);
+    B200_CUDA(cudaStreamSynchronize(nullptr));
+  }
   const Csr& c = transpose ? g->out : g->in;
   if (indptr) *indptr = c.indptr;
   if (indices) *indices = c.indices;
@@ -977,7 +1056,7 @@ int DGLB200GraphCopyCSR(DGLB200GraphHandle g, int transpose, int32_t* indptr, in
   B200_CHECK(g, "NULL graph");
   ensure_device(g->device);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const Csr& c = transpose ? g->out : g->in;
+  const Csr& c = transpose ? g->out : ((indices || eids) ? in_plain(g, s) : g->in);
   bool host = false;
   auto copy = [&](int32_t* dst, const int32_t* src, int64_t n) {
     if (!dst || n <= 0) return;

@@ -164,7 +164,8 @@ void sample_neighbors(DGLB200Graph* g, const int64_t* seeds, int64_t n_seeds, in
                       bool replace, uint64_t rng_seed, const int64_t* offsets, int64_t* out_src,
                       int64_t* out_dst, int64_t* out_eid, int64_t* out_slot, cudaStream_t s) {
   if (n_seeds == 0) return;
-  SampleArgs a{g->in.indptr, g->in.indices, g->in.eids, seeds, offsets, out_src, out_dst, out_eid,
+  const Csr& in = in_plain(g, s);
+  SampleArgs a{in.indptr, in.indices, in.eids, seeds, offsets, out_src, out_dst, out_eid,
                out_slot, n_seeds, fanout, replace ? 1 : 0, mix64(rng_seed)};
   const int blocks = (int)std::min<int64_t>((n_seeds + 7) / 8, 148 * 16);
   if (replace || fanout < 0) {

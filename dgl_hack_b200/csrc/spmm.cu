@@ -310,7 +310,7 @@ bool try_spmm(const KernelCall& c) {
   }
   // forward: reference sum order
   const int walk = use_out_csr ? kWalkOut : (walk_in_plain ? kWalkIn : kWalkInSorted);
-  const Csr& csr = walk_csr(g, walk);
+  const Csr& csr = walk_csr(g, walk, s);
   const int row_tgt = use_out_csr ? kSrc : kDst;
   const int col_tgt = use_out_csr ? kDst : kSrc;
   const bool maps_index_out_csr = (c.mode == kFwd);

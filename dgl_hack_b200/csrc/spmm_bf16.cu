@@ -194,7 +194,7 @@ void spmm_bf16(DGLB200Graph* g, int transpose, const void* in, const float* col_
   B200_CHECK(D > 0 && D % 8 == 0 && D <= 32 * 4 * 8,
              "bf16 aggregation: the row pitch must be a multiple of 8 elements, at most 1024");
   const int walk = transpose ? kWalkOut : kWalkInSorted;
-  const Csr& csr = walk_csr(g, walk);
+  const Csr& csr = walk_csr(g, walk, s);
   if (csr.n_rows == 0) return;
   Bf16Args a;
   a.indptr = csr.indptr;

@@ -190,7 +190,7 @@ class GraphIndex(object):
         cache = self.__dict__.setdefault("_deg_cache", {})
         key = ("mean", dtype)
         if key not in cache:
-            cache[key] = self.in_degrees().to(dtype).clamp(min=1)
+            cache[key] = self._degrees(0).to(dtype).clamp(min=1)
         return cache[key]
 
     def _degrees_uncached(self, which):
@@ -202,7 +202,15 @@ class GraphIndex(object):
         return out
 
     def in_degrees(self):
-        return self._degrees(0)
+        """A fresh tensor per call (as the reference): in-place edits by the caller must not reach
+        the cached degrees behind `mean_divisor` and GraphConv's norms."""
+        return self._degrees(0).clone()
 
     def out_degrees(self):
-        return self._degrees(1)
+        return self._degrees(1).clone()
+
+    def index_bytes(self):
+        """Bytes of index arrays resident on the device right now (DGLB200GraphIndexBytes)."""
+        n = ctypes.c_int64(0)
+        check_call(LIB.DGLB200GraphIndexBytes(self._handle, ctypes.byref(n)))
+        return int(n.value)

@@ -94,6 +94,13 @@ int DGLB200GraphCreateFromCSR(int64_t num_src, int64_t num_dst, int64_t num_edge
 
 int DGLB200GraphFree(DGLB200GraphHandle g);
 
+/* Bytes of index arrays the handle holds right now (CSR arrays and their lazily built
+ * by-products, endpoints by edge id, typed adjacency; segment plans excluded). A graph built
+ * from COO keeps 4 x E int32 ids + the two indptr arrays -- what the reference's in-CSR +
+ * out-CSR hold (include/dgl/immutable_graph.h:242-246: indptr / indices / edge_ids per CSR) --
+ * and rebuilds the plain in-CSR order, row expansions and position maps on demand. */
+int DGLB200GraphIndexBytes(DGLB200GraphHandle g, int64_t* bytes);
+
 /* num_src, num_dst, num_edges, device -> info[4]. */
 int DGLB200GraphInfo(DGLB200GraphHandle g, int64_t* info);
 

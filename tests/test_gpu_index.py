@@ -149,3 +149,30 @@ def test_bad_csr_arrays_are_rejected():
         arrs[which][pos] = val
         with pytest.raises(DGLError):
             B.GraphIndex.from_csr(50, 60, tuple(arrs[:3]), tuple(arrs[3:]))
+
+
+def test_index_memory_is_two_csrs():
+    """a graph built from COO keeps 4 x E ids + two indptr arrays resident (what
+    the reference's in-CSR + out-CSR hold, immutable_graph.h:242-246) through forward + backward
+    message passing; the plain in-CSR order, rebuilt on demand, is still the reference's."""
+    import torch
+    import dgl_hack_b200 as B
+    from dgl_hack_b200 import backend as F
+    from oracle import oracle as O
+    ns, nd, ne = 4000, 3000, 90000
+    src, dst = cases.powerlaw_graph(ns, nd, ne, 0.6, 11)
+    g = B.GraphIndex.from_coo(ns, nd, src, dst, "cuda:0")
+    two_csrs = 4 * (4 * ne + (ns + 1) + (nd + 1))
+    assert g.index_bytes() == two_csrs
+    x = torch.rand(ns, 64, device="cuda").requires_grad_(True)
+    for red in ("sum", "max", "mean"):
+        out = F.copy_reduce(red, g, 0, x, nd)
+        out.backward(torch.rand_like(out))
+    w = torch.rand(ne, 1, device="cuda")
+    F.binary_reduce("sum", "mul", g, 0, 2, x.detach(), w, nd)
+    assert g.index_bytes() == two_csrs, "message passing must not grow the index"
+    og = O.Graph(ns, nd, src, dst)
+    for a, b in zip(g.in_csr + g.out_csr, og.in_csr + og.out_csr):
+        assert np.array_equal(a.astype(np.int64), b)
+    # + the plain in-CSR (and the out-CSR's row expansion its rebuild used), now resident
+    assert two_csrs + 4 * 2 * ne <= g.index_bytes() <= two_csrs + 4 * 3 * ne
