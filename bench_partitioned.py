@@ -233,7 +233,8 @@ def run_partitioned(rank, world, dev, scale=1, steps=10, warmup=3, epochs=5, par
         phases = {k: round(v, 4) for k, v in phases.items()}
         # the same kernels, indices and sizes with every slot aliased to local memory
         real = gth.blocks
-        gth.blocks = LocalBlocks.group(world, p.rows_max, d, dev, alias_rank=rank)[rank]
+        gth.blocks = LocalBlocks.group(world, p.rows_max, d, dev, alias_rank=rank,
+                                       ext_max=p.ext_max)[rank]
         local_ms = _timed(agg_step, steps, warmup, dev, world)
         gth.blocks = real
         if world > 1:

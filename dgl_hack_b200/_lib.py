@@ -102,6 +102,9 @@ SYMBOLS = {
     "DGLB200PeerFree": (_c.c_int, [_c.c_void_p]),
     "DGLB200HaloPush": (_c.c_int, [_c.c_void_p, _c.c_int64, _c.c_int, _c.c_void_p, _c.c_void_p,
                                    _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p]),
+    "DGLB200HaloScatter": (_c.c_int, [_c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p,
+                                      _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int, _c.c_int,
+                                      _c.c_void_p]),
     "DGLB200HaloPull": (_c.c_int, [_c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int64,
                                    _c.c_int64, _c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p]),
     "DGLB200MetisPartition": (_c.c_int, [_c.c_int64, _c.c_void_p, _c.c_void_p, _c.c_void_p,

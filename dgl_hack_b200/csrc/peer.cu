@@ -106,6 +106,65 @@ __global__ void __launch_bounds__(256) halo_pull_kernel(const PullArgs a) {
   }
 }
 
+// Push of halo rows (the mirror of the pull): row rows[i] of x, times scale[rows[i]] when a scale
+// is given, is stored as row (code & kPullRowMask) of buffer tab[code >> 27], code = codes[i].
+// Every store is a peer store (posted: no round trip, so the link is not limited by the number
+// of outstanding remote reads as the pull is). Same work split as the pull: one 16-byte chunk
+// per item, four items per thread, the list interleaved over the destination ranks by the
+// caller.
+struct ScatterArgs {
+  float* tab[kMaxPeers];
+  const int32_t* codes;
+  const int32_t* rows;
+  const float* scale;
+  const float* x;
+  int64_t n_rows, D;
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(256) halo_scatter_kernel(const ScatterArgs a) {
+  const int nvec = (int)(a.D / VEC);
+  const int64_t total = a.n_rows * nvec;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < total;
+       base += stride * kPullUnroll) {
+    float4 v[kPullUnroll];
+    float* o[kPullUnroll];
+#pragma unroll
+    for (int k = 0; k < kPullUnroll; ++k) {
+      const int64_t idx = base + k * stride;
+      o[k] = nullptr;
+      if (idx < total) {
+        const int64_t i = idx / nvec;
+        const int c = (int)(idx - i * nvec);
+        const int32_t code = __ldg(a.codes + i);
+        const int64_t r = __ldg(a.rows + i);
+        const float* src = a.x + r * a.D + c * VEC;
+        if (VEC == 4) v[k] = __ldg(reinterpret_cast<const float4*>(src));
+        else v[k].x = __ldg(src);
+        if (a.scale) {
+          const float sc = __ldg(a.scale + r);
+          v[k].x = __fmul_rn(v[k].x, sc);
+          if (VEC == 4) {
+            v[k].y = __fmul_rn(v[k].y, sc);
+            v[k].z = __fmul_rn(v[k].z, sc);
+            v[k].w = __fmul_rn(v[k].w, sc);
+          }
+        }
+        o[k] = a.tab[(code >> kPullSlotShift) & (kMaxPeers - 1)] +
+               (int64_t)(code & kPullRowMask) * a.D + c * VEC;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kPullUnroll; ++k) {
+      if (o[k]) {
+        if (VEC == 4) *reinterpret_cast<float4*>(o[k]) = v[k];
+        else *o[k] = v[k].x;
+      }
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -232,6 +291,45 @@ int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* co
   else halo_pull_kernel<1><<<blocks, 256, 0, s>>>(a);
   B200_CUDA(cudaGetLastError());
   note_kernel("halo_pull", 1);
+  API_END();
+}
+
+// Pushes n_rows rows of D floats: buffer[codes[i] >> 27][codes[i] & (2^27 - 1)] =
+// scale[rows[i]] * x[rows[i]] (scale NULL: plain copy). slot_base is a HOST array of n_slots <= 16
+// device pointers (the ranks' receive buffers of row pitch D, own or peer-mapped), codes / rows
+// DEVICE int32 arrays, scale a device float vector over x's rows. max_blocks as in
+// DGLB200HaloPull. Ordering against the readers of the buffers is the caller's.
+int DGLB200HaloScatter(int n_slots, void* const* slot_base, const int32_t* codes,
+                       const int32_t* rows, const float* scale, int64_t n_rows, int64_t D,
+                       const float* x, int max_blocks, int device, void* stream) {
+  API_BEGIN();
+  B200_CHECK(n_slots >= 1 && n_slots <= kMaxPeers && slot_base, "DGLB200HaloScatter: 1 to 16 slots");
+  B200_CHECK(D > 0 && n_rows >= 0, "DGLB200HaloScatter: bad size");
+  if (n_rows == 0) return 0;
+  B200_CHECK(codes && rows && x, "DGLB200HaloScatter: NULL argument");
+  ScatterArgs a{};
+  bool al = (D % 4 == 0) && (reinterpret_cast<uintptr_t>(x) % 16 == 0);
+  for (int q = 0; q < n_slots; ++q) {
+    // a rank that receives nothing may have no buffer: its slot is never addressed
+    a.tab[q] = static_cast<float*>(slot_base[q]);
+    al = al && (reinterpret_cast<uintptr_t>(slot_base[q]) % 16 == 0);
+  }
+  a.codes = codes;
+  a.rows = rows;
+  a.scale = scale;
+  a.x = x;
+  a.n_rows = n_rows;
+  a.D = D;
+  B200_CUDA(cudaSetDevice(device));
+  const int64_t items = n_rows * (al ? D / 4 : D);
+  const int cap = max_blocks > 0 ? max_blocks : 148 * 8;
+  const int blocks = (int)std::max<int64_t>(
+      1, std::min<int64_t>((items + 256 * kPullUnroll - 1) / (256 * kPullUnroll), cap));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (al) halo_scatter_kernel<4><<<blocks, 256, 0, s>>>(a);
+  else halo_scatter_kernel<1><<<blocks, 256, 0, s>>>(a);
+  B200_CUDA(cudaGetLastError());
+  note_kernel("halo_scatter", 1);
   API_END();
 }
 

@@ -155,6 +155,8 @@ class Partition(object):
         self.fwd_coo = self.bwd_coo = self.fwd_code = self.bwd_code = None
         self.n_ohalo = 0
         self.rows_max = 0
+        self.push = None       # [(rows, codes)] forward / backward push lists (push mode)
+        self.ext_max = 0
 
     @classmethod
     def build(cls, num_nodes, src, dst, part, rank, world):
@@ -223,6 +225,7 @@ class Partition(object):
         o_src, o_dst = src[mine_src], dst[mine_src]
         away = part[o_dst] != rank
         ohalo = torch.unique(o_dst[away])
+        ohalo = ohalo[torch.argsort(part[ohalo] * num_nodes + ohalo)]   # grouped by owner, like halo
         self.n_ohalo = int(ohalo.numel())
         g2c = torch.full((num_nodes,), -1, dtype=torch.int64, device=dev)
         g2c[self.inner_global] = torch.arange(self.n_inner, device=dev)
@@ -230,6 +233,45 @@ class Partition(object):
         g2c[ohalo] = self.n_inner + torch.arange(self.n_ohalo, device=dev)
         self.bwd_coo = (lsrc, g2c[o_dst])
         self.bwd_code = torch.cat([code[self.inner_global], code[ohalo]]).to(torch.int32)
+        self._build_push_plan(num_nodes, src, dst, part, e_src, e_dst)
+
+    def _build_push_plan(self, num_nodes, src, dst, part, e_src, e_dst):
+        """Push lists of the "push" reduction mode (PeerGather): which of this rank's rows every
+        peer needs and where they land in the peer's receive buffer. Forward: the peer's halo
+        (sources grouped by owner, ascending id: this rank's block starts after the blocks of the
+        owners below it); backward: the peer's remote destinations, same layout. Every rank
+        derives all offsets from the global COO -- no communication. `push[which]` =
+        (rows int32, codes int32): row rows[i] goes to row (codes[i] & mask) of rank
+        (codes[i] >> 27)'s buffer; the list is interleaved over the destination ranks starting at
+        rank + 1, so no GPU's ingress takes all senders at once."""
+        rank, world, dev = self.rank, self.world, src.device
+        cross = part[src] != part[dst]
+        cs, cd = src[cross], dst[cross]
+        g2l = torch.full((num_nodes,), -1, dtype=torch.int64, device=dev)
+        g2l[self.inner_global] = torch.arange(self.n_inner, device=dev)
+        self.push = []
+        # forward: (node = source, consumer = owner of the destination);
+        # backward: (node = destination, consumer = owner of the source)
+        for node, consumer in ((cs, part[cd]), (cd, part[cs])):
+            uk = torch.unique(node * world + consumer)
+            un, uc = uk // world, uk % world            # ascending node id inside a consumer
+            owner = part[un]
+            need = torch.bincount(uc * world + owner, minlength=world * world).view(world, world)
+            mine = owner == rank
+            un, uc = un[mine], uc[mine]
+            order = torch.argsort(uc * num_nodes + un)  # grouped by consumer, ascending id
+            un, uc = un[order], uc[order]
+            cnt = torch.bincount(uc, minlength=world)
+            first = torch.cumsum(cnt, 0) - cnt
+            pos = torch.arange(un.numel(), device=dev) - first[uc]
+            base = need[:, :rank].sum(1)                # my block's first row in each consumer
+            codes = (uc << SLOT_SHIFT) + base[uc] + pos
+            rr = torch.argsort(pos * world + (uc - rank - 1) % world)
+            self.push.append((g2l[un][rr].to(torch.int32).contiguous(),
+                              codes[rr].to(torch.int32).contiguous()))
+            assert int(need[rank].sum()) == (self.n_halo if len(self.push) == 1 else self.n_ohalo)
+            # the largest receive buffer any rank needs (rows): the same number on every rank
+            self.ext_max = max(self.ext_max, int(need.sum(1).max()))
 
     @classmethod
     def from_files(cls, directory, rank, world, device="cpu"):
@@ -549,9 +591,16 @@ class PeerGather(object):
     rank, two forward and two backward staging blocks of rows_max x max_feat floats that every
     rank of the node can read, plus a barrier. Blocks alternate, so a block is rewritten only
     after every rank has passed the barrier that follows its last readers (two barriers lie
-    between two writes of the same block). Three ways to reduce (B200_HALO_MODE):
+    between two writes of the same block). Four ways to reduce (B200_HALO_MODE):
 
-    "split" (default): the de-duplicated halo rows are pulled into a local buffer by ONE streaming
+    "push" (default): every rank STORES the rows its peers need straight into their receive
+        buffers (one streaming kernel on a high-priority side stream, fused with the degree
+        scaling; peer stores are posted, so the link is not bounded by outstanding remote reads
+        the way a pull is) while the SpMM over the inner-source edges runs on x itself -- no
+        staging copy at all; after the barrier a second SpMM adds the halo-source edges from the
+        receive buffer to the same rows (`addend`). Backward is the same thing on the out-edges:
+        no reduction of received gradients.
+    "split": the de-duplicated halo rows are pulled into a local buffer by ONE streaming
         kernel on a side stream (all of its loads are remote; rows listed round-robin over their
         owners) WHILE the SpMM over the inner-source edges runs; a second SpMM then adds the
         halo-source edges to the same rows (`addend`, no add kernel, no third pass).
@@ -565,9 +614,11 @@ class PeerGather(object):
         from .graph_index import GraphIndex
         self.part, self.device, self.blocks = part, torch.device(device), blocks
         if mode is None:
-            mode = os.environ.get("B200_HALO_MODE", "split")
-        if mode not in ("split", "pull", "direct"):
-            raise ValueError("B200_HALO_MODE must be split, pull or direct (got %r)" % (mode,))
+            mode = os.environ.get("B200_HALO_MODE", "push")
+        if mode not in ("push", "split", "pull", "direct"):
+            raise ValueError("B200_HALO_MODE must be push, split, pull or direct (got %r)" % (mode,))
+        if mode == "push" and (part.push is None or not getattr(blocks, "has_recv", False)):
+            mode = "split"           # no receive buffers in this block provider
         self.mode = mode
         n_in = part.n_inner
         n_ext = (part.n_halo, part.n_ohalo)
@@ -599,6 +650,9 @@ class PeerGather(object):
             self._side = torch.cuda.Stream(device=dev, priority=-1)
             self._pull_blocks = int(os.environ.get("B200_PULL_CTAS_PER_SM", "2")) * \
                 torch.cuda.get_device_properties(dev).multi_processor_count
+            if mode == "push":
+                self._push_lists = [(r.to(dev), c.to(dev)) for r, c in part.push]
+                self._pending = [None, None]
         # pull lists: the remote rows of each direction, round-robin over their owners starting
         # at rank + 1 (every GPU's egress serves all its readers at once instead of one GPU
         # serving everybody in turn); dst_row = position in the halo buffer
@@ -615,10 +669,36 @@ class PeerGather(object):
             self.pull_rows.append(order.to(torch.int32).contiguous())
 
     def stage(self, which, x, scale):
-        """Writes scale * x into this rank's next block of direction `which`; returns its index."""
+        """Writes scale * x into this rank's next block of direction `which`; returns its index.
+        Push mode: stores the rows the peers need straight into their receive buffers instead
+        (side stream), and keeps x / scale for the inner-source pass of reduce()."""
         b = 2 * which + self._turn[which]
         self._turn[which] ^= 1
         n, d = x.shape
+        if self.mode == "push":
+            import ctypes
+            from ._lib import LIB, check_call
+            if d > self.blocks.max_feat:
+                raise ValueError("feature width %d exceeds the receive buffers (max_feat=%d)"
+                                 % (d, self.blocks.max_feat))
+            rows, codes = self._push_lists[which]
+            cur = torch.cuda.current_stream(self.device)
+            self._side.wait_stream(cur)                       # x is complete
+            if int(rows.numel()):
+                bases = self.blocks.rbases(b)
+                arr = (ctypes.c_void_p * len(bases))(*[int(p) for p in bases])
+                with torch.cuda.stream(self._side):
+                    check_call(LIB.DGLB200HaloScatter(
+                        len(bases), arr, ctypes.c_void_p(codes.data_ptr()),
+                        ctypes.c_void_p(rows.data_ptr()),
+                        ctypes.c_void_p(scale.data_ptr()) if scale is not None else None,
+                        int(rows.numel()), d, ctypes.c_void_p(x.data_ptr()), self._pull_blocks,
+                        self.device.index or 0, ctypes.c_void_p(self._side.cuda_stream)))
+            # no record_stream: reduce() makes the current stream wait for the side stream before
+            # x can be released, and record_stream would keep freed blocks out of the allocator's
+            # pool until the side stream is polled (new cudaMallocs: +4 ms of host time per epoch)
+            self._pending[which] = (x, scale)
+            return b
         if d > self.blocks.max_feat:
             raise ValueError("feature width %d exceeds the staging blocks (max_feat=%d)"
                              % (d, self.blocks.max_feat))
@@ -659,6 +739,21 @@ class PeerGather(object):
         from . import kernel as K
         n_in = self.part.n_inner
         out = like.new_empty((n_in, d))
+        if self.mode == "push":
+            n_ext = self.part.n_halo if which == 0 else self.part.n_ohalo
+            x, scale = self._pending[which]
+            cur = torch.cuda.current_stream(self.device)
+            if barrier:
+                with torch.cuda.stream(self._side):           # after this rank's pushes
+                    self.blocks.barrier()
+            # inner-source edges (own rows, scaled per gathered row) while the halo rows land
+            K.scaled_copy_sum(self.g_ii, which == 1, x, scale, None if n_ext else row_scale, out)
+            cur.wait_stream(self._side)
+            if n_ext:
+                g = self.g_fh if which == 0 else self.g_bh
+                halo = self.blocks.recv_view(b)[: n_ext * d].view(n_ext, d)
+                K.scaled_copy_sum(g, which == 1, halo, None, row_scale, out, addend=out)
+            return out
         if self.mode == "split":
             n_ext = self.part.n_halo if which == 0 else self.part.n_ohalo
             cur = torch.cuda.current_stream(self.device)
@@ -705,11 +800,31 @@ class LocalBlocks(object):
         self.max_feat = group["max_feat"]
 
     @classmethod
-    def group(cls, world, rows_max, max_feat, device, alias_rank=None):
+    def group(cls, world, rows_max, max_feat, device, alias_rank=None, ext_max=None):
+        """ext_max (Partition.ext_max) also allocates the receive buffers of the push mode."""
+        k = world if alias_rank is None else 1
         bufs = [[torch.zeros(max(rows_max, 1) * max_feat, device=device) for _ in range(4)]
-                for _ in range(world if alias_rank is None else 1)]
+                for _ in range(k)]
         g = {"bufs": bufs, "max_feat": int(max_feat), "world": world, "alias": alias_rank}
+        if ext_max is not None:
+            g["rbufs"] = [[torch.zeros(max(ext_max, 1) * max_feat, device=device)
+                           for _ in range(4)] for _ in range(k)]
         return [cls(g, r) for r in range(world)]
+
+    def _rmine(self):
+        return self._group["rbufs"][0 if self._group["alias"] is not None else self.rank]
+
+    def recv_view(self, b):
+        return self._rmine()[b]
+
+    def rbases(self, b):
+        if self._group["alias"] is not None:
+            return [self._rmine()[b].data_ptr()] * self._group["world"]
+        return [bufs[b].data_ptr() for bufs in self._group["rbufs"]]
+
+    @property
+    def has_recv(self):
+        return "rbufs" in self._group
 
     def _mine(self):
         return self._group["bufs"][0 if self._group["alias"] is not None else self.rank]
@@ -723,7 +838,10 @@ class LocalBlocks(object):
         return [bufs[b].data_ptr() for bufs in self._group["bufs"]]
 
     def barrier(self):
-        pass
+        # one process: every rank's kernels are on this device's streams (aliased blocks = the
+        # all-local timing of ONE rank: nothing to wait for)
+        if self._group["alias"] is None:
+            torch.cuda.synchronize()
 
     def close(self):
         pass
@@ -749,12 +867,17 @@ class IpcBlocks(object):
         k, me = part.world, part.rank
         dev_index = self.device.index or 0
         n = max(part.rows_max, 1) * self.max_feat
-        handles = torch.zeros(4, 64, dtype=torch.uint8)
+        # buffers 0..3: staging blocks of this rank's rows (pull / split / direct modes);
+        # 4..7: receive buffers of the push mode (largest halo of any rank)
+        self.has_recv = part.push is not None
+        sizes = [n] * 4 + ([max(part.ext_max, 1) * self.max_feat] * 4 if self.has_recv else [])
+        nb = len(sizes)
+        handles = torch.zeros(nb, 64, dtype=torch.uint8)
         ok, err = 1.0, None
         try:
-            for i in range(4):
+            for i in range(nb):
                 ptr, h = ctypes.c_void_p(), (ctypes.c_ubyte * 64)()
-                check_call(LIB.DGLB200PeerAlloc(n * 4, dev_index, ctypes.byref(ptr), h))
+                check_call(LIB.DGLB200PeerAlloc(sizes[i] * 4, dev_index, ctypes.byref(ptr), h))
                 self._own.append(ptr.value)
                 handles[i] = torch.tensor(list(h), dtype=torch.uint8)
         except Exception as e:  # agreed on below: every rank takes the same path
@@ -767,11 +890,11 @@ class IpcBlocks(object):
         hd = handles.to(self.device)
         allh = [torch.empty_like(hd) for _ in range(k)]
         dist.all_gather(allh, hd)
-        self._ptr = [[0] * k for _ in range(4)]
+        self._ptr = [[0] * k for _ in range(nb)]
         try:
             for q in range(k):
                 hq = allh[q].cpu()
-                for i in range(4):
+                for i in range(nb):
                     if q == me:
                         self._ptr[i][q] = self._own[i]
                         continue
@@ -787,9 +910,16 @@ class IpcBlocks(object):
             if required:
                 raise RuntimeError("IpcBlocks: peer mapping failed on some rank: %r" % (err,))
             return None
-        self._views = [torch.as_tensor(_RawCuda(p, n), device=self.device) for p in self._own]
+        self._views = [torch.as_tensor(_RawCuda(p, m), device=self.device)
+                       for p, m in zip(self._own, sizes)]
         self._flag = torch.zeros(1, device=self.device)
         return self
+
+    def recv_view(self, b):
+        return self._views[4 + b]
+
+    def rbases(self, b):
+        return self._ptr[4 + b]
 
     def _agree(self, ok):
         t = torch.tensor([ok], device=self.device)

@@ -525,6 +525,18 @@ int DGLB200HaloPull(int n_slots, const void* const* slot_base, const int32_t* co
                     const int32_t* dst_row, int64_t n_rows, int64_t D, float* out, int max_blocks,
                     int device, void* stream);
 
+/* Push of halo rows over NVLink (the mirror of DGLB200HaloPull; peer STORES are posted, so the
+ * link is not bounded by outstanding remote reads): row (codes[i] & (2^27 - 1)) of buffer
+ * slot_base[codes[i] >> 27] = scale[rows[i]] * x[rows[i]], i < n_rows, rows of D floats; scale
+ * NULL = plain copy. slot_base: HOST array of n_slots <= 16 device pointers (the ranks' receive
+ * buffers, own / peer-mapped), codes, rows: device int32, scale: device float over x's rows.
+ * The partition plan lists the rows round-robin over the destination ranks. The receivers read
+ * their buffers after a barrier that follows this kernel in stream order. No counterpart in the
+ * reference (python/dgl/transform.py:551-640 defines what a part's halo is, not how it moves). */
+int DGLB200HaloScatter(int n_slots, void* const* slot_base, const int32_t* codes,
+                       const int32_t* rows, const float* scale, int64_t n_rows, int64_t D,
+                       const float* x, int max_blocks, int device, void* stream);
+
 /* ---- the PackedFunc face: drop-in registration into a loaded libdgl ----
  * DGLValue (include/dgl/runtime/c_runtime_api.h:122-129; DGLType / DGLContext members are
  * 8 bytes as well) and DGLPackedCFunc (:301-306). */

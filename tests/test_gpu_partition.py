@@ -108,8 +108,9 @@ def _nccl_worker(rank, world, port, halo, d, q):
 
 
 @pytest.mark.parametrize("world", [2, 4])
-@pytest.mark.parametrize("halo,d", [("direct", 100), ("direct", 47), ("direct:pull", 100),
-                                    ("direct:direct", 100), ("peer", 100), ("nccl", 47)])
+@pytest.mark.parametrize("halo,d", [("direct", 100), ("direct", 47), ("direct:split", 100),
+                                    ("direct:pull", 100), ("direct:direct", 100), ("peer", 100),
+                                    ("nccl", 47)])
 def test_partitioned_multi_gpu(world, halo, d):
     """The real exchanges between processes (one per GPU): peer loads inside the SpMM
     ("direct"), peer-memory pushes ("peer") and NCCL all-to-all-v, against the whole-graph
@@ -137,7 +138,7 @@ def test_partitioned_multi_gpu(world, halo, d):
 @pytest.mark.parametrize("world,method", [(2, "range"), (4, "range"), (3, "empty_rank"),
                                           (2, "no_halo")])
 @pytest.mark.parametrize("d", [100, 256, 47, 6])
-@pytest.mark.parametrize("mode", ["split", "pull", "direct"])
+@pytest.mark.parametrize("mode", ["push", "split", "pull", "direct"])
 def test_direct_gather_one_process(world, method, d, mode, monkeypatch):
     """The single-pass peer-gather kernels (TAB SpMM, forward over all in-edges, backward over
     all out-edges) with every rank's staging block in THIS process (LocalBlocks): same kernels
@@ -146,6 +147,8 @@ def test_direct_gather_one_process(world, method, d, mode, monkeypatch):
     from dgl_hack_b200 import backend as F
     from dgl_hack_b200.partition import (Partition, PartitionedGraph, LocalBlocks,
                                          range_partition)
+    # push: the owners store the halo rows into the readers' receive buffers (side stream) while
+    # the inner-source edges are reduced from x itself, halo-source edges added by a second pass;
     # split: halo rows pulled into a local buffer on a side stream while the inner-source edges
     # are reduced, halo-source edges added by a second pass; pull: pull, then one pass over two
     # local slots; direct: one pass gathering in place from every rank's block
@@ -174,17 +177,19 @@ def test_direct_gather_one_process(world, method, d, mode, monkeypatch):
     plans = [Partition.build(n, src, dst, part, r, world) for r in range(world)]
     if method == "no_halo":
         assert all(p.n_halo == 0 and p.n_ohalo == 0 for p in plans)
-    blocks = LocalBlocks.group(world, plans[0].rows_max, 256, dev)
+    blocks = LocalBlocks.group(world, plans[0].rows_max, 256, dev, ext_max=plans[0].ext_max)
     pgs = [PartitionedGraph(p, dev, halo="direct", blocks=b) for p, b in zip(plans, blocks)]
     assert all(pg.gather.mode == mode for pg in pgs)
     assert all(pg.halo_path == "direct" for pg in pgs)
     for _ in range(2):               # second round runs on the alternate blocks
         staged = [pg.gather.stage(0, x[p.inner_global].contiguous(), cs[p.inner_global])
                   for p, pg in zip(plans, pgs)]
+        blocks[0].barrier()
         outs = [pg.gather.reduce(0, b, d, rs[p.inner_global].contiguous(), x)
                 for p, pg, b in zip(plans, pgs, staged)]
         staged = [pg.gather.stage(1, w[p.inner_global].contiguous(), rs[p.inner_global])
                   for p, pg in zip(plans, pgs)]
+        blocks[0].barrier()
         grads = [pg.gather.reduce(1, b, d, cs[p.inner_global].contiguous(), x)
                  for p, pg, b in zip(plans, pgs, staged)]
     for p, out, grad in zip(plans, outs, grads):
