@@ -648,7 +648,11 @@ class PeerGather(object):
             # high priority: the pull's few CTAs get onto the SMs as soon as CTAs of the SpMM
             # that was launched first retire, instead of queueing behind its whole grid
             self._side = torch.cuda.Stream(device=dev, priority=-1)
-            self._pull_blocks = int(os.environ.get("B200_PULL_CTAS_PER_SM", "2")) * \
+            # CTAs per SM of the transfer kernel beside the SpMM (8 GPUs, GCN epoch: push 9.3 /
+            # 9.5 / 10.0 ms at 1 / 2 / 3; the pull needs more loads in flight: 13.5 / 11.4 / 11.6
+            # at 1 / 2 / 4)
+            ctas = os.environ.get("B200_PULL_CTAS_PER_SM", "1" if mode == "push" else "2")
+            self._pull_blocks = int(ctas) * \
                 torch.cuda.get_device_properties(dev).multi_processor_count
             if mode == "push":
                 self._push_lists = [(r.to(dev), c.to(dev)) for r, c in part.push]
