@@ -1018,9 +1018,15 @@ class PeerExchange(object):
         self._k = k
 
     def usable(self, x):
+        """Decided from rank-invariant facts only (dtype, rank, width): ranks that disagreed
+        would issue mismatched collectives. Layout / alignment are fixed locally by _aligned()."""
         return x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and \
-            x.shape[1] <= self.max_feat and x.shape[1] % 4 == 0 and x.is_contiguous() and \
-            x.data_ptr() % 16 == 0  # 128-bit peer stores only; other widths go through NCCL
+            x.shape[1] <= self.max_feat and x.shape[1] % 4 == 0   # 128-bit peer stores only
+
+    @staticmethod
+    def _aligned(x):
+        x = x.contiguous()
+        return x if x.data_ptr() % 16 == 0 else x.clone()
 
     def _push(self, x, which, beg, dst, rows):
         ct = self._ct
@@ -1039,11 +1045,13 @@ class PeerExchange(object):
         return work, self._views[b]
 
     def forward(self, x_inner):
+        x_inner = self._aligned(x_inner)
         work, buf = self._push(x_inner, 0, self._f_beg, self._f_dst, self._rows)
         d = x_inner.shape[1]
         return work, buf[: self.part.n_halo * d].view(self.part.n_halo, d)
 
     def backward(self, g_halo):
+        g_halo = self._aligned(g_halo)
         work, buf = self._push(g_halo, 1, self._b_beg, self._b_dst, None)
         d = g_halo.shape[1]
         return work, buf[: self.total_send * d].view(self.total_send, d)

@@ -1,6 +1,6 @@
 """Only the partitioned leg of bench.py (bench_partitioned.run_partitioned), for A/B runs:
 
-    [B200_HALO_MODE=split|pull|direct] [B200_BENCH_PROFILE=gpurun_out/x.txt] python -m torch.distributed.run \
+    [B200_HALO_MODE=push|split|pull|direct] [B200_BENCH_MODES=split,push@2] [B200_BENCH_PROFILE=gpurun_out/x.txt] python -m torch.distributed.run \
         --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29533 \
         profiles/bench_partitioned_only.py [--scale 1] [--steps 5] [--tag name]
 
