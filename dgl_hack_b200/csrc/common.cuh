@@ -279,6 +279,9 @@ struct KernelCall {
   int n_slots = 0;
   // SpMM only, sum reducer: dst = row_scale * (addend + sum); addend may alias dst
   const float* addend = nullptr;
+  // SpMM only: dst rows have a pitch of dst_ld floats and dst_cols valid columns (0 = the
+  // feature width); set by the odd-width route, which gathers from a padded copy
+  int64_t dst_ld = 0, dst_cols = 0;
   cudaStream_t stream;
 };
 

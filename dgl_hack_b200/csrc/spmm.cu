@@ -92,7 +92,8 @@ combine_partials_kernel(const int32_t* __restrict__ heavy_row,
                         const int32_t* __restrict__ heavy_ptr, const float* __restrict__ partial,
                         const int32_t* __restrict__ indptr, float* __restrict__ out,
                         const int32_t* __restrict__ out_map, int D, int red, int mean,
-                        const float* __restrict__ row_scale, const float* addend) {
+                        const float* __restrict__ row_scale, const float* addend, int out_ld,
+                        int out_cols) {
   const int h = blockIdx.x;
   const int r = heavy_row[h];
   const int p0 = heavy_ptr[h], p1 = heavy_ptr[h + 1];
@@ -100,13 +101,13 @@ combine_partials_kernel(const int32_t* __restrict__ heavy_row,
   const int deg = indptr[r + 1] - indptr[r];
   const float dn = (float)(deg > 1 ? deg : 1);
   const float rs = row_scale ? row_scale[r] : 1.f;
-  for (int col = threadIdx.x; col < D; col += blockDim.x) {
+  for (int col = threadIdx.x; col < out_cols; col += blockDim.x) {
     float acc = partial[(int64_t)p0 * D + col];
     for (int k = p0 + 1; k < p1; ++k) acc = red_call(red, acc, partial[(int64_t)k * D + col]);
-    if (addend) acc = __fadd_rn(addend[orow * D + col], acc);
+    if (addend) acc = __fadd_rn(addend[orow * out_ld + col], acc);
     if (mean) acc = __fdiv_rn(acc, dn);
     if (row_scale) acc = __fmul_rn(acc, rs);
-    out[orow * D + col] = acc;
+    out[orow * out_ld + col] = acc;
   }
 }
 
@@ -133,22 +134,31 @@ __global__ void compose_ids_kernel(const int32_t* __restrict__ map,
 }
 
 // out[r, c] = in[r, c] for c < cols (row pitches ld_in / ld_out), 0 for cols <= c < ld_out:
-// re-pitches rows (pad to a 16-byte multiple, or drop the padding again)
+// pads rows to a 16-byte multiple. One item = four output columns (one 16-byte store).
 __global__ void repitch_rows_kernel(const float* __restrict__ in, int64_t ld_in,
                                     float* __restrict__ out, int64_t ld_out, int64_t rows,
                                     int64_t cols) {
-  const int64_t total = rows * ld_out;
+  const int nv = (int)(ld_out / 4);
+  const int64_t total = rows * nv;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int64_t r = i / ld_out, cidx = i - r * ld_out;
-    out[i] = cidx < cols ? __ldg(in + r * ld_in + cidx) : 0.f;
+    const int64_t r = i / nv;
+    const int c0 = (int)(i - r * nv) * 4;
+    const float* src = in + r * ld_in + c0;
+    float4 v;
+    v.x = c0 + 0 < cols ? __ldg(src + 0) : 0.f;
+    v.y = c0 + 1 < cols ? __ldg(src + 1) : 0.f;
+    v.z = c0 + 2 < cols ? __ldg(src + 2) : 0.f;
+    v.w = c0 + 3 < cols ? __ldg(src + 3) : 0.f;
+    *reinterpret_cast<float4*>(out + r * ld_out + c0) = v;
   }
 }
 
+// ld_out % 4 == 0 and out 16-byte aligned (a Scratch buffer)
 static void repitch_rows(const float* in, int64_t ld_in, float* out, int64_t ld_out, int64_t rows,
                          int64_t cols, cudaStream_t s) {
   if (rows <= 0) return;
-  const int blocks = (int)std::min<int64_t>((rows * ld_out + 255) / 256, 148 * 32);
+  const int blocks = (int)std::min<int64_t>((rows * (ld_out / 4) + 255) / 256, 148 * 32);
   repitch_rows_kernel<<<blocks, 256, 0, s>>>(in, ld_in, out, ld_out, rows, cols);
   note_kernel(nullptr, 1);
 }
@@ -213,6 +223,7 @@ bool try_spmm(const KernelCall& c) {
   a.write_empty = 0;
   for (int i = 0; i < kMaxSlots; ++i) a.a_tab[i] = (c.a_tab && i < c.n_slots) ? c.a_tab[i] : nullptr;
   a.addend = c.addend;
+  a.out_ld = a.out_cols = 0;  // set below, once D is known
   int bmode = kBNone;
   bool use_out_csr, walk_in_plain = false;
   // (tensor, target, user map) of the two gathered operands in "row/col of the walked CSR" terms
@@ -327,23 +338,22 @@ bool try_spmm(const KernelCall& c) {
     const int which = c.mode != kFwd ? 2 : (A == c.lhs ? 0 : 1);
     const int64_t a_rows = which == 2 ? c.out_rows : (which == 0 ? c.lhs_rows : c.rhs_rows);
     Scratch a_pad((size_t)std::max<int64_t>(a_rows, 1) * Dp * 4, s);
-    Scratch o_pad((size_t)std::max<int64_t>(c.dst_rows, 1) * Dp * 4, s);
     repitch_rows(A, D, a_pad.as<float>(), Dp, a_rows, D, s);
     KernelCall c2 = c;
     if (which == 0) c2.lhs = a_pad.as<float>();
     else if (which == 1) c2.rhs = a_pad.as<float>();
     else c2.gout = a_pad.as<float>();
-    c2.dst = o_pad.as<float>();
+    // the result goes straight into the caller's rows (pitch D, 4-byte stores): one streaming
+    // pass over the operand is all the padding costs
+    c2.dst_ld = D;
+    c2.dst_cols = D;
     auto widen = [&](int* shape, int64_t* len) {
       if (*len == D) { shape[0] = (int)Dp; *len = Dp; }
     };
     widen(c2.bc.lhs_shape, &c2.bc.lhs_len);
     widen(c2.bc.rhs_shape, &c2.bc.rhs_len);
     widen(c2.bc.out_shape, &c2.bc.out_len);
-    if (try_spmm(c2)) {
-      repitch_rows(o_pad.as<float>(), Dp, c.dst, D, c.dst_rows, D, s);
-      return true;
-    }
+    if (try_spmm(c2)) return true;
   }
 
   // ---- vector width from divisibility and pointer alignment
@@ -352,7 +362,8 @@ bool try_spmm(const KernelCall& c) {
   };
   int vec = 4;
   while (vec > 1) {
-    bool ok = (D % vec == 0) && aligned(A, vec * 4) && aligned(c.dst, vec * 4);
+    // odd-pitch output rows (dst_cols set) are written with 4-byte stores: no alignment needed
+    bool ok = (D % vec == 0) && aligned(A, vec * 4) && (c.dst_cols || aligned(c.dst, vec * 4));
     if (bmode == kBFull) ok = ok && aligned(B, vec * 4);
     if (bmode == kBHead) ok = ok && (a.b_head_div % vec == 0);
     for (int i = 0; c.a_tab && i < c.n_slots; ++i) ok = ok && aligned(c.a_tab[i], vec * 4);
@@ -413,10 +424,13 @@ bool try_spmm(const KernelCall& c) {
   a.nvec = nvec;
   a.out = c.dst;
   a.out_map = o_map;
+  a.out_ld = (int)(c.dst_ld ? c.dst_ld : D);
+  a.out_cols = (int)(c.dst_cols ? c.dst_cols : D);
 
   B200_CHECK(!c.addend || (a.red == kSum && !c.mean && o_map == nullptr && c.dst_rows == csr.n_rows),
              "an addend needs the sum reducer and one output row per reducing node");
-  if (o_map != nullptr || c.dst_rows != csr.n_rows) fill_f32(c.dst, c.dst_rows * D, fill_v, s);
+  if (o_map != nullptr || c.dst_rows != csr.n_rows)
+    fill_f32(c.dst, c.dst_rows * (int64_t)a.out_ld, fill_v, s);
   if (csr.n_rows == 0) return true;
 
   // ---- heavy rows (hubs of power-law graphs) are cut into segments of seg_len edges, each
@@ -440,7 +454,7 @@ bool try_spmm(const KernelCall& c) {
     if (plan.n_seg == 0) return;
     combine_partials_kernel<<<plan.n_heavy, 128, 0, s>>>(
         plan.heavy_row, plan.heavy_ptr, partial.as<float>(), csr.indptr, c.dst, o_map, (int)D,
-        a.red, a.mean, a.row_scale, a.addend);
+        a.red, a.mean, a.row_scale, a.addend, a.out_ld, a.out_cols);
     note_kernel(nullptr, 1);
   };
 

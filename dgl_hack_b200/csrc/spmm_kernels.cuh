@@ -58,6 +58,10 @@ struct SpmmArgs {
   // and allowed to BE out -- the second pass of a two-pass aggregation (partitioned graphs: the
   // halo-source edges added to the inner-source sums) without a separate add kernel
   const float* addend;
+  // output rows of pitch out_ld floats of which the first out_cols are written (out_cols < D:
+  // the operand was gathered from a copy padded to a 16-byte pitch, the result goes straight
+  // into the caller's odd-width rows with 4-byte stores)
+  int out_ld, out_cols;
 };
 
 template <int VEC>
@@ -296,7 +300,7 @@ spmm_kernel(const SpmmArgs a) {
       op = a.partial + item * a.D;
     } else {
       const int64_t orow = a.out_map ? __ldg(a.out_map + r) : r;
-      op = a.out + orow * a.D;
+      op = a.out + orow * a.out_ld;
     }
     const float* addp = (a.addend && !is_seg) ? a.addend + (op - a.out) + cbase : nullptr;
     op += cbase;
@@ -318,7 +322,13 @@ spmm_kernel(const SpmmArgs a) {
 #pragma unroll
           for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fmul_rn(acc[c].v[e], rs);
         }
-        st_vec<VEC>(op + c * lpr * VEC, acc[c]);
+        if (is_seg || a.out_cols == a.D) {
+          st_vec<VEC>(op + c * lpr * VEC, acc[c]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e)
+            if (cbase + c * lpr * VEC + e < a.out_cols) op[c * lpr * VEC + e] = acc[c].v[e];
+        }
       }
     }
   }

@@ -360,7 +360,7 @@ def c5(out):
     src, dst = sbm_graph(n, e, 64, 0.85, 0.5, 5)
     g = B.GraphIndex.from_coo(n, n, src, dst, DEV)
     del src, dst
-    for d in (100, 256, 47):
+    for d in (100, 256, 48, 47):
         x = rand(n, d).requires_grad_(True)
         gout = rand(n, d)
         ms = timeit(lambda: F.copy_reduce("sum", g, 0, x.detach(), n), reps=10, warm=3)
