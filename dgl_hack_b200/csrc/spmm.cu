@@ -111,6 +111,104 @@ combine_partials_kernel(const int32_t* __restrict__ heavy_row,
   }
 }
 
+// Short rows (relation-segment graphs: ~1 edge per (relation, node) row; the halo-source pass of a
+// partitioned aggregation: ~3): the general kernel spends ~330 instructions per warp on a batch of
+// such rows (schedule lookup, id batches, shuffles, unrolled predication) and is issue bound at
+// 46 % with DRAM at 30 % (profiles/r2_c4_ncu_summary.json). Here a lane group walks its row
+// directly -- every lane reads the neighbour id itself (one broadcast transaction), four
+// neighbours' rows in flight -- in the same sequential order, so results are bit-identical.
+// Plain copy + sum (+ row scale, addend); rows longer than seg_len are left to their segments.
+template <int VEC, int CH>
+__global__ void __launch_bounds__(256) spmm_short_rows_kernel(const SpmmArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int lpr = a.lpr;
+  const int sub = lane & (lpr - 1);
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t r = warp * (32 / lpr) + lane / lpr;
+  if (r >= a.n_rows) return;
+  const int beg = __ldg(a.indptr + r), end = __ldg(a.indptr + r + 1);
+  if (a.n_seg > 0 && end - beg > a.seg_len) return;  // heavy row: served by its segments
+  const int cbase = sub * VEC;
+  Vec<VEC> acc[CH];
+#pragma unroll
+  for (int c = 0; c < CH; ++c)
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[c].v[e] = 0.f;
+  auto col_ok = [&](int c) -> bool { return sub + c * lpr < a.nvec; };
+  const float* base = a.A + cbase;
+  int p = beg;
+  for (; p + 4 <= end; p += 4) {
+    int id[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) id[k] = __ldg(a.indices + p + k);
+    Vec<VEC> v[4][CH];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int c = 0; c < CH; ++c)
+        if (col_ok(c)) v[k][c] = ld_vec<VEC>(base + (int64_t)id[k] * a.D + c * lpr * VEC);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int c = 0; c < CH; ++c)
+        if (col_ok(c))
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fadd_rn(acc[c].v[e], v[k][c].v[e]);
+  }
+  {  // up to three left: loads first, then the sums in order
+    const int left = end - p;
+    int id[3];
+    Vec<VEC> v[3][CH];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      if (k < left) id[k] = __ldg(a.indices + p + k);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      if (k < left)
+#pragma unroll
+        for (int c = 0; c < CH; ++c)
+          if (col_ok(c)) v[k][c] = ld_vec<VEC>(base + (int64_t)id[k] * a.D + c * lpr * VEC);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      if (k < left)
+#pragma unroll
+        for (int c = 0; c < CH; ++c)
+          if (col_ok(c))
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fadd_rn(acc[c].v[e], v[k][c].v[e]);
+  }
+  float* op = a.out + r * a.out_ld + cbase;
+  const float* addp = a.addend ? a.addend + r * a.out_ld + cbase : nullptr;
+  const float rs = a.row_scale ? __ldg(a.row_scale + r) : 1.f;
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    if (col_ok(c)) {
+      if (addp) {
+        const Vec<VEC> old = ld_vec<VEC>(addp + c * lpr * VEC);
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fadd_rn(old.v[e], acc[c].v[e]);
+      }
+      if (a.row_scale) {
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fmul_rn(acc[c].v[e], rs);
+      }
+      if (a.out_cols == a.D) {
+        st_vec<VEC>(op + c * lpr * VEC, acc[c]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < VEC; ++e)
+          if (cbase + c * lpr * VEC + e < a.out_cols) op[c * lpr * VEC + e] = acc[c].v[e];
+      }
+    }
+  }
+}
+
+// B200_SPMM_SHORT=0 keeps short-row graphs on the general kernel (A/B runs).
+static bool short_rows_enabled() {
+  const char* e = std::getenv("B200_SPMM_SHORT");
+  return !(e && e[0] == '0');
+}
+
 static int round_tma_ch(int ch) {
   const int allowed[] = {1, 2, 3, 4, 5, 6, 8, 10, 12, 16};
   for (int v : allowed)
@@ -513,6 +611,30 @@ bool try_spmm(const KernelCall& c) {
       combine();
       return true;
     }
+  }
+
+  // ---- short rows: lean kernel for the rows, the general one for the heavy rows' segments only
+  if (short_rows_enabled() && bmode == kBNone && a.red == kSum && !a.mean && a.op == kUseLhs &&
+      a.a_src == kFromCol && a.a_node_map == nullptr && c.a_tab == nullptr && o_map == nullptr &&
+      c.dst_rows == csr.n_rows && vec == 4 && slabs == 1 && ch <= 2 &&
+      E <= 6 * csr.n_rows && forced_path() == 0) {
+    if (plan.n_seg > 0) {
+      SpmmArgs h = a;
+      h.n_rows = 0;  // items = segments only
+      h.n_wide = (lpr < 32 && wide_rows_enabled()) ? plan.n_seg : 0;
+      const int64_t hw = (lpr == 32) ? (int64_t)plan.n_seg
+                                     : h.n_wide + (plan.n_seg - h.n_wide + (32 / lpr) - 1) / (32 / lpr);
+      launch_vec<4>(h, ch, bmode, true, (int)((hw + 7) / 8), s);
+      note_kernel(nullptr, 1);
+    }
+    const int rpw = 32 / lpr;
+    const int64_t sw = (csr.n_rows + rpw - 1) / rpw;
+    const int sblocks = (int)((sw + 7) / 8);
+    if (ch == 1) spmm_short_rows_kernel<4, 1><<<sblocks, 256, 0, s>>>(a);
+    else spmm_short_rows_kernel<4, 2><<<sblocks, 256, 0, s>>>(a);
+    note_kernel("spmm", 1);
+    combine();
+    return true;
   }
 
   // sub-warp rows: segments and (with a degree schedule) rows of >= kLongRow edges get a warp each
