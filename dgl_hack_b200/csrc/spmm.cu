@@ -203,10 +203,19 @@ __global__ void __launch_bounds__(256) spmm_short_rows_kernel(const SpmmArgs a) 
   }
 }
 
-// B200_SPMM_SHORT=0 keeps short-row graphs on the general kernel (A/B runs).
+// B200_SPMM_SHORT=0 keeps short-row graphs on the general kernel (A/B runs);
+// B200_SPMM_SHORT_DEG=<n> moves the mean-degree threshold (default 6).
 static bool short_rows_enabled() {
   const char* e = std::getenv("B200_SPMM_SHORT");
   return !(e && e[0] == '0');
+}
+// Measured (profiles/r2_short_rows_ab.json): whole-warp rows (D >= 100) gain up to ~7 edges per
+// row (arxiv shape D=128: 0.144 -> 0.114 ms) and break even at 25; sub-warp rows (D <= 64) still
+// gain at 25 edges per row (products shape D=48: 3.25 -> 2.43 ms), where the general kernel pays
+// its id batches and shuffles once per lane group.
+static int64_t short_rows_max_degree(int lpr) {
+  const char* e = std::getenv("B200_SPMM_SHORT_DEG");
+  return e ? std::max(1, std::atoi(e)) : (lpr == 32 ? 8 : 32);
 }
 
 static int round_tma_ch(int ch) {
@@ -617,7 +626,7 @@ bool try_spmm(const KernelCall& c) {
   if (short_rows_enabled() && bmode == kBNone && a.red == kSum && !a.mean && a.op == kUseLhs &&
       a.a_src == kFromCol && a.a_node_map == nullptr && c.a_tab == nullptr && o_map == nullptr &&
       c.dst_rows == csr.n_rows && vec == 4 && slabs == 1 && ch <= 2 &&
-      E <= 6 * csr.n_rows && forced_path() == 0) {
+      E <= short_rows_max_degree(lpr) * csr.n_rows && forced_path() == 0) {
     if (plan.n_seg > 0) {
       SpmmArgs h = a;
       h.n_rows = 0;  // items = segments only
