@@ -117,7 +117,8 @@ combine_partials_kernel(const int32_t* __restrict__ heavy_row,
 // 46 % with DRAM at 30 % (profiles/r2_c4_ncu_summary.json). Here a lane group walks its row
 // directly -- every lane reads the neighbour id itself (one broadcast transaction), four
 // neighbours' rows in flight -- in the same sequential order, so results are bit-identical.
-// Plain copy + sum (+ row scale, addend); rows longer than seg_len are left to their segments.
+// Plain copy + sum (+ a scale per gathered row: a.B indexed by the neighbour id, row scale,
+// addend); rows longer than seg_len are left to their segments.
 template <int VEC, int CH>
 __global__ void __launch_bounds__(256) spmm_short_rows_kernel(const SpmmArgs a) {
   const int lane = threadIdx.x & 31;
@@ -148,12 +149,17 @@ __global__ void __launch_bounds__(256) spmm_short_rows_kernel(const SpmmArgs a) 
       for (int c = 0; c < CH; ++c)
         if (col_ok(c)) v[k][c] = ld_vec<VEC>(base + (int64_t)id[k] * a.D + c * lpr * VEC);
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < 4; ++k) {
+      const float sc = a.B ? __ldg(a.B + id[k]) : 1.f;
 #pragma unroll
       for (int c = 0; c < CH; ++c)
         if (col_ok(c))
 #pragma unroll
-          for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fadd_rn(acc[c].v[e], v[k][c].v[e]);
+          for (int e = 0; e < VEC; ++e) {
+            const float val = a.B ? __fmul_rn(v[k][c].v[e], sc) : v[k][c].v[e];
+            acc[c].v[e] = __fadd_rn(acc[c].v[e], val);
+          }
+    }
   }
   {  // up to three left: loads first, then the sums in order
     const int left = end - p;
@@ -170,12 +176,17 @@ __global__ void __launch_bounds__(256) spmm_short_rows_kernel(const SpmmArgs a) 
           if (col_ok(c)) v[k][c] = ld_vec<VEC>(base + (int64_t)id[k] * a.D + c * lpr * VEC);
 #pragma unroll
     for (int k = 0; k < 3; ++k)
-      if (k < left)
+      if (k < left) {
+        const float sc = a.B ? __ldg(a.B + id[k]) : 1.f;
 #pragma unroll
         for (int c = 0; c < CH; ++c)
           if (col_ok(c))
 #pragma unroll
-            for (int e = 0; e < VEC; ++e) acc[c].v[e] = __fadd_rn(acc[c].v[e], v[k][c].v[e]);
+            for (int e = 0; e < VEC; ++e) {
+              const float val = a.B ? __fmul_rn(v[k][c].v[e], sc) : v[k][c].v[e];
+              acc[c].v[e] = __fadd_rn(acc[c].v[e], val);
+            }
+      }
   }
   float* op = a.out + r * a.out_ld + cbase;
   const float* addp = a.addend ? a.addend + r * a.out_ld + cbase : nullptr;
@@ -623,7 +634,10 @@ bool try_spmm(const KernelCall& c) {
   }
 
   // ---- short rows: lean kernel for the rows, the general one for the heavy rows' segments only
-  if (short_rows_enabled() && bmode == kBNone && a.red == kSum && !a.mean && a.op == kUseLhs &&
+  const bool col_scaled = bmode == kBScalar && a.op == kMul && a.b_src == kFromCol &&
+                          a.b_node_map == nullptr;  // GraphConv's source norm inside the sum
+  if (short_rows_enabled() && ((bmode == kBNone && a.op == kUseLhs) || col_scaled) &&
+      a.red == kSum && !a.mean &&
       a.a_src == kFromCol && a.a_node_map == nullptr && c.a_tab == nullptr && o_map == nullptr &&
       c.dst_rows == csr.n_rows && vec == 4 && slabs == 1 && ch <= 2 &&
       E <= short_rows_max_degree(lpr) * csr.n_rows && forced_path() == 0) {
@@ -639,6 +653,7 @@ bool try_spmm(const KernelCall& c) {
     const int rpw = 32 / lpr;
     const int64_t sw = (csr.n_rows + rpw - 1) / rpw;
     const int sblocks = (int)((sw + 7) / 8);
+    if (!col_scaled) a.B = nullptr;
     if (ch == 1) spmm_short_rows_kernel<4, 1><<<sblocks, 256, 0, s>>>(a);
     else spmm_short_rows_kernel<4, 2><<<sblocks, 256, 0, s>>>(a);
     note_kernel("spmm", 1);

@@ -268,7 +268,11 @@ def test_short_row_kernel_is_bit_identical(d, monkeypatch):
         K.scaled_copy_sum(g, False, x, None, rsc, o3)
         o4 = base.clone()
         K.scaled_copy_sum(g, False, x, None, rsc, o4, addend=o4)
-        return [o1, xr.grad, o3, o4]
+        o5 = torch.empty(nd, d, device="cuda")
+        K.scaled_copy_sum(g, False, x, cs, rsc, o5)          # a scale per gathered row as well
+        o6 = torch.empty(ns, d, device="cuda")
+        K.scaled_copy_sum(g, True, go, rsc, cs, o6)           # its gradient: transposed walk
+        return [o1, xr.grad, o3, o4, o5, o6]
     monkeypatch.setenv("B200_SPMM_SHORT", "0")
     general = run()
     monkeypatch.setenv("B200_SPMM_SHORT", "1")
