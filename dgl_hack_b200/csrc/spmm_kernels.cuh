@@ -120,6 +120,9 @@ __device__ __forceinline__ float spmm_value(int op, int b_is_lhs, float av, floa
 // and wants 32+ resident warps whenever accumulators + one neighbour's loads fit in ~60 registers.
 constexpr int min_blocks_for(int vec, int ch, int u, int bmode) {
   const int live = ch * vec * (1 + u * (bmode == kBFull ? 2 : 1)) + (bmode == kBHead ? ch * u : 0);
+  // 48 registers = 5 CTAs per SM where accumulators + one neighbour fit 16 registers (D = 256:
+  // the scaled variant ran at 54 registers = 4 CTAs, 8.85 ms against 7.4 ms for the plain copy)
+  if (vec == 4 && live <= 16) return 5;
   return live <= 40 ? 4 : (live <= 100 ? 2 : 1);
 }
 

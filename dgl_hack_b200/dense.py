@@ -232,7 +232,8 @@ class _TcLinear(torch.autograd.Function):
         a, w, y = ctx.saved_tensors
         g = g.contiguous()
         if ctx.relu:
-            g = g * (y > 0)
+            # one pass (read g, y; write) instead of a compare kernel and a multiply
+            g = torch.ops.aten.threshold_backward(g, y, 0.0)
         ga = tc_gemm(g, w, False) if ctx.needs_input_grad[0] else None
         gw = tc_weight_grad(a, g) if ctx.needs_input_grad[1] else None
         gb = g.sum(0) if ctx.needs_input_grad[2] else None
