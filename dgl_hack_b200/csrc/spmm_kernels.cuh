@@ -206,6 +206,8 @@ spmm_kernel(const SpmmArgs a) {
     // ---- cooperative fetch of up to bw neighbour ids per row
     const int my = base + bl;
     int pa = 0, pb = 0;
+    float psc = 0.f;  // kBScalar: the neighbour's scalar, fetched with the id batch (one gather per
+                      // 32 neighbours instead of a dependent 4-byte load per neighbour)
     if (my < deg) {
       const int p = beg + my;
       int cidx = 0;
@@ -221,6 +223,8 @@ spmm_kernel(const SpmmArgs a) {
         } else if (a.b_src == kFromEid) {
           pb = __ldg(a.b_pos_ids + p);
         }
+        if (BMODE == kBScalar)
+          psc = __ldg(a.B + ((a.b_src == kFromRow) ? b_row_const : (int64_t)pb * a.b_width));
       }
     }
     const int cnt = min(bw, maxdeg - base);  // warp-uniform
@@ -235,7 +239,9 @@ spmm_kernel(const SpmmArgs a) {
         const int srcl = ei & (bw - 1);
         const int ia = __shfl_sync(0xffffffffu, pa, srcl, bw);
         int ib = 0;
-        if (BMODE != kBNone) ib = __shfl_sync(0xffffffffu, pb, srcl, bw);
+        float sck = 0.f;
+        if (BMODE == kBFull || BMODE == kBHead) ib = __shfl_sync(0xffffffffu, pb, srcl, bw);
+        if (BMODE == kBScalar) sck = __shfl_sync(0xffffffffu, psc, srcl, bw);
         const bool on = (ei < bw) && (base + ei < deg);
         const float* ap;
         if (TAB) {
@@ -244,9 +250,9 @@ spmm_kernel(const SpmmArgs a) {
           ap = a.A + (int64_t)ia * a.D + cbase;
         }
         const float* bp = nullptr;
-        if (BMODE != kBNone)
+        if (BMODE == kBFull || BMODE == kBHead)
           bp = a.B + ((a.b_src == kFromRow) ? b_row_const : (int64_t)ib * a.b_width);
-        if (BMODE == kBScalar) ss[k] = on ? __ldg(bp) : 0.f;
+        if (BMODE == kBScalar) ss[k] = on ? sck : 0.f;
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
           if (on && col_ok(c)) {
