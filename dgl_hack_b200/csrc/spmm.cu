@@ -119,7 +119,7 @@ combine_partials_kernel(const int32_t* __restrict__ heavy_row,
 // neighbours' rows in flight -- in the same sequential order, so results are bit-identical.
 // Plain copy + sum (+ a scale per gathered row: a.B indexed by the neighbour id, row scale,
 // addend); rows longer than seg_len are left to their segments.
-template <int VEC, int CH>
+template <int VEC, int CH, bool SCALED>
 __global__ void __launch_bounds__(256) spmm_short_rows_kernel(const SpmmArgs a) {
   const int lane = threadIdx.x & 31;
   const int lpr = a.lpr;
@@ -137,26 +137,31 @@ __global__ void __launch_bounds__(256) spmm_short_rows_kernel(const SpmmArgs a) 
     for (int e = 0; e < VEC; ++e) acc[c].v[e] = 0.f;
   auto col_ok = [&](int c) -> bool { return sub + c * lpr < a.nvec; };
   const float* base = a.A + cbase;
+  // per step: four ids, then their rows AND scales issued back to back, then the sums in order
+  // (fetching the next step's ids ahead was measured and dropped: it helps 25-edge rows by 10 %
+  // but costs rows with 1-7 edges 20-30 % in wasted predicated loads)
   int p = beg;
   for (; p + 4 <= end; p += 4) {
     int id[4];
+    Vec<VEC> v[4][CH];
+    float sc[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) id[k] = __ldg(a.indices + p + k);
-    Vec<VEC> v[4][CH];
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < 4; ++k) {
+      sc[k] = SCALED ? __ldg(a.B + id[k]) : 1.f;
 #pragma unroll
       for (int c = 0; c < CH; ++c)
         if (col_ok(c)) v[k][c] = ld_vec<VEC>(base + (int64_t)id[k] * a.D + c * lpr * VEC);
+    }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float sc = a.B ? __ldg(a.B + id[k]) : 1.f;
 #pragma unroll
       for (int c = 0; c < CH; ++c)
         if (col_ok(c))
 #pragma unroll
           for (int e = 0; e < VEC; ++e) {
-            const float val = a.B ? __fmul_rn(v[k][c].v[e], sc) : v[k][c].v[e];
+            const float val = SCALED ? __fmul_rn(v[k][c].v[e], sc[k]) : v[k][c].v[e];
             acc[c].v[e] = __fadd_rn(acc[c].v[e], val);
           }
     }
@@ -165,25 +170,27 @@ __global__ void __launch_bounds__(256) spmm_short_rows_kernel(const SpmmArgs a) 
     const int left = end - p;
     int id[3];
     Vec<VEC> v[3][CH];
+    float sc[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k)
       if (k < left) id[k] = __ldg(a.indices + p + k);
 #pragma unroll
     for (int k = 0; k < 3; ++k)
-      if (k < left)
+      if (k < left) {
+        sc[k] = SCALED ? __ldg(a.B + id[k]) : 1.f;
 #pragma unroll
         for (int c = 0; c < CH; ++c)
           if (col_ok(c)) v[k][c] = ld_vec<VEC>(base + (int64_t)id[k] * a.D + c * lpr * VEC);
+      }
 #pragma unroll
     for (int k = 0; k < 3; ++k)
       if (k < left) {
-        const float sc = a.B ? __ldg(a.B + id[k]) : 1.f;
 #pragma unroll
         for (int c = 0; c < CH; ++c)
           if (col_ok(c))
 #pragma unroll
             for (int e = 0; e < VEC; ++e) {
-              const float val = a.B ? __fmul_rn(v[k][c].v[e], sc) : v[k][c].v[e];
+              const float val = SCALED ? __fmul_rn(v[k][c].v[e], sc[k]) : v[k][c].v[e];
               acc[c].v[e] = __fadd_rn(acc[c].v[e], val);
             }
       }
@@ -653,9 +660,13 @@ bool try_spmm(const KernelCall& c) {
     const int rpw = 32 / lpr;
     const int64_t sw = (csr.n_rows + rpw - 1) / rpw;
     const int sblocks = (int)((sw + 7) / 8);
-    if (!col_scaled) a.B = nullptr;
-    if (ch == 1) spmm_short_rows_kernel<4, 1><<<sblocks, 256, 0, s>>>(a);
-    else spmm_short_rows_kernel<4, 2><<<sblocks, 256, 0, s>>>(a);
+    if (col_scaled) {
+      if (ch == 1) spmm_short_rows_kernel<4, 1, true><<<sblocks, 256, 0, s>>>(a);
+      else spmm_short_rows_kernel<4, 2, true><<<sblocks, 256, 0, s>>>(a);
+    } else {
+      if (ch == 1) spmm_short_rows_kernel<4, 1, false><<<sblocks, 256, 0, s>>>(a);
+      else spmm_short_rows_kernel<4, 2, false><<<sblocks, 256, 0, s>>>(a);
+    }
     note_kernel("spmm", 1);
     combine();
     return true;
