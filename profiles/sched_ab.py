@@ -25,6 +25,9 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
         x = torch.rand(n, d, device=dev)
         res["scaled fwd D=%d" % d] = round(BC.timeit(lambda: F.scaled_copy_sum(g, x, cs, rs)), 4)
         res["plain fwd D=%d" % d] = round(BC.timeit(lambda: F.copy_reduce("sum", g, 0, x, n)), 4)
+        from dgl_hack_b200 import kernel as K
+        o = torch.empty_like(x)
+        res["scaled bwd D=%d" % d] = round(BC.timeit(lambda: K.scaled_copy_sum(g, True, x, rs, cs, o)), 4)
         del x
     print(json.dumps(res))
 else:
