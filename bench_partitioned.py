@@ -319,7 +319,15 @@ def run_partitioned(rank, world, dev, scale=1, steps=10, warmup=3, epochs=5, par
         return None
     S = torch.stack(allst).cpu()
     cut = float(S[:, 1].sum())
-    remote_reads = int(2 * S[:, 1].max()) if world > 1 else 0   # cut in-edges fwd + as many bwd
+    # rows crossing NVLink per rank and step: push / split / pull move every remote row once per
+    # direction (forward halo + remote destinations of the backward pass); direct reads per edge
+    per_edge = pg.gather is not None and pg.gather.mode == "direct"
+    if world == 1:
+        remote_reads = 0
+    elif per_edge or pg.gather is None:
+        remote_reads = int(2 * S[:, 1].max())
+    else:
+        remote_reads = int((S[:, 3] + S[:, 4]).max())
     rec = {
         "workload": "products_shaped_sbm_full_graph N=%d E=%d D=%d" % (n, e, d),
         "n_gpus": world, "scaling": "strong",
