@@ -179,6 +179,10 @@ struct Csr {
     int32_t* heavy_row = nullptr; // [n_heavy]
     int32_t* heavy_ptr = nullptr; // [n_heavy + 1] segment range of each heavy row
     int32_t* sched = nullptr;     // [n_rows] rows by descending degree class (NULL = natural order)
+    // the same with every row below kLongRow edges in ONE class (natural order); built on the
+    // first request of a one-row-per-warp kernel, and only for graphs whose numbering is local
+    int32_t* sched_nat = nullptr;
+    int8_t nat_state = 0;         // 0 = not probed, 1 = local (sched_nat valid), -1 = not local
   };
   static constexpr int kPlanSlots = 4;
   Plan plan[kPlanSlots];
@@ -253,7 +257,10 @@ const int32_t* csr_rows(DGLB200Graph* g, int walk, cudaStream_t s);      // row-
 // position in the "other" CSR: in -> out, out -> in, in_sorted -> out
 const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s);
 // Segment plan of a CSR for segments of `seg_len` positions (built once; synchronises then).
-SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s);
+// want_natural: the caller's kernel gives every row its own warp (no lockstep between the rows of
+// a warp), so short rows may keep their natural order if the node numbering is local.
+SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s,
+                     bool want_natural = false);
 int segment_length(int64_t num_edges);  // spmm.cu: the segment length every plan is built with
 // Reads the deferred id-validation flag (call only where the stream is synchronised anyway).
 void ensure_valid_ids(DGLB200Graph* g, cudaStream_t s);

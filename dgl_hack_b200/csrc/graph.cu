@@ -449,8 +449,7 @@ const int32_t* csr_to_other(DGLB200Graph* g, int walk, cudaStream_t s) {
 // one class keep their natural order) and the largest degree.
 __global__ void seg_count_kernel(const int32_t* __restrict__ indptr, int64_t n_rows, int seg_len,
                                  int32_t* __restrict__ nseg, int32_t* __restrict__ heavy,
-                                 int32_t* __restrict__ key, int32_t* __restrict__ max_deg,
-                                 int fine_short) {
+                                 int32_t* __restrict__ key, int32_t* __restrict__ max_deg) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   int m = 0;
   for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += stride) {
@@ -464,11 +463,7 @@ __global__ void seg_count_kernel(const int32_t* __restrict__ indptr, int64_t n_r
       const int lg = 31 - __clz(deg);
       cls = 4 * lg + (lg >= 2 ? ((deg >> (lg - 2)) & 3) : 0);
     }
-    // Rows below kLongRow edges form ONE class in natural order: their walks are too short to
-    // make a tail, and interleaving ~25 degree classes over the whole graph re-reads every
-    // community's feature rows once per class (products-shaped SBM graph, D=100: L2 hit rate
-    // 33 %, DRAM 18 GB per launch for a 1 GB matrix). B200_SPMM_SCHED=fine restores the classes.
-    key[r] = h ? 255 : ((deg >= kLongRow || fine_short) ? (127 - cls) : 104);
+    key[r] = h ? 255 : (127 - cls);
     m = max(m, deg);
     if (!h && deg >= kLongRow) atomicAdd(max_deg + 1, 1);
   }
@@ -505,7 +500,47 @@ __global__ void seg_fill_kernel(const int32_t* __restrict__ indptr, int64_t n_ro
     heavy_ptr[heavy_idx[n_rows]] = seg_off[n_rows];  // sentinel: totals after the scans
 }
 
+// Keys of the "natural" schedule: heavy rows last, rows of >= kLongRow edges by degree class
+// (longest first), every shorter row in ONE class -- the stable sort keeps their natural order.
+// Also probes the numbering: of each row's first (up to) four neighbours, how many lie within
+// 1/32 of the id range of the row. Community-ordered graphs (METIS-style numbering, the
+// products-shaped SBM graph: 85 %) keep a community's feature rows in L2 when the rows are
+// walked in natural order; on randomly numbered graphs (a few %) the order buys nothing and the
+// degree classes pack the CTAs better.
+__global__ void natural_keys_kernel(const int32_t* __restrict__ indptr,
+                                    const int32_t* __restrict__ indices, int64_t n_rows,
+                                    int seg_len, int32_t* __restrict__ key,
+                                    unsigned long long* __restrict__ counts) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t window = max((int64_t)1, n_rows / 32);
+  unsigned near = 0, seen = 0;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += stride) {
+    const int beg = indptr[r], deg = indptr[r + 1] - beg;
+    int cls = 0;
+    if (deg > 0) {
+      const int lg = 31 - __clz(deg);
+      cls = 4 * lg + (lg >= 2 ? ((deg >> (lg - 2)) & 3) : 0);
+    }
+    key[r] = deg > seg_len ? 255 : (deg >= kLongRow ? 127 - cls : 104);
+    for (int k = 0; k < min(deg, 4); ++k) {
+      const int64_t d = (int64_t)indices[beg + k] - r;
+      near += (d < window && d > -window) ? 1u : 0u;
+      ++seen;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    near += __shfl_xor_sync(0xffffffffu, near, o);
+    seen += __shfl_xor_sync(0xffffffffu, seen, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(counts, (unsigned long long)near);
+    atomicAdd(counts + 1, (unsigned long long)seen);
+  }
+}
+
 static void free_plan(Csr::Plan& p, cudaStream_t s) {
+  pool_free(p.sched_nat, s);
   pool_free(p.seg_row, s);
   pool_free(p.seg_beg, s);
   pool_free(p.seg_end, s);
@@ -515,7 +550,7 @@ static void free_plan(Csr::Plan& p, cudaStream_t s) {
   p = Csr::Plan();
 }
 
-SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
+SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s, bool want_natural) {
   Csr& csr = (walk == kWalkOut) ? g->out : g->in;  // in_sorted has the in-CSR's degrees
   int slot = -1;
   for (int k = 0; k < Csr::kPlanSlots; ++k)
@@ -549,11 +584,9 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
       Scratch key((size_t)c.n_rows * 4, s), mdeg(8, s);  // [max degree, rows >= kLongRow]
       B200_CUDA(cudaMemsetAsync(mdeg.ptr, 0, 8, s));
       int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 8);
-      const char* sched_env = std::getenv("B200_SPMM_SCHED");
-      const int fine_short = (sched_env && sched_env[0] == 'f') ? 1 : 0;
       seg_count_kernel<<<blocks, 256, 0, s>>>(c.indptr, c.n_rows, seg_len, nseg.as<int32_t>(),
                                               heavy.as<int32_t>(), key.as<int32_t>(),
-                                              mdeg.as<int32_t>(), fine_short);
+                                              mdeg.as<int32_t>());
       note_kernel(nullptr, 1);
       exclusive_scan_i32(nseg.as<int32_t>(), c.n_rows + 1, s);
       exclusive_scan_i32(heavy.as<int32_t>(), c.n_rows + 1, s);
@@ -591,6 +624,44 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
     }
     c.seg_len = seg_len;
   }
+  // ---- natural schedule (lazy): only for callers whose rows do not share a warp, only when a
+  // degree schedule exists at all, and only if the numbering turns out to be local
+  const int32_t* use_sched = c.sched;
+  {
+    const char* env = std::getenv("B200_SPMM_SCHED");  // "fine" / "natural" force one of them
+    const bool force_fine = env && env[0] == 'f', force_nat = env && env[0] == 'n';
+    if (want_natural && c.sched && !force_fine && csr.n_rows == csr.n_cols) {
+      if (pl.nat_state == 0) {
+        const int32_t* idx = (walk == kWalkOut) ? g->out.indices : g->in_s.indices;
+        Scratch key((size_t)c.n_rows * 4, s), cnt(16, s);
+        B200_CUDA(cudaMemsetAsync(cnt.ptr, 0, 16, s));
+        const int blocks = (int)std::min<int64_t>((c.n_rows + 255) / 256, 148 * 8);
+        natural_keys_kernel<<<blocks, 256, 0, s>>>(c.indptr, idx, c.n_rows, seg_len,
+                                                   key.as<int32_t>(),
+                                                   cnt.as<unsigned long long>());
+        note_kernel(nullptr, 1);
+        unsigned long long h[2] = {0, 0};
+        B200_CUDA(cudaMemcpyAsync(h, cnt.ptr, 16, cudaMemcpyDeviceToHost, s));
+        B200_CUDA(cudaStreamSynchronize(s));
+        const bool local = h[1] > 0 && (double)h[0] >= 0.5 * (double)h[1];
+        if (local || force_nat) {
+          Scratch kb((size_t)c.n_rows * 4, s), va((size_t)c.n_rows * 4, s),
+              vb((size_t)c.n_rows * 4, s);
+          int32_t *sk, *sv;
+          radix_sort_pairs(key.as<int32_t>(), kb.as<int32_t>(), nullptr, va.as<int32_t>(),
+                           vb.as<int32_t>(), c.n_rows, 256, &sk, &sv, s);
+          B200_CUDA(pool_alloc(&pl.sched_nat, (size_t)c.n_rows * 4, s));
+          B200_CUDA(cudaMemcpyAsync(pl.sched_nat, sv, (size_t)c.n_rows * 4,
+                                    cudaMemcpyDeviceToDevice, s));
+          B200_CUDA(cudaStreamSynchronize(s));  // the scratch buffers go out of scope
+          pl.nat_state = 1;
+        } else {
+          pl.nat_state = -1;
+        }
+      }
+      if (pl.nat_state == 1) use_sched = pl.sched_nat;
+    }
+  }
   SegPlan p;
   p.seg_len = seg_len;
   p.n_seg = c.n_seg;
@@ -601,7 +672,7 @@ SegPlan csr_segments(DGLB200Graph* g, int walk, int seg_len, cudaStream_t s) {
   p.seg_end = c.seg_end;
   p.heavy_row = c.heavy_row;
   p.heavy_ptr = c.heavy_ptr;
-  p.sched = c.sched;
+  p.sched = use_sched;
   return p;
 }
 

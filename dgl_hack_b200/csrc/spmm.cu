@@ -564,7 +564,10 @@ bool try_spmm(const KernelCall& c) {
   // single-threaded reference) reduction; B200_SPMM_SEG=0 disables segmentation altogether.
   const int64_t warp_bytes = (lpr == 32) ? (int64_t)ch * vec * 128 : D * 4;
   const int unroll = warp_bytes >= 1024 ? 1 : (warp_bytes >= 256 ? 4 : 8);
-  const SegPlan plan = csr_segments(g, walk, segment_length_for(E, D * 4, unroll), s);
+  // whole-warp rows (lpr == 32) do not run in lockstep with other rows: their short rows may
+  // keep the natural order on graphs with a local numbering (graph.cu natural_keys_kernel)
+  const SegPlan plan =
+      csr_segments(g, walk, segment_length_for(E, D * 4, unroll), s, /*want_natural=*/lpr == 32);
   Scratch partial;
   if (plan.n_seg > 0) partial.alloc((size_t)plan.n_seg * D * 4, s);
   a.n_seg = plan.n_seg;

@@ -32,7 +32,7 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
     print(json.dumps(res))
 else:
     out = {}
-    for mode in ("fine", "natural"):
+    for mode in ("fine", "auto"):
         env = dict(os.environ)
         if mode == "fine":
             env["B200_SPMM_SCHED"] = "fine"
