@@ -662,13 +662,14 @@ bool try_spmm(const KernelCall& c) {
     }
     const int rpw = 32 / lpr;
     const int64_t sw = (csr.n_rows + rpw - 1) / rpw;
-    const int sblocks = (int)((sw + 7) / 8);
+    const int T = spmm_block_threads();
+    const int sblocks = (int)((sw * 32 + T - 1) / T);
     if (col_scaled) {
-      if (ch == 1) spmm_short_rows_kernel<4, 1, true><<<sblocks, 256, 0, s>>>(a);
-      else spmm_short_rows_kernel<4, 2, true><<<sblocks, 256, 0, s>>>(a);
+      if (ch == 1) spmm_short_rows_kernel<4, 1, true><<<sblocks, T, 0, s>>>(a);
+      else spmm_short_rows_kernel<4, 2, true><<<sblocks, T, 0, s>>>(a);
     } else {
-      if (ch == 1) spmm_short_rows_kernel<4, 1, false><<<sblocks, 256, 0, s>>>(a);
-      else spmm_short_rows_kernel<4, 2, false><<<sblocks, 256, 0, s>>>(a);
+      if (ch == 1) spmm_short_rows_kernel<4, 1, false><<<sblocks, T, 0, s>>>(a);
+      else spmm_short_rows_kernel<4, 2, false><<<sblocks, T, 0, s>>>(a);
     }
     note_kernel("spmm", 1);
     combine();

@@ -355,24 +355,38 @@ constexpr int unroll_for(int vec, int ch) {
   return bytes >= 1024 ? 1 : (bytes >= 256 ? 4 : 8);
 }
 
+// Threads per CTA of the SpMM launches (B200_SPMM_BLOCK = 64 | 128 | 256; the kernels are
+// compiled for at most 256). A CTA's registers and warp slots are held until its LAST row
+// finishes, so with rows of unequal length small CTAs waste less: measured 256 -> 64 threads on
+// the products-shaped SBM graph D=100 4.31 -> 3.76 ms, D=256 7.00 -> 6.68, D=48 (short-row
+// kernel) 1.52 -> 1.38, config 4 0.241 -> 0.227, Reddit shape D=602 unchanged (29.0 -> 28.9).
+// `blocks256` arrives as the CTA count at 256 threads.
+inline int spmm_block_threads() {
+  const char* e = std::getenv("B200_SPMM_BLOCK");
+  const int t = e ? std::atoi(e) : 64;
+  return (t == 128 || t == 256) ? t : 64;
+}
+
 template <int VEC, int CH, int U>
-static void launch_shape(const SpmmArgs& a, int bmode, bool sum, int blocks, cudaStream_t s) {
+static void launch_shape(const SpmmArgs& a, int bmode, bool sum, int blocks256, cudaStream_t s) {
+  const int T = spmm_block_threads();
+  const int blocks = (int)(((int64_t)blocks256 * 256 + T - 1) / T);
   if (a.a_tab[0] != nullptr) {  // peer-table gather: plain copy + sum only (checked by the caller)
     if (a.lpr == 32) {
-      spmm_kernel<VEC, CH, U, true, kBNone, true, false, true><<<blocks, 256, 0, s>>>(a);
+      spmm_kernel<VEC, CH, U, true, kBNone, true, false, true><<<blocks, T, 0, s>>>(a);
     } else {
       if constexpr (CH == 1)
-        spmm_kernel<VEC, CH, U, true, kBNone, false, false, true><<<blocks, 256, 0, s>>>(a);
+        spmm_kernel<VEC, CH, U, true, kBNone, false, false, true><<<blocks, T, 0, s>>>(a);
     }
     return;
   }
 #define B200_SPMM_LAUNCH(SUMV, BM, MULV)                                             \
   do {                                                                               \
     if (a.lpr == 32) {                                                               \
-      spmm_kernel<VEC, CH, U, SUMV, BM, true, MULV><<<blocks, 256, 0, s>>>(a);       \
+      spmm_kernel<VEC, CH, U, SUMV, BM, true, MULV><<<blocks, T, 0, s>>>(a);       \
     } else {                                                                         \
       if constexpr (CH == 1)                                                         \
-        spmm_kernel<VEC, CH, U, SUMV, BM, false, MULV><<<blocks, 256, 0, s>>>(a);    \
+        spmm_kernel<VEC, CH, U, SUMV, BM, false, MULV><<<blocks, T, 0, s>>>(a);    \
     }                                                                                \
   } while (0)
   // the mul specialisation exists for the sum reducer only (u_mul_e + sum and its transposes)
