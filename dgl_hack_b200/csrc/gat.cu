@@ -623,12 +623,17 @@ static void launch_gat2(const Gat2Args& b, int w4, cudaStream_t s) {
   const int rpw = 32 / b.Gp;
   const int64_t n_short = b.g.n_rows - b.n_long - b.n_heavy;
   const int64_t n_items = b.n_long + b.n_heavy + (n_short + rpw - 1) / rpw;
+  // threads per CTA (B200_GAT_BLOCK = 64 | 128 | 256): see spmm_block_threads()
+  const char* be = std::getenv("B200_GAT_BLOCK");
+  const int tb = be ? std::atoi(be) : 64;   // arxiv shape: 0.158 / 0.467 ms at 256, 0.154 / 0.453 at 64
+  const int T = (tb == 128 || tb == 256) ? tb : 64;
+  const int wpb = T / 32;
   const int blocks = (int)std::max<int64_t>(
-      1, std::min<int64_t>((n_items + 7) / 8, (int64_t)148 * 32));
+      1, std::min<int64_t>((n_items + wpb - 1) / wpb, (int64_t)148 * 32 * (8 / wpb)));
 #define B200_GAT2(W4V)                                                  \
   do {                                                                  \
-    if (FWD) gat_fwd2_kernel<W4V><<<blocks, 256, 0, s>>>(b);            \
-    else gat_bwd2_kernel<W4V><<<blocks, 256, 0, s>>>(b);                \
+    if (FWD) gat_fwd2_kernel<W4V><<<blocks, T, 0, s>>>(b);              \
+    else gat_bwd2_kernel<W4V><<<blocks, T, 0, s>>>(b);                  \
   } while (0)
   switch (w4) {
     case 1: B200_GAT2(1); break;
