@@ -176,13 +176,18 @@ combine_bf16_kernel(const int32_t* __restrict__ heavy_row, const int32_t* __rest
 
 template <int CH, int U>
 void launch(const Bf16Args& a, int64_t n_items, cudaStream_t s) {
+  // 64-thread CTAs by default, as the fp32 kernels (B200_SPMM_BLOCK; spmm_kernels.cuh)
+  const char* be = std::getenv("B200_SPMM_BLOCK");
+  const int tb = be ? std::atoi(be) : 64;
+  const int T = (tb == 128 || tb == 256) ? tb : 64;
+  const int wpb = T / 32;
   if (a.lpr == 32) {
-    const int blocks = (int)((n_items + 7) / 8);
-    spmm_bf16_kernel<CH, U, true><<<blocks, 256, 0, s>>>(a);
+    const int blocks = (int)((n_items + wpb - 1) / wpb);
+    spmm_bf16_kernel<CH, U, true><<<blocks, T, 0, s>>>(a);
   } else {
     if constexpr (CH == 1) {
       const int64_t warps = (n_items + (32 / a.lpr) - 1) / (32 / a.lpr);
-      spmm_bf16_kernel<1, U, false><<<(int)((warps + 7) / 8), 256, 0, s>>>(a);
+      spmm_bf16_kernel<1, U, false><<<(int)((warps + wpb - 1) / wpb), T, 0, s>>>(a);
     }
   }
 }
