@@ -77,6 +77,14 @@ def test_push_plan_fills_every_halo(world, method):
         for r, p in enumerate(plans):
             rows, codes = (t.long() for t in p.push[which])
             assert ((codes >> SLOT_SHIFT) != r).all()
+            # round-robin over the consumers: the k-th row for every consumer comes before the
+            # (k+1)-th row for any consumer (no GPU's ingress takes one sender's whole list at once)
+            cons = (codes >> SLOT_SHIFT).tolist()
+            seen, nth = {}, []
+            for c in cons:
+                nth.append(seen.get(c, 0))
+                seen[c] = nth[-1] + 1
+            assert nth == sorted(nth)
             xb = x[p.inner_global]
             for q in range(world):
                 sel = (codes >> SLOT_SHIFT) == q
